@@ -1,0 +1,249 @@
+// Attention for the tutoring path; head_dim = 64 everywhere (GPT-2 small/large, BERT-base).
+//   attn_prefill : T queries per sequence, causal (GPT-2, HF/integrations/sdpa_attention.py:77: is_causal iff T>1)
+//                  or bidirectional (BERT, HF/models/bert/modeling_bert.py:192-205); scale 1/8.
+//   attn_decode  : one query per (b,h) streaming the KV cache [B][H][Smax][64] - the HBM-bound kernel that
+//                  carries 86 % of the bytes at bs=64.
+#include <math_constants.h>
+
+#include "kernels.h"
+
+namespace {
+
+template <bool FAST> __device__ __forceinline__ float exp_sel(float x) { return FAST ? __expf(x) : expf(x); }
+
+template <typename T> struct Vec16;  // one 16-byte vector of T -> floats
+template <> struct Vec16<float> {
+  static constexpr int N = 4;
+  __device__ static void load(const float* p, float* f) {
+    float4 v = *reinterpret_cast<const float4*>(p);
+    f[0] = v.x; f[1] = v.y; f[2] = v.z; f[3] = v.w;
+  }
+};
+template <> struct Vec16<bf16> {
+  static constexpr int N = 8;
+  __device__ static void load(const bf16* p, float* f) {
+    uint4 v = *reinterpret_cast<const uint4*>(p);
+    unpack_bf16x8(v, f);
+  }
+};
+
+// ------------------------------------------------------------------------------------ decode
+// grid (H, B), 128 threads.  A row of K (64 elements) is covered by LPR lanes holding one 16-byte
+// vector each, so one warp-wide load instruction fetches KPW whole keys (fully coalesced 512 B).
+// Every lane group runs its own online softmax over its share of the keys (4-way unrolled for
+// memory-level parallelism); the 4*KPW partial states are merged once at the end through smem.
+template <typename QT, typename KT, typename OT, bool FAST>
+__global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__ q, const KT* __restrict__ kc,
+                                                          const KT* __restrict__ vc, OT* __restrict__ out, int H,
+                                                          int Smax, const int* __restrict__ len_dev, int len_host) {
+  constexpr int EPL = Vec16<KT>::N;  // elements per lane
+  constexpr int LPR = 64 / EPL;      // lanes per key row
+  constexpr int KPW = 32 / LPR;      // keys per warp-wide load
+  constexpr int NG = 4 * KPW;        // lane groups per block
+  constexpr int UNR = 4;
+  const int h = blockIdx.x, b = blockIdx.y;
+  const int len = len_dev ? *len_dev : len_host;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = warp * KPW + lane / LPR;  // this lane's group
+  const int e0 = (lane % LPR) * EPL;      // first element of the row this lane owns
+  const size_t base = ((size_t)b * H + h) * Smax * 64;
+  const KT* kb = kc + base + e0;
+  const KT* vb = vc + base + e0;
+
+  float qv[EPL];
+  {
+    const QT* qp = q + ((size_t)b * H + h) * 64 + e0;
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) qv[i] = to_f32(qp[i]) * 0.125f;  // scale = head_dim^-0.5
+  }
+  float m = -CUDART_INF_F, l = 0.f, o[EPL];
+#pragma unroll
+  for (int i = 0; i < EPL; ++i) o[i] = 0.f;
+
+  // trip count is uniform per warp (the shuffles below need every lane); groups past the end are masked
+  for (int jw = warp * KPW; jw < len; jw += NG * UNR) {
+    const int j0 = jw + lane / LPR;
+    float kf[UNR][EPL], s[UNR];
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      int j = min(j0 + u * NG, len - 1);  // clamped: masked below, never out of bounds
+      Vec16<KT>::load(kb + (size_t)j * 64, kf[u]);
+    }
+    float vf[UNR][EPL];
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      int j = min(j0 + u * NG, len - 1);
+      Vec16<KT>::load(vb + (size_t)j * 64, vf[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      float d = 0.f;
+#pragma unroll
+      for (int i = 0; i < EPL; ++i) d = fmaf(qv[i], kf[u][i], d);
+#pragma unroll
+      for (int off = LPR / 2; off > 0; off >>= 1) d += __shfl_xor_sync(0xffffffffu, d, off);
+      s[u] = (j0 + u * NG < len) ? d : -CUDART_INF_F;
+    }
+    float mn = m;
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) mn = fmaxf(mn, s[u]);
+    if (mn == -CUDART_INF_F) continue;  // this group has seen no valid key yet (no shuffles below)
+    float corr = exp_sel<FAST>(m - mn);
+    l *= corr;
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) o[i] *= corr;
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      float p = exp_sel<FAST>(s[u] - mn);
+      l += p;
+#pragma unroll
+      for (int i = 0; i < EPL; ++i) o[i] = fmaf(p, vf[u][i], o[i]);
+    }
+    m = mn;
+  }
+
+  __shared__ float sm_m[NG], sm_l[NG], sm_o[NG][64];
+  if (lane % LPR == 0) { sm_m[g] = m; sm_l[g] = l; }
+#pragma unroll
+  for (int i = 0; i < EPL; ++i) sm_o[g][e0 + i] = o[i];
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    float M = -CUDART_INF_F;
+#pragma unroll
+    for (int s2 = 0; s2 < NG; ++s2) M = fmaxf(M, sm_m[s2]);
+    float num = 0.f, den = 0.f;
+#pragma unroll
+    for (int s2 = 0; s2 < NG; ++s2) {
+      float w = (sm_m[s2] == -CUDART_INF_F) ? 0.f : exp_sel<FAST>(sm_m[s2] - M);
+      num = fmaf(w, sm_o[s2][threadIdx.x], num);
+      den = fmaf(w, sm_l[s2], den);
+    }
+    out[((size_t)b * H + h) * 64 + threadIdx.x] = from_f32<OT>(num / den);
+  }
+}
+
+// ----------------------------------------------------------------------------------- prefill
+// grid (ceil(T/64), H, B), 64 threads: one query row per thread (q and the output accumulator live in
+// registers), K/V tiles of 32 keys staged in shared memory as fp32 and read by broadcast.
+// fp32 math throughout; exact expf in parity mode.
+constexpr int PF_Q = 64, PF_KT = 32;
+
+template <typename QT, typename KT, typename OT, bool FAST>
+__global__ void __launch_bounds__(PF_Q) attn_prefill_kernel(const QT* __restrict__ q, const KT* __restrict__ kc,
+                                                            const KT* __restrict__ vc, OT* __restrict__ out, int H,
+                                                            int T, int Smax, int causal) {
+  __shared__ __align__(16) float Ks[PF_KT][64];
+  __shared__ __align__(16) float Vs[PF_KT][64];
+  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int tid = threadIdx.x;
+  const int qi = qt * PF_Q + tid;
+  const int qc = min(qi, T - 1);
+  const int d = H * 64;
+  float qv[64], o[64];
+  {
+    const QT* qp = q + ((size_t)b * T + qc) * d + h * 64;
+#pragma unroll
+    for (int i = 0; i < 64; ++i) { qv[i] = to_f32(qp[i]) * 0.125f; o[i] = 0.f; }
+  }
+  float m = -CUDART_INF_F, l = 0.f;
+  const size_t base = ((size_t)b * H + h) * Smax * 64;
+  const int kend = causal ? min(T, (qt + 1) * PF_Q) : T;  // keys this block can ever need
+  for (int k0 = 0; k0 < kend; k0 += PF_KT) {
+    __syncthreads();
+    constexpr int EPL = Vec16<KT>::N;
+    for (int v = tid; v < PF_KT * 64 / EPL; v += PF_Q) {
+      int r = v / (64 / EPL), c = (v % (64 / EPL)) * EPL;
+      int j = min(k0 + r, T - 1);
+      float f[EPL];
+      Vec16<KT>::load(kc + base + (size_t)j * 64 + c, f);
+#pragma unroll
+      for (int i = 0; i < EPL; ++i) Ks[r][c + i] = f[i];
+      Vec16<KT>::load(vc + base + (size_t)j * 64 + c, f);
+#pragma unroll
+      for (int i = 0; i < EPL; ++i) Vs[r][c + i] = f[i];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int sub = 0; sub < PF_KT; sub += 16) {
+      float s[16];
+      float mn = m;
+#pragma unroll
+      for (int jj = 0; jj < 16; ++jj) {
+        float acc = 0.f;
+#pragma unroll
+        for (int i = 0; i < 64; i += 4) {
+          float4 kk = *reinterpret_cast<const float4*>(&Ks[sub + jj][i]);
+          acc = fmaf(qv[i], kk.x, acc); acc = fmaf(qv[i + 1], kk.y, acc);
+          acc = fmaf(qv[i + 2], kk.z, acc); acc = fmaf(qv[i + 3], kk.w, acc);
+        }
+        int j = k0 + sub + jj;
+        bool ok = (j < T) && (!causal || j <= qc);
+        s[jj] = ok ? acc : -CUDART_INF_F;
+        mn = fmaxf(mn, s[jj]);
+      }
+      if (mn == -CUDART_INF_F) continue;  // nothing visible yet for this row in this sub-tile
+      float corr = exp_sel<FAST>(m - mn);
+      l *= corr;
+#pragma unroll
+      for (int i = 0; i < 64; ++i) o[i] *= corr;
+#pragma unroll
+      for (int jj = 0; jj < 16; ++jj) {
+        float p = exp_sel<FAST>(s[jj] - mn);
+        l += p;
+#pragma unroll
+        for (int i = 0; i < 64; i += 4) {
+          float4 vv = *reinterpret_cast<const float4*>(&Vs[sub + jj][i]);
+          o[i] = fmaf(p, vv.x, o[i]); o[i + 1] = fmaf(p, vv.y, o[i + 1]);
+          o[i + 2] = fmaf(p, vv.z, o[i + 2]); o[i + 3] = fmaf(p, vv.w, o[i + 3]);
+        }
+      }
+      m = mn;
+    }
+  }
+  if (qi < T) {
+    OT* op = out + ((size_t)b * T + qi) * d + h * 64;
+    float inv = 1.0f / l;
+#pragma unroll
+    for (int i = 0; i < 64; ++i) op[i] = from_f32<OT>(o[i] * inv);
+  }
+}
+
+}  // namespace
+
+int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int kv_dtype, void* out, int out_dtype,
+                  int B, int H, int Smax, const int* len_dev, int len_host, cudaStream_t st) {
+  if (B == 0) return TUTOR_OK;
+  ARG_CHECK(len_dev || (len_host >= 1 && len_host <= Smax), "attn_decode: len %d outside [1,%d]", len_host, Smax);
+  dim3 grid(H, B), block(128);
+  if (q_dtype == DT_F32 && kv_dtype == DT_F32 && out_dtype == DT_F32)
+    attn_decode_kernel<float, float, float, false><<<grid, block, 0, st>>>(
+        (const float*)q, (const float*)k, (const float*)v, (float*)out, H, Smax, len_dev, len_host);
+  else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16)
+    attn_decode_kernel<bf16, bf16, bf16, true><<<grid, block, 0, st>>>(
+        (const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)out, H, Smax, len_dev, len_host);
+  else {
+    tutor_set_error("attn_decode: unsupported dtype combination q=%d kv=%d out=%d", q_dtype, kv_dtype, out_dtype);
+    return TUTOR_ERR_ARG;
+  }
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+
+int k_attn_prefill(const void* q, int q_dtype, const void* k, const void* v, int kv_dtype, void* out, int out_dtype,
+                   int B, int H, int T, int Smax, int causal, cudaStream_t st) {
+  if (B == 0 || T == 0) return TUTOR_OK;
+  ARG_CHECK(T <= Smax, "attn_prefill: T=%d > Smax=%d", T, Smax);
+  dim3 grid(ceil_div(T, PF_Q), H, B), block(PF_Q);
+  if (q_dtype == DT_F32 && kv_dtype == DT_F32 && out_dtype == DT_F32)
+    attn_prefill_kernel<float, float, float, false><<<grid, block, 0, st>>>(
+        (const float*)q, (const float*)k, (const float*)v, (float*)out, H, T, Smax, causal);
+  else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16)
+    attn_prefill_kernel<bf16, bf16, bf16, true><<<grid, block, 0, st>>>(
+        (const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)out, H, T, Smax, causal);
+  else {
+    tutor_set_error("attn_prefill: unsupported dtype combination q=%d kv=%d out=%d", q_dtype, kv_dtype, out_dtype);
+    return TUTOR_ERR_ARG;
+  }
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}

@@ -1,0 +1,195 @@
+// C-ABI glue: error text, launch counter, weight upload helpers and the single-kernel entry points
+// declared in include/tutor_b200.h.
+#include <atomic>
+#include <cstring>
+#include <vector>
+
+#include "engine_common.h"
+
+namespace {
+thread_local char g_err[1024] = "";
+std::atomic<uint64_t> g_launches{0};
+
+inline uint16_t f32_to_bf16_rne(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);  // NaN stays NaN
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+}  // namespace
+
+void tutor_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int tutor_cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  const char* base = strrchr(file, '/');
+  tutor_set_error("CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), base ? base + 1 : file, line, what);
+  return TUTOR_ERR_CUDA;
+}
+
+void tutor_count_launches(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int tutor_require_device(int device) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    tutor_set_error("no CUDA device is available (%s); this library has no CPU fallback",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    return TUTOR_ERR_CUDA;
+  }
+  ARG_CHECK(device >= 0 && device < n, "device %d out of range (have %d)", device, n);
+  cudaDeviceProp p;
+  CUDA_TRY(cudaGetDeviceProperties(&p, device));
+  if (p.major != 10) {
+    tutor_set_error("device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, p.major, p.minor);
+    return TUTOR_ERR_CUDA;
+  }
+  CUDA_TRY(cudaSetDevice(device));
+  return TUTOR_OK;
+}
+
+int upload_f32(float** dst, const float* src, size_t n) {
+  dev_free(*dst);
+  TRY(dev_alloc(dst, n * sizeof(float)));
+  CUDA_TRY(cudaMemcpy(*dst, src, n * sizeof(float), cudaMemcpyHostToDevice));
+  return TUTOR_OK;
+}
+
+int upload_matrix(void** dst, const float* src, int64_t rows, int64_t cols, bool transpose, int dt) {
+  const size_t n = (size_t)rows * cols;
+  dev_free(*dst);
+  std::vector<float> t;
+  const float* s = src;
+  if (transpose) {
+    t.resize(n);
+    constexpr int64_t TB = 32;  // blocked so both sides stay cache-friendly on the host
+    for (int64_t r0 = 0; r0 < rows; r0 += TB)
+      for (int64_t c0 = 0; c0 < cols; c0 += TB)
+        for (int64_t r = r0; r < rows && r < r0 + TB; ++r)
+          for (int64_t c = c0; c < cols && c < c0 + TB; ++c) t[(size_t)c * rows + r] = src[(size_t)r * cols + c];
+    s = t.data();
+  }
+  if (dt == DT_F32) {
+    TRY(dev_alloc(dst, n * 4));
+    CUDA_TRY(cudaMemcpy(*dst, s, n * 4, cudaMemcpyHostToDevice));
+  } else {
+    std::vector<uint16_t> h(n);
+    for (size_t i = 0; i < n; ++i) h[i] = f32_to_bf16_rne(s[i]);
+    TRY(dev_alloc(dst, n * 2));
+    CUDA_TRY(cudaMemcpy(*dst, h.data(), n * 2, cudaMemcpyHostToDevice));
+  }
+  return TUTOR_OK;
+}
+
+extern "C" {
+
+const char* tutor_last_error(void) { return g_err; }
+int tutor_version(void) { return 100; }
+uint64_t tutor_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int tutor_layernorm(const float* x, const float* gamma, const float* beta, float eps, float* out_f32, void* out_bf16,
+                    int M, int d, void* stream) {
+  ARG_CHECK(x && gamma && beta && (out_f32 || out_bf16), "layernorm: null argument");
+  return k_layernorm(x, 1, 0, gamma, beta, eps, out_f32, (bf16*)out_bf16, M, d, (cudaStream_t)stream);
+}
+
+int tutor_linear(int dtype, const void* A, const void* W, const float* bias, const float* residual, void* out,
+                 int out_is_f32, int M, int N, int K, int act, int impl, void* stream) {
+  ARG_CHECK(A && W && out, "linear: null argument");
+  GemmEpilogue e{};
+  e.bias = bias; e.residual = residual; e.act = act; e.ldo = N;
+  if (dtype == DT_F32) {
+    e.out_f32 = (float*)out;
+    return k_gemm_f32((const float*)A, (const float*)W, M, N, K, e, (cudaStream_t)stream);
+  }
+  ARG_CHECK(dtype == DT_BF16, "linear: bad dtype %d", dtype);
+  if (out_is_f32) e.out_f32 = (float*)out; else e.out_bf16 = (bf16*)out;
+  if (impl == 1) return k_gemm_bf16_legacy((const bf16*)A, (const bf16*)W, M, N, K, e, (cudaStream_t)stream);
+  return k_gemm_bf16((const bf16*)A, (const bf16*)W, M, N, K, e, (cudaStream_t)stream);
+}
+
+int tutor_attn_prefill(int dtype, const void* q, const void* k, const void* v, void* out, int B, int H, int T, int Smax,
+                       int causal, void* stream) {
+  ARG_CHECK(q && k && v && out, "attn_prefill: null argument");
+  return k_attn_prefill(q, dtype, k, v, dtype, out, dtype, B, H, T, Smax, causal, (cudaStream_t)stream);
+}
+
+int tutor_attn_decode(int dtype, const void* q, const void* k, const void* v, void* out, int B, int H, int Smax, int len,
+                      void* stream) {
+  ARG_CHECK(q && k && v && out, "attn_decode: null argument");
+  return k_attn_decode(q, dtype, k, v, dtype, out, dtype, B, H, Smax, nullptr, len, (cudaStream_t)stream);
+}
+
+size_t tutor_lmhead_scratch_bytes(int B) { return k_lmhead_scratch_bytes(B, 0); }
+
+int tutor_lmhead_argmax(int dtype, const void* x, const void* wte, int B, int V, int d, const uint32_t* seen,
+                        float penalty, int32_t* out_idx, void* scratch, void* stream) {
+  ARG_CHECK(x && wte && out_idx && scratch, "lmhead_argmax: null argument");
+  ARG_CHECK(penalty == 1.0f || seen, "lmhead_argmax: a penalty needs the seen bitmap");
+  DecodeState ds{};
+  ds.seen = const_cast<uint32_t*>(seen);
+  ds.seen_words = ceil_div(V, 32);
+  ds.penalty = penalty;
+  ds.plain_out = out_idx;
+  return k_lmhead_argmax(x, dtype, wte, dtype, B, V, d, ds, scratch, (cudaStream_t)stream);
+}
+
+int tutor_meanpool(const float* x, float* out, int B, int T, int d, void* stream) {
+  ARG_CHECK(x && out && T >= 1, "meanpool: bad argument");
+  return k_meanpool(x, out, B, T, d, (cudaStream_t)stream);
+}
+
+int tutor_cosine_pairs(const float* a, const float* b, float* out, int B, int d, void* stream) {
+  ARG_CHECK(a && b && out, "cosine_pairs: null argument");
+  return k_cosine_pairs(a, b, out, B, d, 1e-8f, (cudaStream_t)stream);
+}
+
+int tutor_cosine_pairs_host(const float* a, const float* b, float* out, int B, int d) {
+  ARG_CHECK(a && b && out && B >= 1 && d >= 1, "cosine_pairs_host: bad argument");
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+  TRY(tutor_require_device(dev));
+  float *da = nullptr, *db = nullptr, *dout = nullptr;
+  const size_t n = (size_t)B * d * sizeof(float);
+  int rc = TUTOR_OK;
+  if ((rc = dev_alloc(&da, n)) == TUTOR_OK && (rc = dev_alloc(&db, n)) == TUTOR_OK &&
+      (rc = dev_alloc(&dout, B * sizeof(float))) == TUTOR_OK) {
+    cudaError_t e = cudaMemcpy(da, a, n, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(db, b, n, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) rc = tutor_cuda_fail(e, "cudaMemcpy", __FILE__, __LINE__);
+    if (rc == TUTOR_OK) rc = k_cosine_pairs(da, db, dout, B, d, 1e-8f, nullptr);
+    if (rc == TUTOR_OK) {
+      e = cudaMemcpy(out, dout, B * sizeof(float), cudaMemcpyDeviceToHost);
+      if (e != cudaSuccess) rc = tutor_cuda_fail(e, "cudaMemcpy", __FILE__, __LINE__);
+    }
+  }
+  dev_free(da); dev_free(db); dev_free(dout);
+  return rc;
+}
+
+int tutor_row_inv_norm(const float* corpus, float* inv_norm, int N, int d, void* stream) {
+  ARG_CHECK(corpus && inv_norm, "row_inv_norm: null argument");
+  return k_row_inv_norm(corpus, DT_F32, inv_norm, N, d, 1e-8f, (cudaStream_t)stream);
+}
+
+size_t tutor_cosine_topk_scratch_bytes(int Q, int N, int k) { return k_cosine_topk_scratch_bytes(Q, N, k); }
+
+int tutor_cosine_topk(const float* queries, const float* corpus, const float* inv_norm, int Q, int N, int d, int k,
+                      float* out_scores, int32_t* out_idx, int idx_base, void* scratch, void* stream) {
+  ARG_CHECK(queries && corpus && inv_norm && out_scores && out_idx && scratch, "cosine_topk: null argument");
+  return k_cosine_topk(queries, corpus, DT_F32, inv_norm, Q, N, d, k, out_scores, out_idx, idx_base, scratch,
+                       (cudaStream_t)stream);
+}
+
+int tutor_topk_merge(const float* cand_scores, const int32_t* cand_idx, int Q, int ncand, int k, float* out_scores,
+                     int32_t* out_idx, void* stream) {
+  ARG_CHECK(cand_scores && cand_idx && out_scores && out_idx, "topk_merge: null argument");
+  return k_topk_merge(cand_scores, cand_idx, Q, ncand, k, out_scores, out_idx, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,232 @@
+// Row-wise kernels of the tutoring path: embeddings, LayerNorm (+residual), mean-pool, cosine.
+// All HBM-bound: one warp per row, 128-bit loads, row cached in registers, shuffle reductions.
+#include "kernels.h"
+
+namespace {
+
+constexpr int LN_V4 = 16;               // float4 slots per lane: supports d <= 2048 (GPT-2 large: 1280)
+constexpr int LN_MAX_PER_LANE = 4 * LN_V4;  // fully unrolled so the row stays in registers
+
+// ---- GPT-2 embedding: x[m,:] = wte[id] + wpe[pos]   (HF/models/gpt2/modeling_gpt2.py:577-585)
+template <typename WT>
+__global__ void gpt2_embed_kernel(const int32_t* __restrict__ ids, int ids_ld, const int* __restrict__ len_dev,
+                                  int T, const WT* __restrict__ wte, const float* __restrict__ wpe, int d,
+                                  float* __restrict__ x, int M) {
+  int m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (m >= M) return;
+  int lane = threadIdx.x & 31;
+  int b = m / T, t = m - b * T;
+  int pos = len_dev ? (*len_dev - 1) : t;  // decode: the last token written; prefill: 0..T-1
+  int id = ids[(size_t)b * ids_ld + pos];
+  const WT* e = wte + (size_t)id * d;
+  const float* p = wpe + (size_t)pos * d;
+  float* o = x + (size_t)m * d;
+  for (int i = lane * 4; i < d; i += 128) {
+    float4 a = load4(e + i), c = load4(p + i);
+    *reinterpret_cast<float4*>(o + i) = make_float4(a.x + c.x, a.y + c.y, a.z + c.z, a.w + c.w);
+  }
+}
+
+// ---- LayerNorm over the last axis, biased variance, two-pass on a register-resident row.
+// in row r is read from x[(r*in_stride + in_offset)*d]; optional fp32 and bf16 outputs.
+__global__ void layernorm_kernel(const float* __restrict__ x, int in_stride, int in_offset,
+                                 const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                                 float* __restrict__ out_f32, bf16* __restrict__ out_bf16, int M, int d) {
+  int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= M) return;
+  int lane = threadIdx.x & 31;
+  const float* xr = x + ((size_t)r * in_stride + in_offset) * d;
+  float v[LN_MAX_PER_LANE];
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < LN_V4; ++j) {
+    int i = lane * 4 + j * 128;
+    float4 a = (i < d) ? load4(xr + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    v[4 * j] = a.x; v[4 * j + 1] = a.y; v[4 * j + 2] = a.z; v[4 * j + 3] = a.w;
+    s += (a.x + a.y) + (a.z + a.w);
+  }
+  float mean = warp_sum(s) / d;
+  float q = 0.f;
+#pragma unroll
+  for (int j = 0; j < LN_V4; ++j) {
+    if (lane * 4 + j * 128 < d) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { float c = v[4 * j + k] - mean; q += c * c; }
+    }
+  }
+  float rstd = 1.0f / sqrtf(warp_sum(q) / d + eps);
+#pragma unroll
+  for (int j = 0; j < LN_V4; ++j) {
+    const int i = lane * 4 + j * 128, nv = 4 * j;
+    if (i >= d) break;
+    float4 g = load4(gamma + i), b = load4(beta + i);
+    float4 o;
+    o.x = (v[nv] - mean) * rstd * g.x + b.x;
+    o.y = (v[nv + 1] - mean) * rstd * g.y + b.y;
+    o.z = (v[nv + 2] - mean) * rstd * g.z + b.z;
+    o.w = (v[nv + 3] - mean) * rstd * g.w + b.w;
+    if (out_f32) *reinterpret_cast<float4*>(out_f32 + (size_t)r * d + i) = o;
+    if (out_bf16) {
+      __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
+      uint2 pk = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+      *reinterpret_cast<uint2*>(out_bf16 + (size_t)r * d + i) = pk;
+    }
+  }
+}
+
+// ---- BERT embeddings: word + token_type(0) + position, then LayerNorm eps 1e-12
+// (HF/models/bert/modeling_bert.py:102-111).
+template <typename WT>
+__global__ void bert_embed_ln_kernel(const int32_t* __restrict__ ids, int T, const WT* __restrict__ word,
+                                     const float* __restrict__ pos, const float* __restrict__ type0,
+                                     const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                                     float* __restrict__ out_f32, bf16* __restrict__ out_bf16, int M, int d) {
+  int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= M) return;
+  int lane = threadIdx.x & 31;
+  int t = r % T;
+  const WT* w = word + (size_t)ids[r] * d;
+  const float* p = pos + (size_t)t * d;
+  float v[LN_MAX_PER_LANE];
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < LN_V4; ++j) {
+    const int i = lane * 4 + j * 128, nv = 4 * j;
+    v[nv] = v[nv + 1] = v[nv + 2] = v[nv + 3] = 0.f;
+    if (i < d) {
+      float4 a = load4(w + i), c = load4(type0 + i), e = load4(p + i);
+      v[nv] = (a.x + c.x) + e.x; v[nv + 1] = (a.y + c.y) + e.y;
+      v[nv + 2] = (a.z + c.z) + e.z; v[nv + 3] = (a.w + c.w) + e.w;
+    }
+    s += (v[nv] + v[nv + 1]) + (v[nv + 2] + v[nv + 3]);
+  }
+  float mean = warp_sum(s) / d;
+  float q = 0.f;
+#pragma unroll
+  for (int j = 0; j < LN_V4; ++j) {
+    if (lane * 4 + j * 128 < d) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { float c = v[4 * j + k] - mean; q += c * c; }
+    }
+  }
+  float rstd = 1.0f / sqrtf(warp_sum(q) / d + eps);
+#pragma unroll
+  for (int j = 0; j < LN_V4; ++j) {
+    const int i = lane * 4 + j * 128, nv = 4 * j;
+    if (i >= d) break;
+    float4 g = load4(gamma + i), b = load4(beta + i);
+    float4 o;
+    o.x = (v[nv] - mean) * rstd * g.x + b.x;
+    o.y = (v[nv + 1] - mean) * rstd * g.y + b.y;
+    o.z = (v[nv + 2] - mean) * rstd * g.z + b.z;
+    o.w = (v[nv + 3] - mean) * rstd * g.w + b.w;
+    if (out_f32) *reinterpret_cast<float4*>(out_f32 + (size_t)r * d + i) = o;
+    if (out_bf16) {
+      __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
+      *reinterpret_cast<uint2*>(out_bf16 + (size_t)r * d + i) =
+          make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+    }
+  }
+}
+
+// ---- unmasked mean over T (REF/lms_server.py:101). grid (d/128, B); each thread owns one column
+// and walks T rows (coalesced 512 B per warp per row); fixed summation order -> deterministic.
+__global__ void meanpool_kernel(const float* __restrict__ x, float* __restrict__ out, int T, int d) {
+  int b = blockIdx.y;
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= d) return;
+  const float* p = x + (size_t)b * T * d + c;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  int t = 0;
+  for (; t + 4 <= T; t += 4) {
+    s0 += p[(size_t)t * d]; s1 += p[(size_t)(t + 1) * d];
+    s2 += p[(size_t)(t + 2) * d]; s3 += p[(size_t)(t + 3) * d];
+  }
+  for (; t < T; ++t) s0 += p[(size_t)t * d];
+  out[(size_t)b * d + c] = ((s0 + s1) + (s2 + s3)) / T;
+}
+
+// ---- F.cosine_similarity(dim=1, eps): x.y / (max(|x|,eps) * max(|y|,eps))  (REF/lms_server.py:104)
+__global__ void cosine_pairs_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                    float* __restrict__ out, int B, int d, float eps) {
+  int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= B) return;
+  int lane = threadIdx.x & 31;
+  float dot = 0.f, na = 0.f, nb = 0.f;
+  for (int i = lane; i < d; i += 32) {
+    float x = a[(size_t)r * d + i], y = b[(size_t)r * d + i];
+    dot += x * y; na += x * x; nb += y * y;
+  }
+  dot = warp_sum(dot); na = warp_sum(na); nb = warp_sum(nb);
+  if (lane == 0) out[r] = dot / (fmaxf(sqrtf(na), eps) * fmaxf(sqrtf(nb), eps));
+}
+
+// ---- mark every prompt token in the per-sequence seen-bitmap (for the fused repetition penalty)
+__global__ void seen_bitmap_kernel(const int32_t* __restrict__ ids, int ids_ld, int T, uint32_t* __restrict__ seen,
+                                   int words_per_row, int B) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * T) return;
+  int b = i / T, t = i - b * T;
+  int id = ids[(size_t)b * ids_ld + t];
+  atomicOr(&seen[(size_t)b * words_per_row + (id >> 5)], 1u << (id & 31));
+}
+
+}  // namespace
+
+int k_gpt2_embed(const int32_t* ids, int ids_ld, const int* len_dev, int T, const void* wte, int wdtype,
+                 const float* wpe, int d, float* x, int M, cudaStream_t st) {
+  ARG_CHECK(d % 4 == 0, "embed: d %% 4 != 0");
+  dim3 grid(ceil_div(M, 8)), block(256);
+  if (wdtype == DT_F32)
+    gpt2_embed_kernel<float><<<grid, block, 0, st>>>(ids, ids_ld, len_dev, T, (const float*)wte, wpe, d, x, M);
+  else
+    gpt2_embed_kernel<bf16><<<grid, block, 0, st>>>(ids, ids_ld, len_dev, T, (const bf16*)wte, wpe, d, x, M);
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+
+int k_layernorm(const float* x, int in_stride, int in_offset, const float* gamma, const float* beta, float eps,
+                float* out_f32, bf16* out_bf16, int M, int d, cudaStream_t st) {
+  ARG_CHECK(d % 4 == 0 && d <= 32 * LN_MAX_PER_LANE, "layernorm: unsupported d=%d", d);
+  if (M == 0) return TUTOR_OK;
+  layernorm_kernel<<<ceil_div(M, 4), 128, 0, st>>>(x, in_stride, in_offset, gamma, beta, eps, out_f32, out_bf16, M, d);
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+
+int k_bert_embed_ln(const int32_t* ids, int T, const void* word, int wdtype, const float* pos, const float* type0,
+                    const float* gamma, const float* beta, float eps, float* out_f32, bf16* out_bf16, int M, int d,
+                    cudaStream_t st) {
+  ARG_CHECK(d % 4 == 0 && d <= 32 * LN_MAX_PER_LANE, "bert_embed: unsupported d=%d", d);
+  if (M == 0) return TUTOR_OK;
+  dim3 grid(ceil_div(M, 4)), block(128);
+  if (wdtype == DT_F32)
+    bert_embed_ln_kernel<float><<<grid, block, 0, st>>>(ids, T, (const float*)word, pos, type0, gamma, beta, eps,
+                                                        out_f32, out_bf16, M, d);
+  else
+    bert_embed_ln_kernel<bf16><<<grid, block, 0, st>>>(ids, T, (const bf16*)word, pos, type0, gamma, beta, eps,
+                                                       out_f32, out_bf16, M, d);
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+
+int k_meanpool(const float* x, float* out, int B, int T, int d, cudaStream_t st) {
+  if (B == 0) return TUTOR_OK;
+  meanpool_kernel<<<dim3(ceil_div(d, 128), B), 128, 0, st>>>(x, out, T, d);
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+
+int k_cosine_pairs(const float* a, const float* b, float* out, int B, int d, float eps, cudaStream_t st) {
+  if (B == 0) return TUTOR_OK;
+  cosine_pairs_kernel<<<ceil_div(B, 4), 128, 0, st>>>(a, b, out, B, d, eps);
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+
+int k_seen_bitmap(const int32_t* ids, int ids_ld, int T, uint32_t* seen, int words_per_row, int B, cudaStream_t st) {
+  if (B * T == 0) return TUTOR_OK;
+  seen_bitmap_kernel<<<ceil_div(B * T, 256), 256, 0, st>>>(ids, ids_ld, T, seen, words_per_row, B);
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}

@@ -1,0 +1,471 @@
+// GPT-2 greedy-generation engine behind tutor_gpt2_* (include/tutor_b200.h).
+// Replaces GPT2LMHeadModel.generate as the reference calls it (REF/tutoring_server.py:21-29):
+//   prefill   = GPT2LMHeadModel.forward over the prompt          (HF/models/gpt2/modeling_gpt2.py:522-706)
+//   decode    = the `while unfinished` loop of GenerationMixin._sample, greedy branch
+//               (HF/generation/utils.py:2743-2805), one captured CUDA graph replayed per token with a
+//               device-side length counter - no per-step host sync, no torch.cat cache regrowth
+//               (HF/cache_utils.py:119-120): the KV cache is preallocated [L][2][B][H][Smax][64].
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "engine_common.h"
+
+struct Gpt2Layer {
+  float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
+  Linear qkv, proj, fc, proj2;
+};
+
+struct tutor_gpt2 {
+  tutor_gpt2_config cfg{};
+  int device = 0, dt = DT_F32;
+  int d = 0, H = 0, L = 0, V = 0, P = 0;
+  std::mutex mu;
+  cudaStream_t stream = nullptr;
+  // weights
+  void* wte = nullptr;
+  float *wpe = nullptr, *lnf_g = nullptr, *lnf_b = nullptr;
+  std::vector<Gpt2Layer> layers;
+  std::map<std::string, bool> loaded;
+  // KV cache [L][2][Bcap][H][Smax][64]
+  void* kv = nullptr;
+  int Bcap = 0, Smax = 0;
+  // activations for up to Mcap tokens
+  int Mcap = 0;
+  float* x = nullptr;
+  void *xn = nullptr, *q = nullptr, *att = nullptr, *hbuf = nullptr, *xn_last = nullptr;
+  // decode state
+  int32_t* ids = nullptr;
+  int ids_ld = 0;
+  int* counters = nullptr;  // [0]=len [1]=stop_len
+  uint32_t* seen = nullptr;
+  int seen_words = 0;
+  int* finished = nullptr;
+  void* lm_scratch = nullptr;
+  int* h_counters = nullptr;  // pinned
+  // current generation
+  int cur_B = 0, cur_T = 0, cur_total = 0;
+  float cur_penalty = 1.f;
+  int cur_eos = -1, cur_pad = 0;
+  // decode graph
+  cudaGraphExec_t graph_exec = nullptr;
+  uint64_t graph_kernels = 0;
+  bool use_graph = true;
+
+  size_t esz() const { return dt == DT_F32 ? 4 : 2; }
+  void* kcache(int l) const {
+    return (uint8_t*)kv + (size_t)(2 * l) * Bcap * H * Smax * 64 * esz();
+  }
+  void* vcache(int l) const {
+    return (uint8_t*)kv + (size_t)(2 * l + 1) * Bcap * H * Smax * 64 * esz();
+  }
+  DecodeState dstate() const {
+    DecodeState ds{};
+    ds.ids = ids; ds.ids_ld = ids_ld; ds.len = counters; ds.stop_len = counters + 1;
+    ds.seen = seen; ds.seen_words = seen_words; ds.finished = finished;
+    ds.penalty = cur_penalty; ds.eos_id = cur_eos; ds.pad_id = cur_pad;
+    return ds;
+  }
+};
+
+namespace {
+
+void drop_graph(tutor_gpt2* e) {
+  if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
+}
+
+int gemm(tutor_gpt2* e, const void* A, const Linear& w, int M, const GemmEpilogue& epi) {
+  if (e->dt == DT_F32) return k_gemm_f32((const float*)A, (const float*)w.w, M, w.N, w.K, epi, e->stream);
+  return k_gemm_bf16((const bf16*)A, (const bf16*)w.w, M, w.N, w.K, epi, e->stream);
+}
+
+// One forward over M = B*T tokens.  decode=true: T == 1 and every position comes from the device counter.
+int forward(tutor_gpt2* e, int B, int T, bool decode) {
+  const int M = B * T, d = e->d, dt = e->dt;
+  cudaStream_t st = e->stream;
+  const int* len_dev = decode ? e->counters : nullptr;
+  float* xn_f = dt == DT_F32 ? (float*)e->xn : nullptr;
+  bf16* xn_b = dt == DT_BF16 ? (bf16*)e->xn : nullptr;
+  TRY(k_gpt2_embed(e->ids, e->ids_ld, len_dev, T, e->wte, dt, e->wpe, d, e->x, M, st));
+  for (int l = 0; l < e->L; ++l) {
+    const Gpt2Layer& w = e->layers[l];
+    TRY(k_layernorm(e->x, 1, 0, w.ln1_g, w.ln1_b, e->cfg.layer_norm_epsilon, xn_f, xn_b, M, d, st));
+    GemmEpilogue qe{};  // c_attn + split + cache append (modeling_gpt2.py:185-196)
+    qe.bias = w.qkv.b;
+    qe.out_f32 = dt == DT_F32 ? (float*)e->q : nullptr;
+    qe.out_bf16 = dt == DT_BF16 ? (bf16*)e->q : nullptr;
+    qe.ldo = d; qe.qkv_mode = 1; qe.kv_dtype = dt;
+    qe.kcache = e->kcache(l); qe.vcache = e->vcache(l);
+    qe.d = d; qe.H = e->H; qe.Smax = e->Smax; qe.T = T; qe.pos0 = 0; qe.pos_dev = len_dev;
+    TRY(gemm(e, e->xn, w.qkv, M, qe));
+    if (decode)
+      TRY(k_attn_decode(e->q, dt, e->kcache(l), e->vcache(l), dt, e->att, dt, B, e->H, e->Smax, e->counters, 0, st));
+    else
+      TRY(k_attn_prefill(e->q, dt, e->kcache(l), e->vcache(l), dt, e->att, dt, B, e->H, T, e->Smax, 1, st));
+    GemmEpilogue pe{};  // attn c_proj + residual (modeling_gpt2.py:223, 282)
+    pe.bias = w.proj.b; pe.residual = e->x; pe.out_f32 = e->x; pe.ldo = d;
+    TRY(gemm(e, e->att, w.proj, M, pe));
+    TRY(k_layernorm(e->x, 1, 0, w.ln2_g, w.ln2_b, e->cfg.layer_norm_epsilon, xn_f, xn_b, M, d, st));
+    GemmEpilogue fe{};  // c_fc + gelu_new (modeling_gpt2.py:239-240)
+    fe.bias = w.fc.b; fe.act = ACT_GELU_TANH; fe.ldo = 4 * d;
+    fe.out_f32 = dt == DT_F32 ? (float*)e->hbuf : nullptr;
+    fe.out_bf16 = dt == DT_BF16 ? (bf16*)e->hbuf : nullptr;
+    TRY(gemm(e, e->xn, w.fc, M, fe));
+    GemmEpilogue oe{};  // mlp c_proj + residual (modeling_gpt2.py:241, 307)
+    oe.bias = w.proj2.b; oe.residual = e->x; oe.out_f32 = e->x; oe.ldo = d;
+    TRY(gemm(e, e->hbuf, w.proj2, M, oe));
+  }
+  // ln_f on the last position of every row only (logits_to_keep = 1, HF/generation/utils.py:2490-2491)
+  TRY(k_layernorm(e->x, T, T - 1, e->lnf_g, e->lnf_b, e->cfg.layer_norm_epsilon,
+                  dt == DT_F32 ? (float*)e->xn_last : nullptr, dt == DT_BF16 ? (bf16*)e->xn_last : nullptr, B, d, st));
+  TRY(k_lmhead_argmax(e->xn_last, dt, e->wte, dt, B, e->V, d, e->dstate(), e->lm_scratch, st));
+  return TUTOR_OK;
+}
+
+int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
+  const int Smax = (int)round_up(total, 64);
+  const size_t es = e->esz();
+  if (B > e->Bcap || Smax > e->Smax) {
+    drop_graph(e);
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    const int nb = B > e->Bcap ? B : e->Bcap, ns = Smax > e->Smax ? Smax : e->Smax;
+    if (e->kv) CUDA_TRY(cudaFree(e->kv));
+    e->kv = nullptr;
+    const size_t bytes = (size_t)e->L * 2 * nb * e->H * ns * 64 * es;
+    CUDA_TRY(cudaMalloc(&e->kv, bytes));
+    // rows past the current length are read (masked) by the attention kernels: they must hold finite values
+    CUDA_TRY(cudaMemsetAsync(e->kv, 0, bytes, e->stream));
+    dev_free(e->ids); dev_free(e->seen); dev_free(e->finished); dev_free(e->lm_scratch); dev_free(e->xn_last);
+    e->ids_ld = ns;
+    e->seen_words = ceil_div(e->V, 32);
+    TRY(dev_alloc(&e->ids, (size_t)nb * ns * sizeof(int32_t)));
+    TRY(dev_alloc(&e->seen, (size_t)nb * e->seen_words * sizeof(uint32_t)));
+    TRY(dev_alloc(&e->finished, (size_t)nb * sizeof(int)));
+    TRY(dev_alloc(&e->lm_scratch, k_lmhead_scratch_bytes(nb, e->V)));
+    TRY(dev_alloc(&e->xn_last, (size_t)nb * e->d * 4));
+    e->Bcap = nb; e->Smax = ns;
+  }
+  const int M = B * T;
+  if (M > e->Mcap) {
+    drop_graph(e);
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    dev_free(e->x); dev_free(e->xn); dev_free(e->q); dev_free(e->att); dev_free(e->hbuf);
+    const size_t d = e->d;
+    TRY(dev_alloc(&e->x, (size_t)M * d * 4));
+    TRY(dev_alloc(&e->xn, (size_t)M * d * es));
+    TRY(dev_alloc(&e->q, (size_t)M * d * es));
+    TRY(dev_alloc(&e->att, (size_t)M * d * es));
+    TRY(dev_alloc(&e->hbuf, (size_t)M * 4 * d * es));
+    e->Mcap = M;
+  }
+  return TUTOR_OK;
+}
+
+int check_args(tutor_gpt2* e, int B, int T, int total) {
+  ARG_CHECK(e != nullptr, "gpt2: null handle");
+  ARG_CHECK(B >= 1 && T >= 1, "gpt2.generate: empty input (B=%d, T=%d)", B, T);
+  // transformers raises ValueError here (generation/utils.py:1575-1581)
+  ARG_CHECK(T < total, "Input length of input_ids is %d, but `max_length` is set to %d. This can lead to unexpected "
+            "behavior. You should consider increasing `max_length` or, better yet, setting `max_new_tokens`.", T, total);
+  // position ids index wpe (modeling_gpt2.py:584): the last forward embeds position total-2
+  ARG_CHECK(total - 1 <= e->P, "gpt2.generate: total length %d exceeds n_positions %d (+1)", total, e->P);
+  ARG_CHECK(e->dt == DT_F32 || B <= 128, "gpt2.generate: bf16 mode supports batch <= 128 per call (got %d)", B);
+  return TUTOR_OK;
+}
+
+// common prologue once the prompt is in e->ids (device, int32, row stride ids_ld)
+int start_generation(tutor_gpt2* e, int B, int T, int total, float penalty, int eos, int pad) {
+  if (penalty != e->cur_penalty || eos != e->cur_eos || pad != e->cur_pad || B != e->cur_B) drop_graph(e);
+  e->cur_B = B; e->cur_T = T; e->cur_total = total; e->cur_penalty = penalty; e->cur_eos = eos; e->cur_pad = pad;
+  cudaStream_t st = e->stream;
+  e->h_counters[0] = T; e->h_counters[1] = 0;
+  CUDA_TRY(cudaMemcpyAsync(e->counters, e->h_counters, 2 * sizeof(int), cudaMemcpyHostToDevice, st));
+  CUDA_TRY(cudaMemsetAsync(e->finished, 0, (size_t)B * sizeof(int), st));
+  CUDA_TRY(cudaMemsetAsync(e->seen, 0, (size_t)B * e->seen_words * sizeof(uint32_t), st));
+  // the penalty covers every id so far, prompt included (logits_process.py:404-410)
+  TRY(k_seen_bitmap(e->ids, e->ids_ld, T, e->seen, e->seen_words, B, st));
+  return forward(e, B, T, false);  // selects token T, len becomes T+1
+}
+
+int run_steps(tutor_gpt2* e, int n_steps, bool poll_eos) {
+  const int B = e->cur_B;
+  cudaStream_t st = e->stream;
+  for (int i = 0; i < n_steps; ++i) {
+    if (e->use_graph && e->graph_exec) {
+      CUDA_TRY(cudaGraphLaunch(e->graph_exec, st));
+      tutor_count_launches(e->graph_kernels);
+    } else {
+      TRY(forward(e, B, 1, true));  // first step runs eagerly (also sets every kernel attribute) ...
+      if (e->use_graph && !e->graph_exec) {  // ... then one step is captured and replayed from here on
+        cudaGraph_t g = nullptr;
+        const uint64_t before = tutor_launch_count();
+        CUDA_TRY(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        int rc = forward(e, B, 1, true);
+        cudaError_t ce = cudaStreamEndCapture(st, &g);
+        const uint64_t n = tutor_launch_count() - before;
+        tutor_count_launches((uint64_t)0 - n);  // captured launches did not run
+        if (rc != TUTOR_OK) { if (g) cudaGraphDestroy(g); return rc; }
+        if (ce != cudaSuccess) return tutor_cuda_fail(ce, "cudaStreamEndCapture", __FILE__, __LINE__);
+        ce = cudaGraphInstantiate(&e->graph_exec, g, 0);
+        cudaGraphDestroy(g);
+        if (ce != cudaSuccess) return tutor_cuda_fail(ce, "cudaGraphInstantiate", __FILE__, __LINE__);
+        e->graph_kernels = n;
+      }
+    }
+    if (poll_eos && e->cur_eos >= 0 && (i % 32) == 31 && i + 1 < n_steps) {
+      CUDA_TRY(cudaMemcpyAsync(e->h_counters, e->counters, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(cudaStreamSynchronize(st));
+      if (e->h_counters[1] != 0) break;  // every row has produced EOS (utils.py:2804-2805)
+    }
+  }
+  return TUTOR_OK;
+}
+
+int read_counters(tutor_gpt2* e, int* len, int* stop_len) {
+  CUDA_TRY(cudaMemcpyAsync(e->h_counters, e->counters, 2 * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  *len = e->h_counters[0];
+  *stop_len = e->h_counters[1];
+  return TUTOR_OK;
+}
+
+int upload_prompt(tutor_gpt2* e, const int64_t* ids_host, int B, int T) {
+  std::vector<int32_t> tmp((size_t)B * T);
+  for (size_t i = 0; i < tmp.size(); ++i) {
+    ARG_CHECK(ids_host[i] >= 0 && ids_host[i] < e->V, "gpt2.generate: token id %lld outside [0,%d)",
+              (long long)ids_host[i], e->V);
+    tmp[i] = (int32_t)ids_host[i];
+  }
+  CUDA_TRY(cudaMemcpy2DAsync(e->ids, (size_t)e->ids_ld * 4, tmp.data(), (size_t)T * 4, (size_t)T * 4, B,
+                             cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(cudaStreamSynchronize(e->stream));  // tmp is pageable and about to go out of scope
+  return TUTOR_OK;
+}
+
+struct NameParts { int layer; std::string rest; };
+NameParts split_name(const std::string& full) {
+  std::string n = full;
+  if (n.rfind("transformer.", 0) == 0) n = n.substr(12);
+  NameParts p{-1, n};
+  if (n.rfind("h.", 0) == 0) {
+    size_t dot = n.find('.', 2);
+    p.layer = atoi(n.substr(2, dot - 2).c_str());
+    p.rest = n.substr(dot + 1);
+  }
+  return p;
+}
+
+}  // namespace
+
+extern "C" {
+
+int tutor_gpt2_create(const tutor_gpt2_config* cfg, int device, tutor_gpt2_t** out) {
+  ARG_CHECK(cfg && out, "gpt2_create: null argument");
+  ARG_CHECK(cfg->n_embd == cfg->n_head * 64, "gpt2_create: head_dim must be 64 (n_embd=%d n_head=%d)", cfg->n_embd,
+            cfg->n_head);
+  ARG_CHECK(cfg->n_embd % 128 == 0, "gpt2_create: n_embd must be a multiple of 128");
+  ARG_CHECK(cfg->dtype == DT_F32 || cfg->dtype == DT_BF16, "gpt2_create: bad dtype %d", cfg->dtype);
+  TRY(tutor_require_device(device));
+  tutor_gpt2* e = new tutor_gpt2();
+  e->cfg = *cfg; e->device = device; e->dt = cfg->dtype;
+  e->d = cfg->n_embd; e->H = cfg->n_head; e->L = cfg->n_layer; e->V = cfg->vocab_size; e->P = cfg->n_positions;
+  e->layers.resize(e->L);
+  e->use_graph = getenv("TUTOR_NO_GRAPH") == nullptr;
+  if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaMalloc(&e->counters, 2 * sizeof(int)) != cudaSuccess ||
+      cudaMallocHost(&e->h_counters, 2 * sizeof(int)) != cudaSuccess) {
+    int rc = tutor_cuda_fail(cudaGetLastError(), "gpt2_create", __FILE__, __LINE__);
+    delete e;
+    return rc;
+  }
+  *out = e;
+  return TUTOR_OK;
+}
+
+void tutor_gpt2_destroy(tutor_gpt2_t* e) {
+  if (!e) return;
+  cudaSetDevice(e->device);
+  cudaStreamSynchronize(e->stream);
+  drop_graph(e);
+  dev_free(e->wte); dev_free(e->wpe); dev_free(e->lnf_g); dev_free(e->lnf_b);
+  for (auto& l : e->layers) {
+    dev_free(l.ln1_g); dev_free(l.ln1_b); dev_free(l.ln2_g); dev_free(l.ln2_b);
+    dev_free(l.qkv.w); dev_free(l.qkv.b); dev_free(l.proj.w); dev_free(l.proj.b);
+    dev_free(l.fc.w); dev_free(l.fc.b); dev_free(l.proj2.w); dev_free(l.proj2.b);
+  }
+  dev_free(e->kv); dev_free(e->x); dev_free(e->xn); dev_free(e->q); dev_free(e->att); dev_free(e->hbuf);
+  dev_free(e->xn_last); dev_free(e->ids); dev_free(e->counters); dev_free(e->seen); dev_free(e->finished);
+  dev_free(e->lm_scratch);
+  if (e->h_counters) cudaFreeHost(e->h_counters);
+  cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+int tutor_gpt2_load_tensor(tutor_gpt2_t* e, const char* name, const float* data, const int64_t* shape, int ndim) {
+  ARG_CHECK(e && name && data && shape, "gpt2_load_tensor: null argument");
+  std::lock_guard<std::mutex> lock(e->mu);
+  CUDA_TRY(cudaSetDevice(e->device));
+  const std::string full(name);
+  if (full == "lm_head.weight") return TUTOR_OK;  // tied to wte
+  NameParts p = split_name(full);
+  if (p.rest == "attn.bias" || p.rest == "attn.masked_bias") return TUTOR_OK;  // causal-mask buffers
+  const int d = e->d;
+  auto want = [&](int64_t a, int64_t b) -> int {
+    bool ok = (b < 0) ? (ndim == 1 && shape[0] == a) : (ndim == 2 && shape[0] == a && shape[1] == b);
+    ARG_CHECK(ok, "gpt2_load_tensor: %s has the wrong shape", name);
+    return TUTOR_OK;
+  };
+  int rc = TUTOR_ERR_ARG;
+  if (p.layer < 0) {
+    if (p.rest == "wte.weight") { TRY(want(e->V, d)); rc = upload_matrix(&e->wte, data, e->V, d, false, e->dt); }
+    else if (p.rest == "wpe.weight") { TRY(want(e->P, d)); rc = upload_f32(&e->wpe, data, (size_t)e->P * d); }
+    else if (p.rest == "ln_f.weight") { TRY(want(d, -1)); rc = upload_f32(&e->lnf_g, data, d); }
+    else if (p.rest == "ln_f.bias") { TRY(want(d, -1)); rc = upload_f32(&e->lnf_b, data, d); }
+    else { tutor_set_error("gpt2_load_tensor: unknown tensor %s", name); return TUTOR_ERR_ARG; }
+  } else {
+    ARG_CHECK(p.layer < e->L, "gpt2_load_tensor: layer %d out of range in %s", p.layer, name);
+    Gpt2Layer& l = e->layers[p.layer];
+    struct { const char* n; Linear* lin; int K, N; } lins[] = {
+        {"attn.c_attn", &l.qkv, d, 3 * d}, {"attn.c_proj", &l.proj, d, d},
+        {"mlp.c_fc", &l.fc, d, 4 * d}, {"mlp.c_proj", &l.proj2, 4 * d, d}};
+    struct { const char* n; float** ptr; } vecs[] = {
+        {"ln_1.weight", &l.ln1_g}, {"ln_1.bias", &l.ln1_b}, {"ln_2.weight", &l.ln2_g}, {"ln_2.bias", &l.ln2_b}};
+    bool found = false;
+    for (auto& v : vecs)
+      if (p.rest == v.n) { TRY(want(d, -1)); rc = upload_f32(v.ptr, data, d); found = true; }
+    for (auto& li : lins) {
+      if (p.rest == std::string(li.n) + ".weight") {
+        TRY(want(li.K, li.N));  // Conv1D stores [in,out]; transpose to [out,in]
+        rc = upload_matrix(&li.lin->w, data, li.K, li.N, true, e->dt);
+        li.lin->N = li.N; li.lin->K = li.K; found = true;
+      } else if (p.rest == std::string(li.n) + ".bias") {
+        TRY(want(li.N, -1));
+        rc = upload_f32(&li.lin->b, data, li.N); found = true;
+      }
+    }
+    if (!found) { tutor_set_error("gpt2_load_tensor: unknown tensor %s", name); return TUTOR_ERR_ARG; }
+  }
+  if (rc == TUTOR_OK) e->loaded[(p.layer < 0 ? std::string() : "h." + std::to_string(p.layer) + ".") + p.rest] = true;
+  return rc;
+}
+
+int tutor_gpt2_check_loaded(tutor_gpt2_t* e) {
+  ARG_CHECK(e, "gpt2: null handle");
+  std::vector<std::string> need = {"wte.weight", "wpe.weight", "ln_f.weight", "ln_f.bias"};
+  const char* per[] = {"ln_1.weight", "ln_1.bias", "ln_2.weight", "ln_2.bias", "attn.c_attn.weight", "attn.c_attn.bias",
+                       "attn.c_proj.weight", "attn.c_proj.bias", "mlp.c_fc.weight", "mlp.c_fc.bias",
+                       "mlp.c_proj.weight", "mlp.c_proj.bias"};
+  for (int l = 0; l < e->L; ++l)
+    for (const char* n : per) need.push_back("h." + std::to_string(l) + "." + n);
+  for (auto& n : need)
+    if (!e->loaded.count(n)) {
+      tutor_set_error("gpt2: weight transformer.%s has not been loaded", n.c_str());
+      return TUTOR_ERR_STATE;
+    }
+  return TUTOR_OK;
+}
+
+int tutor_gpt2_prefill(tutor_gpt2_t* e, const int64_t* ids_host, int B, int T, int total, float penalty, int eos,
+                       int pad) {
+  TRY(check_args(e, B, T, total));
+  ARG_CHECK(ids_host, "gpt2: null ids");
+  std::lock_guard<std::mutex> lock(e->mu);
+  CUDA_TRY(cudaSetDevice(e->device));
+  TRY(tutor_gpt2_check_loaded(e));
+  TRY(ensure_capacity(e, B, T, total));
+  TRY(upload_prompt(e, ids_host, B, T));
+  return start_generation(e, B, T, total, penalty, eos, pad);
+}
+
+int tutor_gpt2_step(tutor_gpt2_t* e, int n_steps) {
+  ARG_CHECK(e && e->cur_B > 0, "gpt2_step: no generation in progress");
+  std::lock_guard<std::mutex> lock(e->mu);
+  CUDA_TRY(cudaSetDevice(e->device));
+  int len, stop;
+  TRY(read_counters(e, &len, &stop));
+  ARG_CHECK(len + n_steps <= e->cur_total, "gpt2_step: %d more steps would exceed max length %d (len %d)", n_steps,
+            e->cur_total, len);
+  return run_steps(e, n_steps, false);
+}
+
+static int read_ids_locked(tutor_gpt2_t* e, int64_t* out_host, int cap, int* out_len, int* stop_len) {
+  int len, stop;
+  TRY(read_counters(e, &len, &stop));
+  const int n = stop ? stop : len;
+  ARG_CHECK((size_t)cap >= (size_t)e->cur_B * n, "gpt2_read_ids: output capacity %d < %d", cap, e->cur_B * n);
+  std::vector<int32_t> tmp((size_t)e->cur_B * n);
+  CUDA_TRY(cudaMemcpy2D(tmp.data(), (size_t)n * 4, e->ids, (size_t)e->ids_ld * 4, (size_t)n * 4, e->cur_B,
+                        cudaMemcpyDeviceToHost));
+  for (size_t i = 0; i < tmp.size(); ++i) out_host[i] = tmp[i];
+  *out_len = n;
+  if (stop_len) *stop_len = stop;
+  return TUTOR_OK;
+}
+
+int tutor_gpt2_read_ids(tutor_gpt2_t* e, int64_t* out_host, int cap, int* out_len, int* stop_len) {
+  ARG_CHECK(e && e->cur_B > 0 && out_host && out_len, "gpt2_read_ids: bad argument or no generation in progress");
+  std::lock_guard<std::mutex> lock(e->mu);
+  CUDA_TRY(cudaSetDevice(e->device));
+  return read_ids_locked(e, out_host, cap, out_len, stop_len);
+}
+
+int tutor_gpt2_generate(tutor_gpt2_t* e, const int64_t* ids_host, int B, int T, int total, float penalty, int eos,
+                        int pad, int64_t* out_host, int* out_len) {
+  TRY(check_args(e, B, T, total));
+  ARG_CHECK(ids_host && out_host && out_len, "gpt2.generate: null argument");
+  std::lock_guard<std::mutex> lock(e->mu);  // held to the end: 10 gRPC handler threads share one engine
+  CUDA_TRY(cudaSetDevice(e->device));
+  TRY(tutor_gpt2_check_loaded(e));
+  TRY(ensure_capacity(e, B, T, total));
+  TRY(upload_prompt(e, ids_host, B, T));
+  TRY(start_generation(e, B, T, total, penalty, eos, pad));
+  TRY(run_steps(e, total - T - 1, true));
+  return read_ids_locked(e, out_host, B * total, out_len, nullptr);
+}
+
+int tutor_gpt2_generate_dev(tutor_gpt2_t* e, const int32_t* ids_dev, int B, int T, int total, float penalty, int eos,
+                            int pad, int32_t* out_dev, int* out_len) {
+  TRY(check_args(e, B, T, total));
+  ARG_CHECK(ids_dev && out_dev && out_len, "gpt2.generate_dev: null argument");
+  std::lock_guard<std::mutex> lock(e->mu);
+  CUDA_TRY(cudaSetDevice(e->device));
+  TRY(tutor_gpt2_check_loaded(e));
+  TRY(ensure_capacity(e, B, T, total));
+  CUDA_TRY(cudaMemcpy2DAsync(e->ids, (size_t)e->ids_ld * 4, ids_dev, (size_t)T * 4, (size_t)T * 4, B,
+                             cudaMemcpyDeviceToDevice, e->stream));
+  TRY(start_generation(e, B, T, total, penalty, eos, pad));
+  TRY(run_steps(e, total - T - 1, true));
+  int len, stop;
+  TRY(read_counters(e, &len, &stop));
+  CUDA_TRY(cudaMemcpy2DAsync(out_dev, (size_t)total * 4, e->ids, (size_t)e->ids_ld * 4, (size_t)total * 4, B,
+                             cudaMemcpyDeviceToDevice, e->stream));
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  *out_len = stop ? stop : len;
+  return TUTOR_OK;
+}
+
+int tutor_gpt2_logits(tutor_gpt2_t* e, float* logits_dev) {
+  ARG_CHECK(e && e->cur_B > 0 && logits_dev, "gpt2_logits: bad argument or no forward has run");
+  std::lock_guard<std::mutex> lock(e->mu);
+  CUDA_TRY(cudaSetDevice(e->device));
+  TRY(k_lmhead_logits(e->xn_last, e->dt, e->wte, e->dt, e->cur_B, e->V, e->V, e->d, logits_dev, e->stream));
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  return TUTOR_OK;
+}
+
+double tutor_gpt2_decode_bytes(tutor_gpt2_t* e, int B, int S) {
+  if (!e) return 0.0;
+  const double d = e->d, es = (double)e->esz();
+  // parameters streamed per forward: 12 d^2 + 13 d per layer, 2 d for ln_f, V*d for the tied head
+  const double params = e->L * (12.0 * d * d + 13.0 * d) + 2.0 * d + (double)e->V * d;
+  const double kv_read = (double)B * S * e->L * 2.0 * d * es;
+  const double kv_write = (double)B * e->L * 2.0 * d * es;
+  return params * es + kv_read + kv_write;
+}
+
+void* tutor_gpt2_stream(tutor_gpt2_t* e) { return e ? (void*)e->stream : nullptr; }
+
+}  // extern "C"

@@ -1,0 +1,428 @@
+// bf16 contraction  D[i,j] = sum_k A[i,k] * B[j,k]  on the 5th-gen tensor cores (sm_100a):
+// TMA (cp.async.bulk.tensor, SWIZZLE_128B) stages K-major tiles in shared memory, one elected thread
+// issues tcgen05.mma (UMMA 128 x BN x 16, kind::f16, bf16 in / fp32 accumulate) into TMEM, four
+// epilogue warps read the accumulator back with tcgen05.ld and apply the shared fused epilogue.
+//
+//   prefill / BERT  (M = tokens, large):  A = activations [M,K], B = weights [N,K]   -> EPI_ROWMAJOR
+//   decode (M = batch <= 256, "swap-AB"): A = weights [N,K],     B = activations [M,K] -> EPI_SWAPPED
+//   LM head at decode:                    A = wte [V,K],         B = ln_f(x) [batch,K] -> EPI_ARGMAX
+//                                         (penalty + per-tile argmax; no logits tensor is written)
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
+// warps 2..5 = epilogue (TMEM lane quadrant = warp_id % 4).  Every mbarrier wait is bounded
+// (clock64 deadline -> __trap) so a protocol bug aborts the launch instead of hanging the GPU.
+#include <cuda.h>
+#include <math_constants.h>
+
+#include <mutex>
+
+#include "kernels.h"
+
+namespace {
+
+constexpr int BM = 128, BK = 64, UMMA_K = 16;
+constexpr int NTHREADS = 192;
+enum { EPI_ROWMAJOR = 0, EPI_SWAPPED = 1, EPI_ARGMAX = 2 };
+
+struct ArgmaxArgs {
+  const uint32_t* seen;  // [B][seen_words]
+  int seen_words;
+  float penalty;
+  int V;                 // real vocabulary size (rows >= V are padding)
+  float* part_val;       // [ntiles][B]
+  int* part_idx;
+  int B;
+};
+
+// ------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __noinline__ void mbar_timeout(int which, uint32_t parity) {
+  printf("tutor_b200 gemm_bf16: mbarrier wait timed out (role %d parity %u block %d,%d)\n", which, parity,
+         blockIdx.x, blockIdx.y);
+  __trap();
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int which) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) mbar_timeout(which, parity);  // ~2 s at 2 GHz
+  }
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 lanes x 32 consecutive fp32 columns of TMEM -> 32 registers per thread
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, float* v) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// UMMA shared-memory descriptor, K-major operand, SWIZZLE_128B, one 128-byte swizzle atom along K:
+// start address >>4 in [0,14), LBO (unused, 0) in [16,30), SBO = 8 rows * 128 B = 1024 B (>>4) in [32,46),
+// descriptor version 1 in [46,48), layout type SWIZZLE_128B (=2) in [61,64).
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// UMMA instruction descriptor (kind::f16): D=f32 (bits 4-5 = 1), A=B=bf16 (bits 7-9, 10-12 = 1),
+// A and B K-major (bits 15,16 = 0), N>>3 in [17,23), M>>4 in [24,29).
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int m, int n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+template <int BN> struct SmemLayout {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN >= 128) ? 4 : 6;
+  static constexpr int TILE_BYTES = STAGES * STAGE_BYTES;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int TOTAL = TILE_BYTES + BAR_BYTES + 1024;  // +1024: manual 1 KB alignment of the tiles
+};
+
+// vectorised row run: 32 consecutive columns n0.. of row m (EPI_ROWMAJOR)
+__device__ __forceinline__ void store_run32(const GemmEpilogue& e, int m, int n0, int N, float* v) {
+  if (n0 + 32 > N || (e.ldo & 7)) {  // ragged edge: scalar path
+    for (int i = 0; i < 32 && n0 + i < N; ++i) epilogue_store(e, m, n0 + i, v[i]);
+    return;
+  }
+  if (e.bias) {
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      float4 b = *reinterpret_cast<const float4*>(e.bias + n0 + i);
+      v[i] += b.x; v[i + 1] += b.y; v[i + 2] += b.z; v[i + 3] += b.w;
+    }
+  }
+  if (e.act != ACT_NONE) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = apply_act(v[i], e.act);
+  }
+  float* of = nullptr;
+  bf16* ob = nullptr;
+  if (!e.qkv_mode || n0 < e.d) {
+    size_t o = (size_t)m * e.ldo + n0;
+    if (!e.qkv_mode && e.residual) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        float4 r = *reinterpret_cast<const float4*>(e.residual + o + i);
+        v[i] += r.x; v[i + 1] += r.y; v[i + 2] += r.z; v[i + 3] += r.w;
+      }
+    }
+    if (e.out_f32) of = e.out_f32 + o;
+    if (e.out_bf16) ob = e.out_bf16 + o;
+  } else {  // 32 columns sit inside one head's 64-wide row of the K or V cache
+    int which = (n0 >= 2 * e.d);
+    int c = n0 - (which ? 2 * e.d : e.d);
+    int h = c >> 6, i0 = c & 63;
+    int b = m / e.T, t = m - b * e.T;
+    int s = e.pos_dev ? (*e.pos_dev - 1) : (e.pos0 + t);
+    size_t o = (((size_t)b * e.H + h) * e.Smax + s) * 64 + i0;
+    void* base = which ? e.vcache : e.kcache;
+    if (e.kv_dtype == DT_F32) of = reinterpret_cast<float*>(base) + o;
+    else ob = reinterpret_cast<bf16*>(base) + o;
+  }
+  if (of) {
+#pragma unroll
+    for (int i = 0; i < 32; i += 4)
+      *reinterpret_cast<float4*>(of + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+  }
+  if (ob) {
+#pragma unroll
+    for (int i = 0; i < 32; i += 8) {
+      __nv_bfloat162 p0 = __floats2bfloat162_rn(v[i], v[i + 1]), p1 = __floats2bfloat162_rn(v[i + 2], v[i + 3]);
+      __nv_bfloat162 p2 = __floats2bfloat162_rn(v[i + 4], v[i + 5]), p3 = __floats2bfloat162_rn(v[i + 6], v[i + 7]);
+      uint4 pk = make_uint4(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1),
+                            *reinterpret_cast<uint32_t*>(&p2), *reinterpret_cast<uint32_t*>(&p3));
+      *reinterpret_cast<uint4*>(ob + i) = pk;
+    }
+  }
+}
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                      const __grid_constant__ CUtensorMap tmB,
+                                                                      int rowsA, int rowsB, int K, GemmEpilogue epi,
+                                                                      ArgmaxArgs am) {
+  using L = SmemLayout<BN>;
+  constexpr int TMEM_COLS = (BN < 32) ? 32 : BN;  // power of two >= 32 (BN in {16,32,64,128,256})
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + L::TILE_BYTES);
+  uint64_t* empty_bar = full_bar + L::STAGES;
+  uint64_t* tmem_full_bar = empty_bar + L::STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int a_row0 = blockIdx.x * BM, b_row0 = blockIdx.y * BN;
+  const int nk = K / BK;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+    for (int s = 0; s < L::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      for (int kb = 0; kb < nk; ++kb) {
+        const int s = kb % L::STAGES;
+        const uint32_t ph = (kb / L::STAGES) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1, 0);
+        mbar_expect_tx(&full_bar[s], L::STAGE_BYTES);
+        uint8_t* sa = tiles + s * L::STAGE_BYTES;
+        tma_load_2d(sa, &tmA, &full_bar[s], kb * BK, a_row0);
+        tma_load_2d(sa + L::A_BYTES, &tmB, &full_bar[s], kb * BK, b_row0);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+      for (int kb = 0; kb < nk; ++kb) {
+        const int s = kb % L::STAGES;
+        const uint32_t ph = (kb / L::STAGES) & 1;
+        mbar_wait(&full_bar[s], ph, 1);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(tiles + s * L::STAGE_BYTES);
+        const uint32_t sb = sa + L::A_BYTES;
+#pragma unroll
+        for (int k = 0; k < BK / UMMA_K; ++k) {
+          // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle atom
+          tc_mma_bf16(tmem_base, umma_desc_sw128(sa + k * UMMA_K * 2), umma_desc_sw128(sb + k * UMMA_K * 2), idesc,
+                      (kb | k) != 0);
+        }
+        tc_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
+      }
+      tc_commit(tmem_full_bar);    // accumulator complete
+    }
+  } else {
+    // ===== epilogue: 4 warps, each owns the 32 TMEM lanes of its quadrant =====
+    const int quad = warp & 3;
+    const int row = a_row0 + quad * 32 + lane;  // index along A's rows
+    mbar_wait(tmem_full_bar, 0, 2);
+    tc_fence_after();
+    const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16);
+    if (EPI == EPI_ARGMAX) {
+      // per-tile argmax over the 128 vocabulary rows for every batch column
+      float* red_val = reinterpret_cast<float*>(tiles);  // pipeline smem is idle now: [4][BN] + [4][BN]
+      int* red_idx = reinterpret_cast<int*>(tiles + 4 * BN * sizeof(float));
+      const int wslot = warp - 2;
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        float v[32];
+        tc_ld32(taddr + c0, v);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          if (c0 + i >= BN) break;  // BN = 16: only half of the 32-column load is real
+          const int b = b_row0 + c0 + i;
+          float val = v[i];
+          int idx = row;
+          if (b < am.B && am.penalty != 1.0f) {
+            // 32 lanes = 32 consecutive vocabulary rows = one word of the seen-bitmap
+            uint32_t w = am.seen[(size_t)b * am.seen_words + (row >> 5)];
+            if ((w >> (row & 31)) & 1u) val = (val < 0.f) ? val * am.penalty : val / am.penalty;
+          }
+          if (row >= am.V) val = -CUDART_INF_F;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            float ov = __shfl_xor_sync(0xffffffffu, val, o);
+            int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+            if (ov > val || (ov == val && oi < idx)) { val = ov; idx = oi; }
+          }
+          if (lane == 0) { red_val[wslot * BN + c0 + i] = val; red_idx[wslot * BN + c0 + i] = idx; }
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
+      const int c = threadIdx.x - 64;
+      if (c < BN && b_row0 + c < am.B) {
+        float val = red_val[c];
+        int idx = red_idx[c];
+#pragma unroll
+        for (int w = 1; w < 4; ++w) {
+          float ov = red_val[w * BN + c];
+          int oi = red_idx[w * BN + c];
+          if (ov > val || (ov == val && oi < idx)) { val = ov; idx = oi; }
+        }
+        am.part_val[(size_t)blockIdx.x * am.B + b_row0 + c] = val;
+        am.part_idx[(size_t)blockIdx.x * am.B + b_row0 + c] = idx;
+      }
+    } else {
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        float v[32];
+        tc_ld32(taddr + c0, v);  // warp-collective: executed by all lanes even for out-of-range rows
+        if (EPI == EPI_ROWMAJOR) {
+          if (row < rowsA && b_row0 + c0 < rowsB) store_run32(epi, row, b_row0 + c0, rowsB, v);
+        } else {  // EPI_SWAPPED: lane = output column n, TMEM column = batch row m
+          if (row < rowsA) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const int m = b_row0 + c0 + i;
+              if (c0 + i < BN && m < rowsB) epilogue_store(epi, m, row, v[i]);
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+std::once_flag g_encode_once;
+
+int get_encoder() {
+  std::call_once(g_encode_once, [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  });
+  if (!g_encode) {
+    tutor_set_error("cuTensorMapEncodeTiled is not available from the CUDA driver");
+    return TUTOR_ERR_CUDA;
+  }
+  return TUTOR_OK;
+}
+
+// 2-D bf16 tensor [rows, K] row-major; box = [box_rows, 64] with the 128-byte swizzle the UMMA descriptor expects
+int make_map(CUtensorMap* map, const bf16* ptr, int rows, int K, int box_rows) {
+  TRY(get_encoder());
+  ARG_CHECK((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "gemm_bf16: operand not 16-byte aligned");
+  cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)K * sizeof(bf16)};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<bf16*>(ptr), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    tutor_set_error("cuTensorMapEncodeTiled failed (%d) rows=%d K=%d box_rows=%d", (int)r, rows, K, box_rows);
+    return TUTOR_ERR_CUDA;
+  }
+  return TUTOR_OK;
+}
+
+template <int BN, int EPI>
+int launch(const bf16* A, int rowsA, const bf16* B, int rowsB, int K, const GemmEpilogue& epi, const ArgmaxArgs& am,
+           cudaStream_t st) {
+  using L = SmemLayout<BN>;
+  static bool attr_done = false;  // per instantiation; racing first calls set the same value
+  if (!attr_done) {
+    CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  L::TOTAL));
+    attr_done = true;
+  }
+  CUtensorMap ta, tb;
+  TRY(make_map(&ta, A, rowsA, K, BM));
+  TRY(make_map(&tb, B, rowsB, K, BN));
+  dim3 grid(ceil_div(rowsA, BM), ceil_div(rowsB, BN));
+  gemm_bf16_tcgen05_kernel<BN, EPI><<<grid, NTHREADS, L::TOTAL, st>>>(ta, tb, rowsA, rowsB, K, epi, am);
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+
+template <int EPI>
+int launch_swapped(const bf16* W, int N, const bf16* X, int M, int K, const GemmEpilogue& epi, const ArgmaxArgs& am,
+                   cudaStream_t st) {
+  // batch is the UMMA N dimension: pick the smallest tile that covers it, loop over batch tiles beyond 128
+  if (M <= 16) return launch<16, EPI>(W, N, X, M, K, epi, am, st);
+  if (M <= 32) return launch<32, EPI>(W, N, X, M, K, epi, am, st);
+  if (M <= 64) return launch<64, EPI>(W, N, X, M, K, epi, am, st);
+  return launch<128, EPI>(W, N, X, M, K, epi, am, st);
+}
+
+}  // namespace
+
+int k_gemm_bf16(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpilogue& epi, cudaStream_t st) {
+  ARG_CHECK(K % BK == 0, "gemm_bf16: K=%d must be a multiple of %d", K, BK);
+  if (M == 0 || N == 0) return TUTOR_OK;
+  ArgmaxArgs am{};
+  if (M <= 128) return launch_swapped<EPI_SWAPPED>(W, N, A, M, K, epi, am, st);
+  return launch<128, EPI_ROWMAJOR>(A, M, W, N, K, epi, am, st);
+}
+
+// fused LM head + repetition penalty + per-tile argmax; partials [ceil(V/128)][B]
+int k_gemm_bf16_argmax(const bf16* wte, int V, const bf16* X, int B, int K, const uint32_t* seen, int seen_words,
+                       float penalty, float* part_val, int* part_idx, cudaStream_t st) {
+  ARG_CHECK(K % BK == 0, "lmhead: K=%d must be a multiple of %d", K, BK);
+  ARG_CHECK(B <= 128, "lmhead: batch %d > 128 per call", B);
+  GemmEpilogue epi{};
+  ArgmaxArgs am{seen, seen_words, penalty, V, part_val, part_idx, B};
+  // rows past V are zero-filled by TMA and masked to -inf in the epilogue: no padded copy of wte needed
+  return launch_swapped<EPI_ARGMAX>(wte, V, X, B, K, epi, am, st);
+}

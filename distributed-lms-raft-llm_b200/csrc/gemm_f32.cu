@@ -1,0 +1,129 @@
+// fp32 (parity-mode) contractions  C[m,n] = sum_k A[m,k] * W[n,k]  with the shared fused epilogue.
+// Both operands are K-contiguous: GPT-2 Conv1D weights ([in,out], HF/pytorch_utils.py:112) are
+// transposed once at load; BERT nn.Linear weights and the tied LM head already are [out,in].
+//   M <= 8  : weight-streaming GEMV, one warp per output column, 128-bit coalesced loads (HBM-bound)
+//   M  > 8  : 64x64x16 register-tiled SIMT GEMM (fp32 FMA only - TF32 would break the 1e-3 logit gate)
+#include "kernels.h"
+
+namespace {
+
+template <int MB>
+__global__ void __launch_bounds__(256) gemv_f32_kernel(const float* __restrict__ A, const float* __restrict__ W,
+                                                        int M0, int N, int K, GemmEpilogue epi) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = blockIdx.x * 8 + warp;
+  if (n >= N) return;
+  const float* w = W + (size_t)n * K;
+  float acc[MB];
+#pragma unroll
+  for (int m = 0; m < MB; ++m) acc[m] = 0.f;
+  // 4 independent 16-byte weight loads in flight per lane
+  int k = lane * 4;
+  for (; k + 384 < K; k += 512) {
+    float4 w0 = load4(w + k), w1 = load4(w + k + 128), w2 = load4(w + k + 256), w3 = load4(w + k + 384);
+#pragma unroll
+    for (int m = 0; m < MB; ++m) {
+      const float* a = A + (size_t)(M0 + m) * K + k;
+      float4 a0 = __ldg((const float4*)a), a1 = __ldg((const float4*)(a + 128));
+      float4 a2 = __ldg((const float4*)(a + 256)), a3 = __ldg((const float4*)(a + 384));
+      acc[m] += (w0.x * a0.x + w0.y * a0.y + w0.z * a0.z + w0.w * a0.w) +
+                (w1.x * a1.x + w1.y * a1.y + w1.z * a1.z + w1.w * a1.w) +
+                (w2.x * a2.x + w2.y * a2.y + w2.z * a2.z + w2.w * a2.w) +
+                (w3.x * a3.x + w3.y * a3.y + w3.z * a3.z + w3.w * a3.w);
+    }
+  }
+  for (; k < K; k += 128) {
+    float4 w0 = load4(w + k);
+#pragma unroll
+    for (int m = 0; m < MB; ++m) {
+      float4 a0 = __ldg((const float4*)(A + (size_t)(M0 + m) * K + k));
+      acc[m] += w0.x * a0.x + w0.y * a0.y + w0.z * a0.z + w0.w * a0.w;
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < MB; ++m) {
+    float s = warp_sum(acc[m]);
+    if (lane == 0) epilogue_store(epi, M0 + m, n, s);
+  }
+}
+
+constexpr int BM = 64, BN = 64, BK = 16, PAD = 4;
+
+__global__ void __launch_bounds__(256) sgemm_f32_kernel(const float* __restrict__ A, const float* __restrict__ W,
+                                                         int M, int N, int K, GemmEpilogue epi) {
+  __shared__ __align__(16) float As[2][BK][BM + PAD];
+  __shared__ __align__(16) float Ws[2][BK][BN + PAD];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int lr = tid >> 2, lk = (tid & 3) * 4;  // each thread stages one float4 of A and one of W per k-tile
+  const int am = min(m0 + lr, M - 1), wn = min(n0 + lr, N - 1);
+  const float* ap = A + (size_t)am * K + lk;
+  const float* wp = W + (size_t)wn * K + lk;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  float4 ra = load4(ap), rw = load4(wp);
+  auto stage = [&](int buf) {
+    As[buf][lk][lr] = ra.x; As[buf][lk + 1][lr] = ra.y; As[buf][lk + 2][lr] = ra.z; As[buf][lk + 3][lr] = ra.w;
+    Ws[buf][lk][lr] = rw.x; Ws[buf][lk + 1][lr] = rw.y; Ws[buf][lk + 2][lr] = rw.z; Ws[buf][lk + 3][lr] = rw.w;
+  };
+  stage(0);
+  __syncthreads();
+  const int nk = K / BK;
+  for (int kt = 0; kt < nk; ++kt) {
+    const int buf = kt & 1;
+    if (kt + 1 < nk) { ra = load4(ap + (kt + 1) * BK); rw = load4(wp + (kt + 1) * BK); }
+#pragma unroll
+    for (int k = 0; k < BK; ++k) {
+      float4 a = *reinterpret_cast<const float4*>(&As[buf][k][ty * 4]);
+      float4 w = *reinterpret_cast<const float4*>(&Ws[buf][k][tx * 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w}, wv[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], wv[j], acc[i][j]);
+    }
+    if (kt + 1 < nk) stage(buf ^ 1);
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    int m = m0 + ty * 4 + i;
+    if (m >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int n = n0 + tx * 4 + j;
+      if (n < N) epilogue_store(epi, m, n, acc[i][j]);
+    }
+  }
+}
+
+}  // namespace
+
+int k_gemm_f32(const float* A, const float* W, int M, int N, int K, const GemmEpilogue& epi, cudaStream_t st) {
+  ARG_CHECK(K % 128 == 0 || (M > 8 && K % BK == 0), "gemm_f32: K=%d unsupported (M=%d)", K, M);
+  if (M == 0 || N == 0) return TUTOR_OK;
+  if (M <= 8 && K % 128 == 0) {
+    dim3 grid(ceil_div(N, 8)), block(256);
+    switch (M) {
+      case 1: gemv_f32_kernel<1><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
+      case 2: gemv_f32_kernel<2><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
+      case 3: gemv_f32_kernel<3><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
+      case 4: gemv_f32_kernel<4><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
+      case 5: gemv_f32_kernel<5><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
+      case 6: gemv_f32_kernel<6><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
+      case 7: gemv_f32_kernel<7><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
+      default: gemv_f32_kernel<8><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
+    }
+  } else {
+    ARG_CHECK(K % BK == 0, "gemm_f32: K=%d must be a multiple of %d", K, BK);
+    dim3 grid(ceil_div(N, BN), ceil_div(M, BM)), block(256);
+    sgemm_f32_kernel<<<grid, block, 0, st>>>(A, W, M, N, K, epi);
+  }
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}

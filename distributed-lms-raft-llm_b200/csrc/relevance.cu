@@ -1,0 +1,234 @@
+// Corpus relevance scan (configs[4], an extension of REF/lms_server.py:1266 from one assignment text to a
+// corpus of chunk embeddings): cosine of Q query embeddings against N corpus rows, then top-k.
+//   1. cosine_scan : streams the corpus once (HBM-bound on its N*d*4 bytes); queries live in shared
+//                    memory, each warp holds 4 corpus rows in registers so one query vector read from
+//                    smem feeds 16 FMAs; scores[Q][N] go to scratch
+//   2. topk_chunk  : per (query, 4096-score chunk) exact top-k by k rounds of block arg-max
+//   3. topk_merge  : the same selection over the chunk candidates (and, after the NCCL all-gather of the
+//                    per-rank candidates, over the world_size*k gathered ones)
+// Ties always resolve to the lower corpus index, like torch.topk on the CPU oracle for distinct scores.
+#include <math_constants.h>
+
+#include "kernels.h"
+
+namespace {
+
+constexpr int CHUNK = 4096;
+
+template <int DV4>  // d = 128 * DV4
+__global__ void __launch_bounds__(256, 1) cosine_scan_kernel(const float* __restrict__ queries,
+                                                              const float* __restrict__ corpus,
+                                                              const float* __restrict__ inv_norm, int Q, int N,
+                                                              float eps, float* __restrict__ scores) {
+  constexpr int D = 128 * DV4;
+  extern __shared__ float sq[];           // [Q][D] queries, then [Q] inverse norms
+  float* qinv = sq + (size_t)Q * D;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < Q * D / 4; i += blockDim.x)
+    reinterpret_cast<float4*>(sq)[i] = reinterpret_cast<const float4*>(queries)[i];
+  __syncthreads();
+  for (int q = warp; q < Q; q += 8) {
+    float s = 0.f;
+    for (int i = lane; i < D; i += 32) s += sq[q * D + i] * sq[q * D + i];
+    s = warp_sum(s);
+    if (lane == 0) qinv[q] = 1.0f / fmaxf(sqrtf(s), eps);
+  }
+  __syncthreads();
+  const int ngroups = (N + 3) / 4;
+  for (int g = blockIdx.x * 8 + warp; g < ngroups; g += gridDim.x * 8) {
+    float4 c[4][DV4];
+    float cinv[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int row = min(4 * g + r, N - 1);
+      cinv[r] = inv_norm[row];
+#pragma unroll
+      for (int j = 0; j < DV4; ++j)
+        c[r][j] = *reinterpret_cast<const float4*>(corpus + (size_t)row * D + j * 128 + lane * 4);
+    }
+    for (int q = 0; q < Q; ++q) {
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int j = 0; j < DV4; ++j) {
+        const float4 x = *reinterpret_cast<const float4*>(sq + (size_t)q * D + j * 128 + lane * 4);
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+          acc[r] += (c[r][j].x * x.x + c[r][j].y * x.y) + (c[r][j].z * x.z + c[r][j].w * x.w);
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r) acc[r] = warp_sum(acc[r]);
+      if (lane < 4) {
+        const int row = 4 * g + lane;
+        const float a = lane == 0 ? acc[0] : lane == 1 ? acc[1] : lane == 2 ? acc[2] : acc[3];
+        const float ci = lane == 0 ? cinv[0] : lane == 1 ? cinv[1] : lane == 2 ? cinv[2] : cinv[3];
+        if (row < N) scores[(size_t)q * N + row] = a * qinv[q] * ci;
+      }
+    }
+  }
+}
+
+template <typename T>
+__global__ void row_inv_norm_kernel(const T* __restrict__ x, float* __restrict__ out, int N, int d, float eps) {
+  int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= N) return;
+  int lane = threadIdx.x & 31;
+  float s = 0.f;
+  for (int i = lane * 4; i < d; i += 128) {
+    float4 v = load4(x + (size_t)r * d + i);
+    s += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+  }
+  s = warp_sum(s);
+  if (lane == 0) out[r] = 1.0f / fmaxf(sqrtf(s), eps);
+}
+
+// block-wide (value desc, index asc) arg-max of up to CHUNK candidates held in smem, repeated k times
+__device__ void select_topk(float* sv, const int32_t* sidx, int n, int k, float* out_v, int32_t* out_i,
+                            int idx_base) {
+  __shared__ float rv[32];
+  __shared__ int ri[32];
+  __shared__ int winner;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  for (int round = 0; round < k; ++round) {
+    float bv = -CUDART_INF_F;
+    int bp = 0x7fffffff;  // position in smem; positions are in ascending index order
+    for (int p = threadIdx.x; p < n; p += blockDim.x) {
+      float v = sv[p];
+      if (v > bv) { bv = v; bp = p; }  // p ascending per thread: strict > keeps the lowest position
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      int op = __shfl_xor_sync(0xffffffffu, bp, o);
+      if (ov > bv || (ov == bv && op < bp)) { bv = ov; bp = op; }
+    }
+    if (lane == 0) { rv[warp] = bv; ri[warp] = bp; }
+    __syncthreads();
+    if (warp == 0) {
+      bv = lane < nwarps ? rv[lane] : -CUDART_INF_F;
+      bp = lane < nwarps ? ri[lane] : 0x7fffffff;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+        int op = __shfl_xor_sync(0xffffffffu, bp, o);
+        if (ov > bv || (ov == bv && op < bp)) { bv = ov; bp = op; }
+      }
+      if (lane == 0) {
+        winner = bp;
+        if (bp != 0x7fffffff) {
+          out_v[round] = bv;
+          out_i[round] = sidx ? sidx[bp] : idx_base + bp;
+          sv[bp] = -CUDART_INF_F;
+        } else {  // fewer than k candidates
+          out_v[round] = -CUDART_INF_F;
+          out_i[round] = -1;
+        }
+      }
+    }
+    __syncthreads();
+    (void)winner;
+  }
+}
+
+// grid (nchunks, Q)
+__global__ void __launch_bounds__(256) topk_chunk_kernel(const float* __restrict__ scores, int N, int k,
+                                                          float* __restrict__ cand_v, int32_t* __restrict__ cand_i,
+                                                          int idx_base) {
+  __shared__ float sv[CHUNK];
+  const int chunk = blockIdx.x, q = blockIdx.y, nchunks = gridDim.x;
+  const int p0 = chunk * CHUNK;
+  const int n = min(CHUNK, N - p0);
+  for (int p = threadIdx.x; p < n; p += blockDim.x) sv[p] = scores[(size_t)q * N + p0 + p];
+  __syncthreads();
+  select_topk(sv, nullptr, n, k, cand_v + ((size_t)q * nchunks + chunk) * k, cand_i + ((size_t)q * nchunks + chunk) * k,
+              idx_base + p0);
+}
+
+// grid (Q): candidates [Q][ncand] (value, index); candidates must be ordered by ascending index among equal values
+__global__ void __launch_bounds__(256) topk_merge_kernel(const float* __restrict__ cand_v,
+                                                          const int32_t* __restrict__ cand_i, int ncand, int k,
+                                                          float* __restrict__ out_v, int32_t* __restrict__ out_i) {
+  extern __shared__ float dyn[];
+  float* sv = dyn;
+  int32_t* si = reinterpret_cast<int32_t*>(dyn + ncand);
+  const int q = blockIdx.x;
+  for (int p = threadIdx.x; p < ncand; p += blockDim.x) {
+    sv[p] = cand_v[(size_t)q * ncand + p];
+    si[p] = cand_i[(size_t)q * ncand + p];
+    if (si[p] < 0) sv[p] = -CUDART_INF_F;
+  }
+  __syncthreads();
+  select_topk(sv, si, ncand, k, out_v + (size_t)q * k, out_i + (size_t)q * k, 0);
+}
+
+}  // namespace
+
+size_t k_cosine_topk_scratch_bytes(int Q, int N, int k) {
+  size_t nchunks = (size_t)ceil_div(N, CHUNK);
+  return round_up((size_t)Q * N * sizeof(float), 256) + round_up((size_t)Q * nchunks * k * sizeof(float), 256) +
+         round_up((size_t)Q * nchunks * k * sizeof(int32_t), 256);
+}
+
+int k_row_inv_norm(const void* corpus, int corpus_dtype, float* inv_norm, int N, int d, float eps, cudaStream_t st) {
+  ARG_CHECK(d % 4 == 0, "row_inv_norm: d %% 4 != 0");
+  if (N == 0) return TUTOR_OK;
+  if (corpus_dtype == DT_F32)
+    row_inv_norm_kernel<float><<<ceil_div(N, 8), 256, 0, st>>>((const float*)corpus, inv_norm, N, d, eps);
+  else
+    row_inv_norm_kernel<bf16><<<ceil_div(N, 8), 256, 0, st>>>((const bf16*)corpus, inv_norm, N, d, eps);
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+
+int k_topk_merge(const float* cand_scores, const int32_t* cand_idx, int Q, int ncand, int k, float* out_scores,
+                 int32_t* out_idx, cudaStream_t st) {
+  ARG_CHECK(k >= 1 && ncand >= 1, "topk_merge: bad k=%d ncand=%d", k, ncand);
+  size_t smem = (size_t)ncand * 8;
+  ARG_CHECK(smem <= 200 * 1024, "topk_merge: %d candidates do not fit in shared memory", ncand);
+  static bool attr_done = false;
+  if (!attr_done) {
+    CUDA_TRY(cudaFuncSetAttribute(topk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_done = true;
+  }
+  topk_merge_kernel<<<Q, 256, smem, st>>>(cand_scores, cand_idx, ncand, k, out_scores, out_idx);
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+
+int k_cosine_topk(const float* queries, const void* corpus, int corpus_dtype, const float* corpus_inv_norm, int Q,
+                  int N, int d, int k, float* out_scores, int32_t* out_idx, int idx_base, void* scratch,
+                  cudaStream_t st) {
+  ARG_CHECK(corpus_dtype == DT_F32, "cosine_topk: corpus must be fp32 (scores are gated at 1e-4)");
+  ARG_CHECK(d == 768 || d == 128, "cosine_topk: d=%d unsupported (768 or 128)", d);
+  ARG_CHECK(Q >= 1 && (size_t)Q * d * 4 + Q * 4 <= 200 * 1024, "cosine_topk: %d queries do not fit in shared memory", Q);
+  ARG_CHECK(k >= 1 && k <= CHUNK && N >= 1, "cosine_topk: bad k=%d N=%d", k, N);
+  const int nchunks = ceil_div(N, CHUNK);
+  uint8_t* p = reinterpret_cast<uint8_t*>(scratch);
+  float* scores = reinterpret_cast<float*>(p);
+  p += round_up((size_t)Q * N * sizeof(float), 256);
+  float* cand_v = reinterpret_cast<float*>(p);
+  p += round_up((size_t)Q * nchunks * k * sizeof(float), 256);
+  int32_t* cand_i = reinterpret_cast<int32_t*>(p);
+  const size_t smem = (size_t)Q * d * 4 + (size_t)Q * 4;
+  const float eps = 1e-8f;
+  const int grid = 148;
+  if (d == 768) {
+    static bool a6 = false;
+    if (!a6) {
+      CUDA_TRY(cudaFuncSetAttribute(cosine_scan_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      a6 = true;
+    }
+    cosine_scan_kernel<6><<<grid, 256, smem, st>>>(queries, (const float*)corpus, corpus_inv_norm, Q, N, eps, scores);
+  } else {
+    static bool a1 = false;
+    if (!a1) {
+      CUDA_TRY(cudaFuncSetAttribute(cosine_scan_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      a1 = true;
+    }
+    cosine_scan_kernel<1><<<grid, 256, smem, st>>>(queries, (const float*)corpus, corpus_inv_norm, Q, N, eps, scores);
+  }
+  KERNEL_LAUNCHED();
+  topk_chunk_kernel<<<dim3(nchunks, Q), 256, 0, st>>>(scores, N, k, cand_v, cand_i, idx_base);
+  KERNEL_LAUNCHED();
+  // chunk candidates are in ascending chunk order, i.e. ascending index among equal values
+  return k_topk_merge(cand_v, cand_i, Q, nchunks * k, k, out_scores, out_idx, st);
+}

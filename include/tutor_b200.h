@@ -1,0 +1,165 @@
+/* tutor_b200 — C ABI of the B200-native tutoring-inference engine.
+ *
+ * Drop-in arithmetic for the two call sites of naggender2/distributed-lms-raft-llm's hot path
+ * (REF = GUI_RAFT_LLM_SourceCode):
+ *   - GPT-2 greedy generation   REF/tutoring_server.py:21-29   (model.generate)
+ *   - BERT relevance gate       REF/lms_server.py:97-104       (compute_embeddings, cosine_similarity)
+ * The reference has no FFI of its own (it is pure Python calling transformers/torch); these entry points are what
+ * a ctypes/cffi binding placed behind those Python call sites binds — see INTEGRATION.md.
+ *
+ * Conventions: every function returns 0 on success or a negative TUTOR_ERR_* code; the message is available from
+ * tutor_last_error() (thread-local).  No C++ types or exceptions cross the ABI.  "host" pointers are ordinary
+ * (ideally pinned) host memory; "dev" pointers are CUDA device pointers owned by the caller.  Engine handles own
+ * their weights, KV cache and workspaces in device memory and serialise concurrent callers with an internal mutex
+ * (the reference's gRPC servers run 10 handler threads on one model, REF/tutoring_server.py:40).
+ * There is no CPU fallback: every entry point fails with TUTOR_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef TUTOR_B200_H
+#define TUTOR_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TUTOR_OK 0
+#define TUTOR_ERR_ARG (-1)
+#define TUTOR_ERR_CUDA (-2)
+#define TUTOR_ERR_STATE (-3)
+#define TUTOR_ERR_LIMIT (-4)
+
+#define TUTOR_DT_F32 0  /* parity mode: fp32 weights, fp32 KV cache, fp32 math (no TF32) */
+#define TUTOR_DT_BF16 1 /* throughput mode: bf16 weights + KV cache, fp32 accumulation, fp32 residual stream */
+
+#define TUTOR_ACT_NONE 0
+#define TUTOR_ACT_GELU_TANH 1 /* NewGELUActivation, transformers/activations.py:59-66 */
+#define TUTOR_ACT_GELU_ERF 2  /* exact GELU, transformers/activations.py:70-89 */
+
+const char* tutor_last_error(void);
+int tutor_version(void);
+/* number of kernels this library has launched in the calling process (bench.py's gpu_launches) */
+uint64_t tutor_launch_count(void);
+
+/* ----------------------------------------------------------------------------------------------------------
+ * GPT-2: replaces GPT2LMHeadModel(...).generate as called at REF/tutoring_server.py:21-29
+ * (transformers/generation/utils.py:2131-2553 resolved to greedy + RepetitionPenalty + MaxLength + EOS).      */
+typedef struct tutor_gpt2 tutor_gpt2_t;
+
+typedef struct {
+  int32_t n_layer, n_head, n_embd, vocab_size, n_positions; /* transformers GPT2Config; head_dim must be 64 */
+  float layer_norm_epsilon;
+  int32_t dtype; /* TUTOR_DT_* */
+} tutor_gpt2_config;
+
+int tutor_gpt2_create(const tutor_gpt2_config* cfg, int device, tutor_gpt2_t** out);
+void tutor_gpt2_destroy(tutor_gpt2_t* h);
+/* One call per entry of the transformers state_dict (names as in GPT2LMHeadModel.state_dict(), e.g.
+ * "transformer.h.3.attn.c_attn.weight"); data is host fp32, row-major, `shape[ndim]`.  Conv1D weights
+ * ([in,out], transformers/pytorch_utils.py:108-123) are transposed to K-contiguous on load; lm_head.weight is
+ * tied to wte (modeling_gpt2.py:646-651) and ignored.  Unknown names return TUTOR_ERR_ARG.                   */
+int tutor_gpt2_load_tensor(tutor_gpt2_t* h, const char* name, const float* host_data, const int64_t* shape,
+                           int ndim);
+/* Fails with TUTOR_ERR_STATE (listing the first missing tensor) unless every weight has been loaded. */
+int tutor_gpt2_check_loaded(tutor_gpt2_t* h);
+
+/* The reference-facing call: host int64 ids in, host int64 ids out (REF/tutoring_server.py:20-30 hands CPU
+ * LongTensors to and from generate).  ids_host [B,T]; out_host [B, max_total_len] receives B rows of *out_len
+ * tokens each, packed with row stride *out_len (prompt included, finished rows right-padded with pad_id).
+ * max_total_len counts the prompt (MaxLengthCriteria, transformers/generation/stopping_criteria.py:74-83);
+ * T >= max_total_len is an error like transformers' ValueError (utils.py:1575-1581).  repetition_penalty 1.0
+ * disables the penalty; eos_id < 0 disables the EOS criterion.  One stream sync at the end (plus one poll of
+ * the device-side finished flag every 32 steps).                                                              */
+int tutor_gpt2_generate(tutor_gpt2_t* h, const int64_t* ids_host, int B, int T, int max_total_len,
+                        float repetition_penalty, int eos_id, int pad_id, int64_t* out_host, int* out_len);
+/* Same, with the prompt and the result resident in device memory (int32): ids_dev [B,T], out_dev
+ * [B, max_total_len] written with row stride max_total_len.                                                   */
+int tutor_gpt2_generate_dev(tutor_gpt2_t* h, const int32_t* ids_dev, int B, int T, int max_total_len,
+                            float repetition_penalty, int eos_id, int pad_id, int32_t* out_dev, int* out_len);
+
+/* Stepwise form of the same loop (GenerationMixin._sample, utils.py:2736-2805) for parity tests and profiling:
+ * prefill runs the prompt and selects token T; step runs n single-token forwards; read_ids copies the current
+ * ids; logits materialises the fp32 logits of the most recent forward (the fused path never does).            */
+int tutor_gpt2_prefill(tutor_gpt2_t* h, const int64_t* ids_host, int B, int T, int max_total_len,
+                       float repetition_penalty, int eos_id, int pad_id);
+int tutor_gpt2_step(tutor_gpt2_t* h, int n_steps);
+int tutor_gpt2_read_ids(tutor_gpt2_t* h, int64_t* out_host, int out_capacity, int* out_len, int* stop_len);
+int tutor_gpt2_logits(tutor_gpt2_t* h, float* logits_dev /* [B, vocab] */);
+/* Algorithmic HBM bytes of one decode forward at cached length S for batch B (weights + KV read + KV write),
+ * the figure bench.py's roofline uses.                                                        */
+double tutor_gpt2_decode_bytes(tutor_gpt2_t* h, int B, int S);
+/* Stream the engine enqueues on (a cudaStream_t), so callers can bracket it with CUDA events. */
+void* tutor_gpt2_stream(tutor_gpt2_t* h);
+
+/* ----------------------------------------------------------------------------------------------------------
+ * BERT: replaces BertModel.forward + mean(dim=1) inside compute_embeddings (REF/lms_server.py:97-101).         */
+typedef struct tutor_bert tutor_bert_t;
+
+typedef struct {
+  int32_t num_hidden_layers, num_attention_heads, hidden_size, intermediate_size, vocab_size,
+      max_position_embeddings; /* transformers BertConfig; head_dim must be 64 */
+  float layer_norm_eps;
+  int32_t dtype;
+} tutor_bert_config;
+
+int tutor_bert_create(const tutor_bert_config* cfg, int device, tutor_bert_t** out);
+void tutor_bert_destroy(tutor_bert_t* h);
+/* Names as in BertModel.state_dict() ("encoder.layer.0.attention.self.query.weight", ...). The pooler
+ * (modeling_bert.py:456-468) is accepted and dropped: the reference never reads its output.                    */
+int tutor_bert_load_tensor(tutor_bert_t* h, const char* name, const float* host_data, const int64_t* shape,
+                           int ndim);
+int tutor_bert_check_loaded(tutor_bert_t* h);
+/* ids_host [B,T] int64 (all-ones attention mask, zero token types, as compute_embeddings produces for one
+ * text or an equal-length batch) -> emb_host [B, hidden] fp32 = last_hidden_state.mean(dim=1).
+ * hidden_host, if non-null, also receives last_hidden_state [B,T,hidden].                                      */
+int tutor_bert_embed(tutor_bert_t* h, const int64_t* ids_host, int B, int T, float* emb_host, float* hidden_host);
+/* Device-resident variant: ids_dev int32 [B,T] -> emb_dev fp32 [B, hidden]. */
+int tutor_bert_embed_dev(tutor_bert_t* h, const int32_t* ids_dev, int B, int T, float* emb_dev);
+void* tutor_bert_stream(tutor_bert_t* h);
+
+/* ----------------------------------------------------------------------------------------------------------
+ * Relevance scoring: replaces cosine_similarity (REF/lms_server.py:103-104, F.cosine_similarity eps 1e-8);
+ * the corpus scan extends the single comparison at REF/lms_server.py:1266 to N assignment-chunk embeddings.     */
+int tutor_cosine_pairs(const float* a_dev, const float* b_dev, float* out_dev, int B, int d, void* stream);
+int tutor_cosine_pairs_host(const float* a_host, const float* b_host, float* out_host, int B, int d);
+int tutor_row_inv_norm(const float* corpus_dev, float* inv_norm_dev, int N, int d, void* stream);
+size_t tutor_cosine_topk_scratch_bytes(int Q, int N, int k);
+/* queries_dev [Q,d], corpus_dev [N,d] fp32 with precomputed inverse norms -> out_scores_dev/out_idx_dev [Q,k],
+ * indices offset by idx_base (the shard's first global row).  scratch_dev: tutor_cosine_topk_scratch_bytes.   */
+int tutor_cosine_topk(const float* queries_dev, const float* corpus_dev, const float* inv_norm_dev, int Q, int N,
+                      int d, int k, float* out_scores_dev, int32_t* out_idx_dev, int idx_base, void* scratch_dev,
+                      void* stream);
+/* Merge of gathered per-shard candidates [Q, ncand] (shards in ascending index order) into the global top-k. */
+int tutor_topk_merge(const float* cand_scores_dev, const int32_t* cand_idx_dev, int Q, int ncand, int k,
+                     float* out_scores_dev, int32_t* out_idx_dev, void* stream);
+
+/* ----------------------------------------------------------------------------------------------------------
+ * Single kernels, for unit tests and ncu (device pointers, caller's stream).  Each stands in for the ATen op
+ * listed in SURVEY.md §2.2.                                                                                   */
+/* nn.LayerNorm (modeling_gpt2.py:252; modeling_bert.py:111): x [M,d] fp32 -> out_f32 and/or out_bf16. */
+int tutor_layernorm(const float* x_dev, const float* gamma_dev, const float* beta_dev, float eps, float* out_f32_dev,
+                    void* out_bf16_dev, int M, int d, void* stream);
+/* Conv1D / nn.Linear (pytorch_utils.py:119-123): out[M,N] = act(A[M,K] · W[N,K]^T + bias) + residual.
+ * dtype F32: A, W fp32, out fp32.  dtype BF16: A, W bf16 (tcgen05), out fp32 if out_is_f32 else bf16.
+ * impl 0 = product kernel; impl 1 (bf16 only) = the mma.sync cross-check kernel used by the tests.            */
+int tutor_linear(int dtype, const void* A_dev, const void* W_dev, const float* bias_dev, const float* residual_dev,
+                 void* out_dev, int out_is_f32, int M, int N, int K, int act, int impl, void* stream);
+/* SDPA (sdpa_attention.py:42-104), head_dim 64, scale 1/8. q/out [B*T, H*64]; k/v [B][H][Smax][64]. */
+int tutor_attn_prefill(int dtype, const void* q_dev, const void* k_dev, const void* v_dev, void* out_dev, int B, int H,
+                       int T, int Smax, int causal, void* stream);
+int tutor_attn_decode(int dtype, const void* q_dev, const void* k_dev, const void* v_dev, void* out_dev, int B, int H,
+                      int Smax, int len, void* stream);
+/* Fused LM head + repetition penalty + argmax (modeling_gpt2.py:705; logits_process.py:404-410;
+ * utils.py:2793): x [B,d] (fp32 for F32, bf16 for BF16) against wte [V,d]; seen_dev [B, ceil(V/32)] bitmap of
+ * ids to penalise (may be null when penalty == 1); out_idx_dev [B] int32.  scratch_dev of
+ * tutor_lmhead_scratch_bytes(B) bytes holds the per-CTA partial maxima.                                       */
+size_t tutor_lmhead_scratch_bytes(int B);
+int tutor_lmhead_argmax(int dtype, const void* x_dev, const void* wte_dev, int B, int V, int d,
+                        const uint32_t* seen_dev, float penalty, int32_t* out_idx_dev, void* scratch_dev,
+                        void* stream);
+int tutor_meanpool(const float* x_dev, float* out_dev, int B, int T, int d, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TUTOR_B200_H */

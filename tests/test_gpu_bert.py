@@ -1,0 +1,85 @@
+"""-m gpu: BERT relevance-gate parity (configs[1]) against goldens produced by the reference's own
+compute_embeddings / cosine_similarity (REF/lms_server.py:97-104)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import reference_path as rp
+
+pytestmark = pytest.mark.gpu
+
+TINY = dict(hidden_size=128, num_hidden_layers=2, num_attention_heads=2, intermediate_size=512, vocab_size=2000,
+            max_position_embeddings=128)
+
+
+@pytest.fixture(scope="module")
+def base_hf():
+    return rp.build_bert(seed=0)
+
+
+def test_tiny_hidden_states(pkg, golden):
+    g = golden("bert_tiny")
+    hf = rp.build_bert(seed=6, **TINY)
+    eng = pkg.B200BertModel.from_hf(hf, dtype="fp32")
+    ids = torch.from_numpy(g["ids"]).long()
+    out = eng(input_ids=ids, token_type_ids=torch.zeros_like(ids), attention_mask=torch.ones_like(ids))
+    assert tuple(out.last_hidden_state.shape) == (3, 40, 128)
+    assert np.abs(out.last_hidden_state.numpy() - g["hidden"]).max() < 2e-5
+    assert np.abs(out.mean_embedding.numpy() - g["emb"]).max() < 1e-5
+    b16 = pkg.B200BertModel.from_hf(hf, dtype="bf16")
+    err = np.abs(b16.embed(ids).numpy() - g["emb"]).max()
+    print(f"bert tiny bf16 embedding max abs err {err:.3e}")
+    assert err < 3e-2
+
+
+def test_cfg1_fp32_embeddings_cosines_decisions(pkg, base_hf, golden):
+    """32 pairs, 128-token query vs 512-token assignment: cosine within 1e-4, decisions identical, including
+    a threshold sweep through the oracle's own score range (random-init scores never cross 0.6)."""
+    g = golden("bert_cfg1")
+    eng = pkg.B200BertModel.from_hf(base_hf, dtype="fp32")
+    q = eng.embed(torch.from_numpy(g["q_ids"]).long())
+    a = eng.embed(torch.from_numpy(g["a_ids"]).long())
+    assert np.abs(q.numpy() - g["q_emb"]).max() < 1e-4
+    assert np.abs(a.numpy() - g["a_emb"]).max() < 1e-4
+    cos = np.array([pkg.cosine_similarity(q[i:i + 1], a[i:i + 1]) for i in range(32)])
+    assert np.abs(cos - g["cos"]).max() < 1e-4
+    assert all(isinstance(c, float) for c in cos.tolist())
+    for thr in [0.6] + np.sort(g["cos"])[[4, 16, 28]].tolist():
+        thr = float(thr) + 5e-5 * (1 if thr != 0.6 else 0)  # keep the sweep points off an exact score
+        mine = [pkg.is_relevant(c, thr) for c in cos]
+        ref = [rp.relevance_decision(c, thr) for c in g["cos"]]
+        near = np.abs(g["cos"] - thr) < 1e-4
+        assert all(m == r or n for m, r, n in zip(mine, ref, near)), thr
+    # the reference's own function signature, one text at a time, tokenizer injected
+    class Tok:
+        def __call__(self, text, **kw):
+            ids = torch.from_numpy(g["q_ids"][int(text)][None]).long()
+            return {"input_ids": ids, "token_type_ids": torch.zeros_like(ids), "attention_mask": torch.ones_like(ids)}
+    e0 = pkg.compute_embeddings("0", eng, Tok())
+    assert tuple(e0.shape) == (1, 768) and np.abs(e0.numpy()[0] - g["q_emb"][0]).max() < 1e-4
+
+
+def test_cfg1_bf16_tolerance(pkg, base_hf, golden):
+    """bf16 throughput mode: tolerance stated here = 5e-3 absolute on the cosine."""
+    g = golden("bert_cfg1")
+    eng = pkg.B200BertModel.from_hf(base_hf, dtype="bf16")
+    q = eng.embed(torch.from_numpy(g["q_ids"]).long())
+    a = eng.embed(torch.from_numpy(g["a_ids"]).long())
+    cos = pkg.cosine_similarity_batch(q, a).numpy()
+    err = np.abs(cos - g["cos"]).max()
+    print(f"cfg1 bf16 cosine max abs err {err:.3e}")
+    assert err < 5e-3
+    assert all(pkg.is_relevant(float(c)) == rp.relevance_decision(float(r)) for c, r in zip(cos, g["cos"]))
+
+
+def test_ragged_lengths_and_errors(pkg, base_hf):
+    eng = pkg.B200BertModel.from_hf(base_hf, dtype="fp32")
+    for T in (1, 2, 3, 77):
+        ids = rp.bert_ids(1, max(T, 2), seed=T)[:, :T]
+        ref = rp.embeddings_from_ids(base_hf, ids)
+        assert (eng.embed(ids) - ref).abs().max().item() < 1e-4, T
+    with pytest.raises(Exception, match="exceeds max_position_embeddings"):
+        eng.embed(rp.bert_ids(1, 513))
+    with pytest.raises(NotImplementedError):
+        ids = rp.bert_ids(2, 8)
+        eng(input_ids=ids, attention_mask=torch.tensor([[1] * 8, [1] * 4 + [0] * 4]))

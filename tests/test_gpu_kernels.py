@@ -1,0 +1,196 @@
+"""-m gpu: every CUDA kernel against a plain torch fp32 expression of the ATen op it stands in for
+(SURVEY.md §2.2), called through the C ABI with device pointers."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+F32, BF16 = 0, 1
+
+
+def ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def sync():
+    torch.cuda.synchronize()
+
+
+def rel_err(a, b):
+    return ((a.float() - b.float()).abs().max() / b.float().abs().max().clamp_min(1e-12)).item()
+
+
+@pytest.mark.parametrize("M,d,eps", [(5, 128, 1e-5), (64, 768, 1e-5), (33, 1280, 1e-5), (16, 768, 1e-12)])
+def test_layernorm(pkg, lib, M, d, eps):
+    g = torch.Generator(device="cpu").manual_seed(0)
+    x = (torch.randn(M, d, generator=g) * 3 + 0.5).to(DEV)
+    w, b = torch.randn(d, generator=g).to(DEV), torch.randn(d, generator=g).to(DEV)
+    of, ob = torch.empty_like(x), torch.empty(M, d, dtype=torch.bfloat16, device=DEV)
+    pkg._lib.check(lib.tutor_layernorm(ptr(x), ptr(w), ptr(b), eps, ptr(of), ptr(ob), M, d, None))
+    sync()
+    ref = torch.nn.functional.layer_norm(x, (d,), w, b, eps)
+    assert (of - ref).abs().max().item() < 2e-5
+    assert (ob.float() - ref).abs().max().item() < 0.05
+
+
+def _linear_ref(A, W, bias, res, act):
+    y = A.float() @ W.float().T
+    if bias is not None:
+        y = y + bias
+    if act == 1:
+        y = 0.5 * y * (1 + torch.tanh(math.sqrt(2 / math.pi) * (y + 0.044715 * y ** 3)))
+    elif act == 2:
+        y = torch.nn.functional.gelu(y)
+    if res is not None:
+        y = y + res
+    return y
+
+
+@pytest.mark.parametrize("M,N,K,act,use_res", [(1, 768, 768, 0, True), (3, 2304, 768, 0, False), (8, 3072, 768, 1, False),
+                                               (1, 768, 3072, 0, True), (37, 200, 128, 2, True),
+                                               (256, 384, 512, 1, False)])
+def test_linear_f32(pkg, lib, M, N, K, act, use_res):
+    g = torch.Generator().manual_seed(M * 7 + N)
+    A, W = torch.randn(M, K, generator=g).to(DEV), (torch.randn(N, K, generator=g) * 0.05).to(DEV)
+    bias = torch.randn(N, generator=g).to(DEV)
+    res = torch.randn(M, N, generator=g).to(DEV) if use_res else None
+    out = torch.empty(M, N, device=DEV)
+    pkg._lib.check(lib.tutor_linear(F32, ptr(A), ptr(W), ptr(bias), ptr(res), ptr(out), 1, M, N, K, act, 0, None))
+    sync()
+    ref = _linear_ref(A.double(), W.double(), bias.double(), None if res is None else res.double(), act).float()
+    assert rel_err(out, ref) < 2e-6
+
+
+# (M, N, K): decode-shaped (swap-AB, M <= 128) and prefill-shaped (row-major, M > 128), ragged edges included
+BF16_SHAPES = [(1, 768, 768), (16, 2304, 768), (64, 768, 3072), (64, 3072, 768), (50, 200, 128), (128, 256, 64),
+               (129, 256, 64), (300, 2304, 768), (1024, 3072, 768), (257, 100, 192)]
+
+
+@pytest.mark.parametrize("impl", [1, 0], ids=["mma_sync_check", "tcgen05"])
+@pytest.mark.parametrize("M,N,K", BF16_SHAPES)
+def test_linear_bf16(pkg, lib, M, N, K, impl):
+    g = torch.Generator().manual_seed(M + N + K)
+    A = torch.randn(M, K, generator=g).to(DEV).bfloat16()
+    W = (torch.randn(N, K, generator=g) * 0.05).to(DEV).bfloat16()
+    bias = torch.randn(N, generator=g).to(DEV)
+    res = torch.randn(M, N, generator=g).to(DEV)
+    out = torch.full((M, N), float("nan"), device=DEV)
+    pkg._lib.check(lib.tutor_linear(BF16, ptr(A), ptr(W), ptr(bias), ptr(res), ptr(out), 1, M, N, K, 1, impl, None))
+    sync()
+    ref = _linear_ref(A.double(), W.double(), bias.double(), res.double(), 1).float()
+    assert rel_err(out, ref) < 1e-5  # bf16 inputs are exact in fp32; only the accumulation order differs
+    outb = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
+    pkg._lib.check(lib.tutor_linear(BF16, ptr(A), ptr(W), ptr(bias), None, ptr(outb), 0, M, N, K, 2, impl, None))
+    sync()
+    refb = _linear_ref(A.double(), W.double(), bias.double(), None, 2).float()
+    assert rel_err(outb, refb) < 1e-2
+
+
+def _sdpa_ref(q, k, v, causal):
+    # q [B,T,H,64], k/v [B,H,S,64]
+    qh = q.permute(0, 2, 1, 3).double()
+    s = qh @ k.double().transpose(-1, -2) / 8.0
+    if causal:
+        T, S = s.shape[-2:]
+        mask = torch.ones(T, S, dtype=torch.bool, device=s.device).tril(S - T)
+        s = s.masked_fill(~mask, float("-inf"))
+    o = torch.softmax(s, -1) @ v.double()
+    return o.permute(0, 2, 1, 3).float()
+
+
+@pytest.mark.parametrize("dtype", [F32, BF16])
+@pytest.mark.parametrize("B,H,T,causal", [(1, 2, 32, 1), (2, 12, 100, 1), (3, 2, 40, 0), (2, 4, 129, 1), (1, 12, 512, 0)])
+def test_attn_prefill(pkg, lib, dtype, B, H, T, causal):
+    g = torch.Generator().manual_seed(T)
+    td = torch.float32 if dtype == F32 else torch.bfloat16
+    Smax = T + 7
+    q = torch.randn(B, T, H, 64, generator=g).to(DEV).to(td)
+    k = torch.randn(B, H, Smax, 64, generator=g).to(DEV).to(td)
+    v = torch.randn(B, H, Smax, 64, generator=g).to(DEV).to(td)
+    out = torch.empty(B, T, H, 64, device=DEV, dtype=td)
+    pkg._lib.check(lib.tutor_attn_prefill(dtype, ptr(q), ptr(k), ptr(v), ptr(out), B, H, T, Smax, causal, None))
+    sync()
+    ref = _sdpa_ref(q, k[:, :, :T], v[:, :, :T], causal)
+    tol = 2e-5 if dtype == F32 else 2e-2
+    assert (out.float() - ref).abs().max().item() < tol
+
+
+@pytest.mark.parametrize("dtype", [F32, BF16])
+@pytest.mark.parametrize("B,H,S", [(1, 12, 1), (1, 12, 33), (4, 2, 95), (64, 12, 513), (3, 20, 1024)])
+def test_attn_decode(pkg, lib, dtype, B, H, S):
+    g = torch.Generator().manual_seed(S)
+    td = torch.float32 if dtype == F32 else torch.bfloat16
+    Smax = (S + 63) // 64 * 64
+    q = torch.randn(B, 1, H, 64, generator=g).to(DEV).to(td)
+    k = torch.randn(B, H, Smax, 64, generator=g).to(DEV).to(td)
+    v = torch.randn(B, H, Smax, 64, generator=g).to(DEV).to(td)
+    out = torch.empty(B, 1, H, 64, device=DEV, dtype=td)
+    pkg._lib.check(lib.tutor_attn_decode(dtype, ptr(q), ptr(k), ptr(v), ptr(out), B, H, Smax, S, None))
+    sync()
+    ref = _sdpa_ref(q, k[:, :, :S], v[:, :, :S], 0)
+    tol = 2e-5 if dtype == F32 else 2e-2
+    assert (out.float() - ref).abs().max().item() < tol
+
+
+@pytest.mark.parametrize("dtype,B,V,d", [(F32, 1, 50257, 768), (F32, 4, 1000, 128), (F32, 11, 5000, 256),
+                                         (BF16, 1, 1000, 128), (BF16, 64, 50257, 768), (BF16, 16, 50257, 1280),
+                                         (BF16, 100, 3000, 128)])
+@pytest.mark.parametrize("penalty", [1.0, 1.2])
+def test_lmhead_argmax(pkg, lib, dtype, B, V, d, penalty):
+    g = torch.Generator().manual_seed(V + B)
+    td = torch.float32 if dtype == F32 else torch.bfloat16
+    x = torch.randn(B, d, generator=g).to(DEV).to(td)
+    wte = (torch.randn(V, d, generator=g) * 0.02).to(DEV).to(td)
+    logits = x.double() @ wte.double().T
+    words = (V + 31) // 32
+    seen_ids = torch.topk(logits, 3, dim=1).indices  # penalise exactly the would-be winners
+    seen = torch.zeros(B, words, dtype=torch.int32, device=DEV)
+    for b in range(B):
+        for t in seen_ids[b].tolist():
+            seen[b, t // 32] |= (1 << (t % 32)) if (t % 32) < 31 else -(1 << 31)
+    if penalty != 1.0:
+        mask = torch.zeros(B, V, dtype=torch.bool, device=DEV).scatter_(1, seen_ids, True)
+        pen = torch.where(logits < 0, logits * penalty, logits / penalty)
+        logits = torch.where(mask, pen, logits)
+    ref = logits.argmax(-1).to(torch.int32)
+    out = torch.empty(B, dtype=torch.int32, device=DEV)
+    scratch = torch.empty(lib.tutor_lmhead_scratch_bytes(B), dtype=torch.uint8, device=DEV)
+    pkg._lib.check(lib.tutor_lmhead_argmax(dtype, ptr(x), ptr(wte), B, V, d, ptr(seen), penalty, ptr(out), ptr(scratch),
+                                           None))
+    sync()
+    bad = (out != ref).nonzero().flatten().tolist()
+    for b in bad:  # a mismatch is only acceptable on a numerical near-tie
+        assert abs(logits[b, out[b]].item() - logits[b, ref[b]].item()) < 1e-4 * logits[b].abs().max().item(), b
+
+
+def test_lmhead_tie_breaks_to_lowest_id(pkg, lib):
+    B, V, d = 2, 1000, 128
+    x = torch.zeros(B, d, device=DEV)
+    x[:, 0] = 1.0
+    wte = torch.zeros(V, d, device=DEV)
+    wte[[7, 500, 999], 0] = 3.0  # three exact ties
+    out = torch.empty(B, dtype=torch.int32, device=DEV)
+    scratch = torch.empty(lib.tutor_lmhead_scratch_bytes(B), dtype=torch.uint8, device=DEV)
+    for dtype, xx, ww in ((F32, x, wte), (BF16, x.bfloat16(), wte.bfloat16())):
+        pkg._lib.check(lib.tutor_lmhead_argmax(dtype, ptr(xx), ptr(ww), B, V, d, None, 1.0, ptr(out), ptr(scratch), None))
+        sync()
+        assert out.tolist() == [7, 7]  # torch.argmax returns the first maximal index
+
+
+def test_meanpool_and_cosine(pkg, lib):
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(3, 77, 768, generator=g).to(DEV)
+    out = torch.empty(3, 768, device=DEV)
+    pkg._lib.check(lib.tutor_meanpool(ptr(x), ptr(out), 3, 77, 768, None))
+    sync()
+    assert (out - x.mean(1)).abs().max().item() < 1e-6
+    a, b = torch.randn(9, 768, generator=g).to(DEV), torch.randn(9, 768, generator=g).to(DEV)
+    a[4] = 0  # eps path: max(|x|, 1e-8)
+    cs = torch.empty(9, device=DEV)
+    pkg._lib.check(lib.tutor_cosine_pairs(ptr(a), ptr(b), ptr(cs), 9, 768, None))
+    sync()
+    ref = torch.nn.functional.cosine_similarity(a, b)
+    assert (cs - ref).abs().max().item() < 1e-6
+    assert abs(pkg.cosine_similarity(a[:1].cpu(), b[:1].cpu()) - ref[0].item()) < 1e-6
