@@ -71,6 +71,8 @@ SIGNATURES = {
     "tutor_lmhead_argmax": (c_int, [c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_float, c_void_p,
                                     c_void_p, c_void_p]),
     "tutor_meanpool": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "tutor_lmhead_argmax_static": (c_int, [c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_float, c_void_p,
+                                           c_void_p]),
 }
 
 

@@ -159,6 +159,19 @@ int tutor_lmhead_argmax(int dtype, const void* x_dev, const void* wte_dev, int B
                         void* stream);
 int tutor_meanpool(const float* x_dev, float* out_dev, int B, int T, int d, void* stream);
 
+/* No counterpart in the reference: tutor_lmhead_argmax for callers that may not allocate device memory (a host
+ * whose own pool owns the whole GPU heap, a latency-critical loop that must stay off the driver's allocation lock,
+ * a plug-in with a fixed memory budget).  Same arguments and result as tutor_lmhead_argmax minus scratch_dev: the
+ * partial maxima go to a 1 MiB __device__ array built into the library (resident on every GPU that loads it until
+ * exit), which limits B to TUTOR_STATIC_MAX_BATCH; a larger B returns TUTOR_ERR_LIMIT.  It calls no cudaMalloc,
+ * cudaFree or allocating library routine.  The first call on each device looks the array's address up
+ * (cudaGetSymbolAddress) - make that call outside any stream capture.  All calls on a device share the array:
+ * calls that can overlap on the GPU race; keep them on one stream.  Nothing in the array needs clearing between
+ * calls (every slot that is read has been rewritten by the same call).                                          */
+#define TUTOR_STATIC_MAX_BATCH 128
+int tutor_lmhead_argmax_static(int dtype, const void* x_dev, const void* wte_dev, int B, int V, int d,
+                               const uint32_t* seen_dev, float penalty, int32_t* out_idx_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
