@@ -32,15 +32,24 @@ template <> struct Vec16<bf16> {
 // vector each, so one warp-wide load instruction fetches KPW whole keys (fully coalesced 512 B).
 // Every lane group runs its own online softmax over its share of the keys (4-way unrolled for
 // memory-level parallelism); the 4*KPW partial states are merged once at the end through smem.
-template <typename QT, typename KT, typename OT, bool FAST>
-__global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__ q, const KT* __restrict__ kc,
-                                                          const KT* __restrict__ vc, OT* __restrict__ out, int H,
-                                                          int Smax, const int* __restrict__ len_dev, int len_host) {
+//
+// FUSED (split-K decode path): the c_attn GEMM left raw partial sums [ks][B][3*H*64] in L2; this kernel finishes
+// them for its own (b,h) - bias + fixed-order sum - appends the new K/V row to the cache (DynamicLayer.update,
+// HF/cache_utils.py:119-120, without the torch.cat) and attends over positions [0,len) with the fresh row taken
+// from shared memory, so the q/k/v of the current token never make a round trip through HBM.
+template <typename QT, typename KT, typename OT, bool FAST, bool FUSED>
+__global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__ q, KT* kc, KT* vc,
+                                                          OT* __restrict__ out, int H, int Smax,
+                                                          const int* __restrict__ len_dev, int len_host,
+                                                          const float* __restrict__ qkv_partial, int ks,
+                                                          const float* __restrict__ qkv_bias, int B) {
   constexpr int EPL = Vec16<KT>::N;  // elements per lane
   constexpr int LPR = 64 / EPL;      // lanes per key row
   constexpr int KPW = 32 / LPR;      // keys per warp-wide load
   constexpr int NG = 4 * KPW;        // lane groups per block
   constexpr int UNR = 4;
+  pdl_launch_dependents();
+  pdl_wait();
   const int h = blockIdx.x, b = blockIdx.y;
   const int len = len_dev ? *len_dev : len_host;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -50,8 +59,28 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
   const KT* kb = kc + base + e0;
   const KT* vb = vc + base + e0;
 
+  __shared__ float s_new[3][64];  // FUSED: q, and the K/V row of the current token (as stored, i.e. rounded to KT)
   float qv[EPL];
-  {
+  if (FUSED) {
+    const int d = H * 64;
+    for (int e = threadIdx.x; e < 192; e += 128) {
+      const int which = e >> 6, i = e & 63;
+      const int n = which * d + h * 64 + i;
+      float acc = qkv_bias[n];
+#pragma unroll 8
+      for (int z = 0; z < ks; ++z) acc += qkv_partial[((size_t)z * B + b) * (3 * d) + n];
+      if (which == 0) {
+        s_new[0][i] = acc;
+      } else {
+        const KT st = from_f32<KT>(acc);
+        (which == 1 ? kc : vc)[base + (size_t)(len - 1) * 64 + i] = st;
+        s_new[which][i] = to_f32(st);
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) qv[i] = s_new[0][e0 + i] * 0.125f;
+  } else {
     const QT* qp = q + ((size_t)b * H + h) * 64 + e0;
 #pragma unroll
     for (int i = 0; i < EPL; ++i) qv[i] = to_f32(qp[i]) * 0.125f;  // scale = head_dim^-0.5
@@ -60,21 +89,24 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
 #pragma unroll
   for (int i = 0; i < EPL; ++i) o[i] = 0.f;
 
+  // FUSED: the row this CTA just appended (position len-1) is taken from shared memory after the loop
+  const int nkeys = FUSED ? len - 1 : len;
   // trip count is uniform per warp (the shuffles below need every lane); groups past the end are masked
-  for (int jw = warp * KPW; jw < len; jw += NG * UNR) {
+  for (int jw = warp * KPW; jw < nkeys; jw += NG * UNR) {
     const int j0 = jw + lane / LPR;
     float kf[UNR][EPL], s[UNR];
 #pragma unroll
     for (int u = 0; u < UNR; ++u) {
-      int j = min(j0 + u * NG, len - 1);  // clamped: masked below, never out of bounds
+      int j = min(j0 + u * NG, nkeys - 1);  // clamped: masked below, never out of bounds
       Vec16<KT>::load(kb + (size_t)j * 64, kf[u]);
     }
     float vf[UNR][EPL];
 #pragma unroll
     for (int u = 0; u < UNR; ++u) {
-      int j = min(j0 + u * NG, len - 1);
+      int j = min(j0 + u * NG, nkeys - 1);
       Vec16<KT>::load(vb + (size_t)j * 64, vf[u]);
     }
+
 #pragma unroll
     for (int u = 0; u < UNR; ++u) {
       float d = 0.f;
@@ -82,7 +114,7 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
       for (int i = 0; i < EPL; ++i) d = fmaf(qv[i], kf[u][i], d);
 #pragma unroll
       for (int off = LPR / 2; off > 0; off >>= 1) d += __shfl_xor_sync(0xffffffffu, d, off);
-      s[u] = (j0 + u * NG < len) ? d : -CUDART_INF_F;
+      s[u] = (j0 + u * NG < nkeys) ? d : -CUDART_INF_F;
     }
     float mn = m;
 #pragma unroll
@@ -100,6 +132,22 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
       for (int i = 0; i < EPL; ++i) o[i] = fmaf(p, vf[u][i], o[i]);
     }
     m = mn;
+  }
+
+  if (FUSED) {  // the current token's own key/value, folded into group 0's running softmax
+    float d = 0.f;
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) d = fmaf(qv[i], s_new[1][e0 + i], d);
+#pragma unroll
+    for (int off = LPR / 2; off > 0; off >>= 1) d += __shfl_xor_sync(0xffffffffu, d, off);
+    if (g == 0) {
+      const float mn = fmaxf(m, d);
+      const float corr = exp_sel<FAST>(m - mn), p = exp_sel<FAST>(d - mn);
+      l = l * corr + p;
+#pragma unroll
+      for (int i = 0; i < EPL; ++i) o[i] = fmaf(p, s_new[2][e0 + i], o[i] * corr);
+      m = mn;
+    }
   }
 
   __shared__ float sm_m[NG], sm_l[NG], sm_o[NG][64];
@@ -216,15 +264,29 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
   ARG_CHECK(len_dev || (len_host >= 1 && len_host <= Smax), "attn_decode: len %d outside [1,%d]", len_host, Smax);
   dim3 grid(H, B), block(128);
   if (q_dtype == DT_F32 && kv_dtype == DT_F32 && out_dtype == DT_F32)
-    attn_decode_kernel<float, float, float, false><<<grid, block, 0, st>>>(
-        (const float*)q, (const float*)k, (const float*)v, (float*)out, H, Smax, len_dev, len_host);
+    attn_decode_kernel<float, float, float, false, false><<<grid, block, 0, st>>>(
+        (const float*)q, (float*)k, (float*)v, (float*)out, H, Smax, len_dev, len_host, nullptr, 0, nullptr, B);
   else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16)
-    attn_decode_kernel<bf16, bf16, bf16, true><<<grid, block, 0, st>>>(
-        (const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)out, H, Smax, len_dev, len_host);
+    attn_decode_kernel<bf16, bf16, bf16, true, false><<<grid, block, 0, st>>>(
+        (const bf16*)q, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, nullptr, 0, nullptr, B);
   else {
     tutor_set_error("attn_decode: unsupported dtype combination q=%d kv=%d out=%d", q_dtype, kv_dtype, out_dtype);
     return TUTOR_ERR_ARG;
   }
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+
+int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias, void* k, void* v, int kv_dtype,
+                        void* out, int out_dtype, int B, int H, int Smax, const int* len_dev, int len_host,
+                        cudaStream_t st) {
+  if (B == 0) return TUTOR_OK;
+  ARG_CHECK(kv_dtype == DT_BF16 && out_dtype == DT_BF16, "attn_decode_fused: bf16 cache and output only");
+  ARG_CHECK(qkv_partial && qkv_bias && ks >= 1, "attn_decode_fused: bad partials");
+  ARG_CHECK(len_dev || (len_host >= 1 && len_host <= Smax), "attn_decode_fused: len %d outside [1,%d]", len_host, Smax);
+  CUDA_TRY(tutor_launch(attn_decode_kernel<bf16, bf16, bf16, true, true>, dim3(H, B), dim3(128), 0, st,
+                        (const bf16*)nullptr, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks,
+                        qkv_bias, B));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }

@@ -6,6 +6,8 @@
 
 #include "engine_common.h"
 
+thread_local bool tutor_pdl_enabled = false;
+
 namespace {
 thread_local char g_err[1024] = "";
 std::atomic<uint64_t> g_launches{0};

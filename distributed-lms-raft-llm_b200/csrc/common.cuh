@@ -44,6 +44,28 @@ void tutor_count_launches(uint64_t n);
 
 typedef __nv_bfloat16 bf16;
 
+// Programmatic dependent launch (PDL): while set (per host thread, by the decode engine), kernels launched through
+// tutor_launch() may start before their stream predecessor has finished; each of them calls pdl_wait() before it
+// touches anything another kernel produces or still reads, so only launch latency and prologues overlap.
+extern thread_local bool tutor_pdl_enabled;
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+inline cudaError_t tutor_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr;
+  attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr.val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = tutor_pdl_enabled ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+// no-ops unless the kernel was launched with the PDL attribute
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
+
 enum { ACT_NONE = 0, ACT_GELU_TANH = 1, ACT_GELU_ERF = 2 };
 enum { DT_F32 = 0, DT_BF16 = 1 };
 

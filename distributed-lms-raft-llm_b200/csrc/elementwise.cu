@@ -12,6 +12,8 @@ template <typename WT>
 __global__ void gpt2_embed_kernel(const int32_t* __restrict__ ids, int ids_ld, const int* __restrict__ len_dev,
                                   int T, const WT* __restrict__ wte, const float* __restrict__ wpe, int d,
                                   float* __restrict__ x, int M) {
+  pdl_launch_dependents();
+  pdl_wait();
   int m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (m >= M) return;
   int lane = threadIdx.x & 31;
@@ -32,6 +34,8 @@ __global__ void gpt2_embed_kernel(const int32_t* __restrict__ ids, int ids_ld, c
 __global__ void layernorm_kernel(const float* __restrict__ x, int in_stride, int in_offset,
                                  const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                                  float* __restrict__ out_f32, bf16* __restrict__ out_bf16, int M, int d) {
+  pdl_launch_dependents();
+  pdl_wait();
   int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (r >= M) return;
   int lane = threadIdx.x & 31;
@@ -178,9 +182,11 @@ int k_gpt2_embed(const int32_t* ids, int ids_ld, const int* len_dev, int T, cons
   ARG_CHECK(d % 4 == 0, "embed: d %% 4 != 0");
   dim3 grid(ceil_div(M, 8)), block(256);
   if (wdtype == DT_F32)
-    gpt2_embed_kernel<float><<<grid, block, 0, st>>>(ids, ids_ld, len_dev, T, (const float*)wte, wpe, d, x, M);
+    CUDA_TRY(tutor_launch(gpt2_embed_kernel<float>, grid, block, 0, st, ids, ids_ld, len_dev, T, (const float*)wte, wpe,
+                          d, x, M));
   else
-    gpt2_embed_kernel<bf16><<<grid, block, 0, st>>>(ids, ids_ld, len_dev, T, (const bf16*)wte, wpe, d, x, M);
+    CUDA_TRY(tutor_launch(gpt2_embed_kernel<bf16>, grid, block, 0, st, ids, ids_ld, len_dev, T, (const bf16*)wte, wpe,
+                          d, x, M));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }
@@ -189,7 +195,8 @@ int k_layernorm(const float* x, int in_stride, int in_offset, const float* gamma
                 float* out_f32, bf16* out_bf16, int M, int d, cudaStream_t st) {
   ARG_CHECK(d % 4 == 0 && d <= 32 * LN_MAX_PER_LANE, "layernorm: unsupported d=%d", d);
   if (M == 0) return TUTOR_OK;
-  layernorm_kernel<<<ceil_div(M, 4), 128, 0, st>>>(x, in_stride, in_offset, gamma, beta, eps, out_f32, out_bf16, M, d);
+  CUDA_TRY(tutor_launch(layernorm_kernel, dim3(ceil_div(M, 4)), dim3(128), 0, st, x, in_stride, in_offset, gamma, beta,
+                        eps, out_f32, out_bf16, M, d));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }

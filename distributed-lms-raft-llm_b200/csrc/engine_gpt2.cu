@@ -45,6 +45,9 @@ struct tutor_gpt2 {
   int seen_words = 0;
   int* finished = nullptr;
   void* lm_scratch = nullptr;
+  float* partial = nullptr;   // split-K partial sums of the decode GEMMs (bf16 mode), [ks][B][N] fp32
+  int num_sms = 148;
+  bool use_fused = true, use_pdl = true;
   int* h_counters = nullptr;  // pinned
   // current generation
   int cur_B = 0, cur_T = 0, cur_total = 0;
@@ -125,6 +128,48 @@ int forward(tutor_gpt2* e, int B, int T, bool decode) {
   return TUTOR_OK;
 }
 
+// One decode forward (T == 1) in bf16 mode, B <= 128: every GEMM is split along K over ~all SMs and leaves raw
+// partials in L2; the reductions are fused with the work that follows (QKV -> attention prologue + cache append,
+// c_proj -> bias + residual + next LayerNorm, c_fc -> bias + gelu_new).  8 launches per layer, all deterministic.
+int forward_decode_fused(tutor_gpt2* e, int B) {
+  const int d = e->d;
+  cudaStream_t st = e->stream;
+  const float eps = e->cfg.layer_norm_epsilon;
+  bf16* xn = (bf16*)e->xn;
+  TRY(k_gpt2_embed(e->ids, e->ids_ld, e->counters, 1, e->wte, e->dt, e->wpe, d, e->x, B, st));
+  TRY(k_layernorm(e->x, 1, 0, e->layers[0].ln1_g, e->layers[0].ln1_b, eps, nullptr, xn, B, d, st));
+  for (int l = 0; l < e->L; ++l) {
+    const Gpt2Layer& w = e->layers[l];
+    int ks = k_pick_splitk(3 * d, d, e->num_sms);
+    TRY(k_gemm_bf16_splitk(xn, (const bf16*)w.qkv.w, B, 3 * d, d, ks, e->partial, st));
+    TRY(k_attn_decode_fused(e->partial, ks, w.qkv.b, e->kcache(l), e->vcache(l), DT_BF16, e->att, DT_BF16, B, e->H,
+                            e->Smax, e->counters, 0, st));
+    ks = k_pick_splitk(d, d, e->num_sms);
+    TRY(k_gemm_bf16_splitk((const bf16*)e->att, (const bf16*)w.proj.w, B, d, d, ks, e->partial, st));
+    TRY(k_reduce_bias_residual_ln(e->partial, ks, B, d, w.proj.b, e->x, w.ln2_g, w.ln2_b, eps, nullptr, xn, st));
+    ks = k_pick_splitk(4 * d, d, e->num_sms);
+    TRY(k_gemm_bf16_splitk(xn, (const bf16*)w.fc.w, B, 4 * d, d, ks, e->partial, st));
+    TRY(k_reduce_bias_act(e->partial, ks, B, 4 * d, w.fc.b, ACT_GELU_TANH, (bf16*)e->hbuf, st));
+    ks = k_pick_splitk(d, 4 * d, e->num_sms);
+    TRY(k_gemm_bf16_splitk((const bf16*)e->hbuf, (const bf16*)w.proj2.w, B, d, 4 * d, ks, e->partial, st));
+    const bool last = l + 1 == e->L;  // the last block's residual feeds ln_f, every other one the next ln_1
+    TRY(k_reduce_bias_residual_ln(e->partial, ks, B, d, w.proj2.b, e->x, last ? e->lnf_g : e->layers[l + 1].ln1_g,
+                                  last ? e->lnf_b : e->layers[l + 1].ln1_b, eps, nullptr,
+                                  last ? (bf16*)e->xn_last : xn, st));
+  }
+  return k_lmhead_argmax(e->xn_last, e->dt, e->wte, e->dt, B, e->V, d, e->dstate(), e->lm_scratch, st);
+}
+
+int decode_forward(tutor_gpt2* e, int B) {
+  if (e->dt == DT_BF16 && e->use_fused && B <= 128) {
+    tutor_pdl_enabled = e->use_pdl;  // every kernel on this path waits (griddepcontrol.wait) before dependent accesses
+    int rc = forward_decode_fused(e, B);
+    tutor_pdl_enabled = false;
+    return rc;
+  }
+  return forward(e, B, 1, true);
+}
+
 int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
   const int Smax = (int)round_up(total, 64);
   const size_t es = e->esz();
@@ -139,6 +184,17 @@ int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
     // rows past the current length are read (masked) by the attention kernels: they must hold finite values
     CUDA_TRY(cudaMemsetAsync(e->kv, 0, bytes, e->stream));
     dev_free(e->ids); dev_free(e->seen); dev_free(e->finished); dev_free(e->lm_scratch); dev_free(e->xn_last);
+    dev_free(e->partial);
+    if (e->dt == DT_BF16) {  // largest [ks][B][N] any decode GEMM of this model writes
+      const int d = e->d;
+      const int shapes[4][2] = {{3 * d, d}, {d, d}, {4 * d, d}, {d, 4 * d}};
+      size_t elems = 0;
+      for (auto& s : shapes) {
+        const size_t n = (size_t)k_pick_splitk(s[0], s[1], e->num_sms) * nb * s[0];
+        if (n > elems) elems = n;
+      }
+      TRY(dev_alloc(&e->partial, elems * sizeof(float)));
+    }
     e->ids_ld = ns;
     e->seen_words = ceil_div(e->V, 32);
     TRY(dev_alloc(&e->ids, (size_t)nb * ns * sizeof(int32_t)));
@@ -198,12 +254,12 @@ int run_steps(tutor_gpt2* e, int n_steps, bool poll_eos) {
       CUDA_TRY(cudaGraphLaunch(e->graph_exec, st));
       tutor_count_launches(e->graph_kernels);
     } else {
-      TRY(forward(e, B, 1, true));  // first step runs eagerly (also sets every kernel attribute) ...
+      TRY(decode_forward(e, B));  // first step runs eagerly (also sets every kernel attribute) ...
       if (e->use_graph && !e->graph_exec) {  // ... then one step is captured and replayed from here on
         cudaGraph_t g = nullptr;
         const uint64_t before = tutor_launch_count();
         CUDA_TRY(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        int rc = forward(e, B, 1, true);
+        int rc = decode_forward(e, B);
         cudaError_t ce = cudaStreamEndCapture(st, &g);
         const uint64_t n = tutor_launch_count() - before;
         tutor_count_launches((uint64_t)0 - n);  // captured launches did not run
@@ -274,6 +330,12 @@ int tutor_gpt2_create(const tutor_gpt2_config* cfg, int device, tutor_gpt2_t** o
   e->d = cfg->n_embd; e->H = cfg->n_head; e->L = cfg->n_layer; e->V = cfg->vocab_size; e->P = cfg->n_positions;
   e->layers.resize(e->L);
   e->use_graph = getenv("TUTOR_NO_GRAPH") == nullptr;
+  e->use_fused = getenv("TUTOR_NO_FUSED") == nullptr;  // debugging aids: unfused decode kernels / no PDL
+  e->use_pdl = getenv("TUTOR_NO_PDL") == nullptr;
+  {
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) e->num_sms = prop.multiProcessorCount;
+  }
   if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaMalloc(&e->counters, 2 * sizeof(int)) != cudaSuccess ||
       cudaMallocHost(&e->h_counters, 2 * sizeof(int)) != cudaSuccess) {
@@ -298,7 +360,7 @@ void tutor_gpt2_destroy(tutor_gpt2_t* e) {
   }
   dev_free(e->kv); dev_free(e->x); dev_free(e->xn); dev_free(e->q); dev_free(e->att); dev_free(e->hbuf);
   dev_free(e->xn_last); dev_free(e->ids); dev_free(e->counters); dev_free(e->seen); dev_free(e->finished);
-  dev_free(e->lm_scratch);
+  dev_free(e->lm_scratch); dev_free(e->partial);
   if (e->h_counters) cudaFreeHost(e->h_counters);
   cudaStreamDestroy(e->stream);
   delete e;

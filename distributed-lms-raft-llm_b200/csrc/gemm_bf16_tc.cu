@@ -22,7 +22,7 @@ namespace {
 
 constexpr int BM = 128, BK = 64, UMMA_K = 16;
 constexpr int NTHREADS = 192;
-enum { EPI_ROWMAJOR = 0, EPI_SWAPPED = 1, EPI_ARGMAX = 2 };
+enum { EPI_ROWMAJOR = 0, EPI_SWAPPED = 1, EPI_ARGMAX = 2, EPI_PARTIAL = 3 };
 
 struct ArgmaxArgs {
   const uint32_t* seen;  // [B][seen_words]
@@ -206,7 +206,9 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int a_row0 = blockIdx.x * BM, b_row0 = blockIdx.y * BN;
-  const int nk = K / BK;
+  // split-K: blockIdx.z owns k-blocks [kb0, kb0 + nk); gridDim.z == 1 for the unsplit flavours
+  const int nk = (K / BK) / (int)gridDim.z;
+  const int kb0 = (int)blockIdx.z * nk;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
@@ -227,17 +229,29 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  pdl_launch_dependents();
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      for (int kb = 0; kb < nk; ++kb) {
+      // PDL: in the swapped (decode) flavours operand A is a weight matrix nobody writes, so its first tiles are
+      // requested before waiting for the predecessor kernel; operand B (activations) only after the wait.
+      const bool a_is_static = (EPI != EPI_ROWMAJOR);
+      const int pre = a_is_static ? (nk < L::STAGES ? nk : L::STAGES) : 0;
+      for (int kb = 0; kb < pre; ++kb) {
+        mbar_expect_tx(&full_bar[kb], L::STAGE_BYTES);
+        tma_load_2d(tiles + kb * L::STAGE_BYTES, &tmA, &full_bar[kb], (kb0 + kb) * BK, a_row0);
+      }
+      pdl_wait();
+      for (int kb = 0; kb < pre; ++kb)
+        tma_load_2d(tiles + kb * L::STAGE_BYTES + L::A_BYTES, &tmB, &full_bar[kb], (kb0 + kb) * BK, b_row0);
+      for (int kb = pre; kb < nk; ++kb) {
         const int s = kb % L::STAGES;
         const uint32_t ph = (kb / L::STAGES) & 1;
         mbar_wait(&empty_bar[s], ph ^ 1, 0);
         mbar_expect_tx(&full_bar[s], L::STAGE_BYTES);
         uint8_t* sa = tiles + s * L::STAGE_BYTES;
-        tma_load_2d(sa, &tmA, &full_bar[s], kb * BK, a_row0);
-        tma_load_2d(sa + L::A_BYTES, &tmB, &full_bar[s], kb * BK, b_row0);
+        tma_load_2d(sa, &tmA, &full_bar[s], (kb0 + kb) * BK, a_row0);
+        tma_load_2d(sa + L::A_BYTES, &tmB, &full_bar[s], (kb0 + kb) * BK, b_row0);
       }
     }
   } else if (warp == 1) {
@@ -267,6 +281,7 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
     const int row = a_row0 + quad * 32 + lane;  // index along A's rows
     mbar_wait(tmem_full_bar, 0, 2);
     tc_fence_after();
+    pdl_wait();  // outputs may overwrite buffers the predecessor kernel still reads (already satisfied by now)
     const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16);
     if (EPI == EPI_ARGMAX) {
       // per-tile argmax over the 128 vocabulary rows for every batch column
@@ -317,6 +332,15 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
         tc_ld32(taddr + c0, v);  // warp-collective: executed by all lanes even for out-of-range rows
         if (EPI == EPI_ROWMAJOR) {
           if (row < rowsA && b_row0 + c0 < rowsB) store_run32(epi, row, b_row0 + c0, rowsB, v);
+        } else if (EPI == EPI_PARTIAL) {  // raw fp32 partial sums [z][m][n] for the fused reduce kernels
+          if (row < rowsA) {
+            float* dst = epi.out_f32 + (size_t)blockIdx.z * rowsB * rowsA + row;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const int m = b_row0 + c0 + i;
+              if (c0 + i < BN && m < rowsB) dst[(size_t)m * rowsA] = v[i];
+            }
+          }
         } else {  // EPI_SWAPPED: lane = output column n, TMEM column = batch row m
           if (row < rowsA) {
 #pragma unroll
@@ -379,7 +403,7 @@ int make_map(CUtensorMap* map, const bf16* ptr, int rows, int K, int box_rows) {
 
 template <int BN, int EPI>
 int launch(const bf16* A, int rowsA, const bf16* B, int rowsB, int K, const GemmEpilogue& epi, const ArgmaxArgs& am,
-           cudaStream_t st) {
+           cudaStream_t st, int ks = 1) {
   using L = SmemLayout<BN>;
   static bool attr_done = false;  // per instantiation; racing first calls set the same value
   if (!attr_done) {
@@ -390,20 +414,21 @@ int launch(const bf16* A, int rowsA, const bf16* B, int rowsB, int K, const Gemm
   CUtensorMap ta, tb;
   TRY(make_map(&ta, A, rowsA, K, BM));
   TRY(make_map(&tb, B, rowsB, K, BN));
-  dim3 grid(ceil_div(rowsA, BM), ceil_div(rowsB, BN));
-  gemm_bf16_tcgen05_kernel<BN, EPI><<<grid, NTHREADS, L::TOTAL, st>>>(ta, tb, rowsA, rowsB, K, epi, am);
+  dim3 grid(ceil_div(rowsA, BM), ceil_div(rowsB, BN), ks);
+  CUDA_TRY(tutor_launch(gemm_bf16_tcgen05_kernel<BN, EPI>, grid, dim3(NTHREADS), (size_t)L::TOTAL, st, ta, tb, rowsA, rowsB,
+                        K, epi, am));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }
 
 template <int EPI>
 int launch_swapped(const bf16* W, int N, const bf16* X, int M, int K, const GemmEpilogue& epi, const ArgmaxArgs& am,
-                   cudaStream_t st) {
+                   cudaStream_t st, int ks = 1) {
   // batch is the UMMA N dimension: pick the smallest tile that covers it, loop over batch tiles beyond 128
-  if (M <= 16) return launch<16, EPI>(W, N, X, M, K, epi, am, st);
-  if (M <= 32) return launch<32, EPI>(W, N, X, M, K, epi, am, st);
-  if (M <= 64) return launch<64, EPI>(W, N, X, M, K, epi, am, st);
-  return launch<128, EPI>(W, N, X, M, K, epi, am, st);
+  if (M <= 16) return launch<16, EPI>(W, N, X, M, K, epi, am, st, ks);
+  if (M <= 32) return launch<32, EPI>(W, N, X, M, K, epi, am, st, ks);
+  if (M <= 64) return launch<64, EPI>(W, N, X, M, K, epi, am, st, ks);
+  return launch<128, EPI>(W, N, X, M, K, epi, am, st, ks);
 }
 
 }  // namespace
@@ -414,6 +439,27 @@ int k_gemm_bf16(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpi
   ArgmaxArgs am{};
   if (M <= 128) return launch_swapped<EPI_SWAPPED>(W, N, A, M, K, epi, am, st);
   return launch<128, EPI_ROWMAJOR>(A, M, W, N, K, epi, am, st);
+}
+
+// Decode-time split-K: ks CTAs share one 128-row weight tile, each streaming K/ks of it, so that a GEMM whose
+// whole weight is only a few MB still spreads over ~all SMs.  Raw fp32 partials [ks][M][N] go to `partial`
+// (L2-resident); the fused reduce kernels in decode_fused.cu sum them in a fixed order (deterministic).
+int k_gemm_bf16_splitk(const bf16* X, const bf16* W, int M, int N, int K, int ks, float* partial, cudaStream_t st) {
+  ARG_CHECK(K % BK == 0 && ks >= 1 && (K / BK) % ks == 0, "gemm_bf16_splitk: K=%d not divisible into %d splits", K, ks);
+  ARG_CHECK(M >= 1 && M <= 128, "gemm_bf16_splitk: batch %d outside 1..128", M);
+  GemmEpilogue epi{};
+  epi.out_f32 = partial;
+  ArgmaxArgs am{};
+  return launch_swapped<EPI_PARTIAL>(W, N, X, M, K, epi, am, st, ks);
+}
+
+// number of K-splits for a decode GEMM: the largest divisor of K/64 that keeps tiles*ks within one wave of SMs
+int k_pick_splitk(int N, int K, int num_sms) {
+  const int tiles = ceil_div(N, BM), nk = K / BK;
+  int best = 1;
+  for (int ks = 1; ks <= nk && ks <= 32; ++ks)
+    if (nk % ks == 0 && tiles * ks <= num_sms) best = ks;
+  return best;
 }
 
 // fused LM head + repetition penalty + per-tile argmax; partials [ceil(V/128)][B]

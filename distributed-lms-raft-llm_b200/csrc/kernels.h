@@ -20,6 +20,8 @@ int k_gemm_f32(const float* A, const float* W, int M, int N, int K, const GemmEp
 
 // ---- gemm_bf16_tc.cu : same contraction on bf16 operands, fp32 accumulation in TMEM (tcgen05 + TMA)
 int k_gemm_bf16(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpilogue& epi, cudaStream_t st);
+int k_gemm_bf16_splitk(const bf16* X, const bf16* W, int M, int N, int K, int ks, float* partial, cudaStream_t st);
+int k_pick_splitk(int N, int K, int num_sms);
 // legacy mma.sync kernel kept only as an on-GPU cross-check of the tcgen05 kernel (tests)
 int k_gemm_bf16_legacy(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpilogue& epi, cudaStream_t st);
 
@@ -30,6 +32,20 @@ int k_attn_prefill(const void* q, int q_dtype, const void* k, const void* v, int
 // one query per (b,h) against cache positions [0, len): len = *len_dev if non-null else len_host
 int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int kv_dtype, void* out, int out_dtype,
                   int B, int H, int Smax, const int* len_dev, int len_host, cudaStream_t st);
+
+// fused QKV reduce + cache append + attention for the split-K decode path (bf16): qkv_partial [ks][B][3*H*64]
+int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias, void* k, void* v, int kv_dtype,
+                        void* out, int out_dtype, int B, int H, int Smax, const int* len_dev, int len_host,
+                        cudaStream_t st);
+
+// ---- decode_fused.cu : deterministic split-K reductions fused with what follows them
+// x[m,:] += bias + sum_z partial[z][m][:]  (x fp32 in/out), then LayerNorm(x[m,:]) -> xn
+int k_reduce_bias_residual_ln(const float* partial, int ks, int M, int N, const float* bias, float* x,
+                              const float* gamma, const float* beta, float eps, float* xn_f32, bf16* xn_bf16,
+                              cudaStream_t st);
+// out[m,n] = act(bias[n] + sum_z partial[z][m][n]) as bf16
+int k_reduce_bias_act(const float* partial, int ks, int M, int N, const float* bias, int act, bf16* out,
+                      cudaStream_t st);
 
 // ---- lmhead.cu : fused LM head + repetition penalty + argmax (no logits tensor)
 struct DecodeState {

@@ -72,20 +72,33 @@ __global__ void __launch_bounds__(256) lmhead_argmax_simt_kernel(const float* __
   }
 }
 
-__global__ void argmax_finalize_kernel(const float* __restrict__ part_val, const int* __restrict__ part_idx,
-                                       int nparts, int B, DecodeState ds) {
+// one warp per batch row scans the partials (independent loads in flight instead of one dependent chain)
+__global__ void __launch_bounds__(1024) argmax_finalize_kernel(const float* __restrict__ part_val,
+                                                               const int* __restrict__ part_idx, int nparts, int B,
+                                                               DecodeState ds) {
   __shared__ int all_finished;
+  pdl_launch_dependents();
+  pdl_wait();
   if (threadIdx.x == 0) all_finished = 1;
   __syncthreads();
   const int len = ds.plain_out ? 0 : *ds.len;
-  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  for (int b = warp; b < B; b += nwarps) {
     float bv = -CUDART_INF_F;
     int bi = 0x7fffffff;
-    for (int p = 0; p < nparts; ++p) {
+#pragma unroll 4
+    for (int p = lane; p < nparts; p += 32) {
       float v = part_val[(size_t)p * B + b];
       int i = part_idx[(size_t)p * B + b];
       if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; }
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    }
+    if (lane != 0) continue;
     if (bi == 0x7fffffff) bi = 0;  // all-NaN row: stay in range
     if (ds.plain_out) { ds.plain_out[b] = bi; continue; }
     int fin = ds.finished[b];
@@ -144,7 +157,7 @@ int k_lmhead_argmax(const void* xn, int x_dtype, const void* wte, int w_dtype, i
     ARG_CHECK(nparts <= LM_MAX_PARTS, "lmhead: vocabulary %d too large for the partial buffer", V);
     TRY(k_gemm_bf16_argmax((const bf16*)wte, V, (const bf16*)xn, B, d, ds.seen, ds.seen_words, ds.penalty, pv, pi, st));
   }
-  argmax_finalize_kernel<<<1, 256, 0, st>>>(pv, pi, nparts, B, ds);
+  CUDA_TRY(tutor_launch(argmax_finalize_kernel, dim3(1), dim3(1024), 0, st, (const float*)pv, (const int*)pi, nparts, B, ds));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }

@@ -161,3 +161,24 @@ def test_cfg2_fp32_parity_subset(small_f32, golden):
         mism = np.nonzero(mine[b] != ref[b])[0]
         if mism.size:
             assert gap[b, mism[0]] < 1e-4, (b, mism[0], gap[b, mism[0]])
+
+
+def test_fused_decode_path_matches_unfused(pkg, tiny_hf, monkeypatch):
+    """bf16 decode runs split-K GEMMs with fused reductions; TUTOR_NO_FUSED=1 selects the plain kernel chain.
+    Same weights, same prompt: logits must agree to bf16 noise and the greedy ids must be the same."""
+    ids = rp.gpt2_prompt_ids(5, 9, seed=11, vocab=1000)
+    fused = pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="bf16")
+    monkeypatch.setenv("TUTOR_NO_FUSED", "1")
+    plain = pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="bf16")
+    monkeypatch.delenv("TUTOR_NO_FUSED")
+    logits = []
+    for eng in (fused, plain):
+        eng.prefill(ids, max_new_tokens=24, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
+        eng.step(12)
+        logits.append(eng.last_logits().float().cpu())
+    err = ((logits[0] - logits[1]).abs().max() / logits[1].abs().max()).item()
+    print(f"fused vs unfused bf16 decode: relative logit difference {err:.3e}")
+    assert err < 2e-2
+    a = fused.generate(ids, max_new_tokens=24, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
+    b = plain.generate(ids, max_new_tokens=24, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
+    assert (a == b).float().mean().item() > 0.9
