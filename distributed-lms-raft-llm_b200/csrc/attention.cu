@@ -256,6 +256,168 @@ __global__ void __launch_bounds__(PF_Q) attn_prefill_kernel(const QT* __restrict
   }
 }
 
+// ------------------------------------------------------------------- prefill on tensor cores (bf16)
+// Flash-attention-2 style: grid (ceil(T/64), H, B), 4 warps x 16 query rows.  Q lives in registers as
+// mma.m16n8k16 A-fragments; K/V tiles of 64 keys are staged with cp.async into XOR-swizzled shared memory
+// (double buffered) and read with ldmatrix (K) / ldmatrix.trans (V); S = QK^T and O += PV accumulate in fp32,
+// the online softmax runs on the accumulator fragments and P is re-packed to bf16 A-fragments in registers.
+// (The dense projections around it are the tcgen05 kernel; attention at these sizes - T <= 1024, hd 64 - is
+// ~5 % of the prefill FLOPs, so the warp-level tensor path is enough to take it off the critical path.)
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void ldmatrix_x4(uint32_t* r, const void* smem) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"((uint32_t)__cvta_generic_to_shared(smem)));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t* r, const void* smem) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"((uint32_t)__cvta_generic_to_shared(smem)));
+}
+__device__ __forceinline__ void mma_bf16_16816(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 p = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&p);
+}
+
+template <bool CAUSAL>
+__global__ void __launch_bounds__(128) attn_prefill_mma_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc,
+                                                                const bf16* __restrict__ vc, bf16* __restrict__ out,
+                                                                int H, int T, int Smax) {
+  __shared__ __align__(128) uint8_t tiles[2][2][64 * 128];  // [stage][K|V][64 keys x 128 B], 16-byte chunks XOR-swizzled
+  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int d = H * 64;
+  const int q0 = qt * 64 + warp * 16;
+  uint32_t qf[4][4];
+  {
+    const bf16* p0 = q + ((size_t)b * T + min(q0 + g, T - 1)) * d + h * 64 + 2 * t;
+    const bf16* p1 = q + ((size_t)b * T + min(q0 + g + 8, T - 1)) * d + h * 64 + 2 * t;
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+      qf[kk][0] = *reinterpret_cast<const uint32_t*>(p0 + kk * 16);
+      qf[kk][1] = *reinterpret_cast<const uint32_t*>(p1 + kk * 16);
+      qf[kk][2] = *reinterpret_cast<const uint32_t*>(p0 + kk * 16 + 8);
+      qf[kk][3] = *reinterpret_cast<const uint32_t*>(p1 + kk * 16 + 8);
+    }
+  }
+  float o[8][4];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
+  float m0 = -CUDART_INF_F, m1 = -CUDART_INF_F, l0 = 0.f, l1 = 0.f;
+  const size_t base = ((size_t)b * H + h) * Smax * 64;
+  const int nkt_all = (T + 63) / 64;
+  const int nkt = CAUSAL ? min(qt + 1, nkt_all) : nkt_all;
+
+  auto load_tile = [&](int kt, int stage) {
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int idx = threadIdx.x + 128 * r;
+      const int row = idx >> 3, ch = idx & 7;
+      const int key = min(kt * 64 + row, T - 1);
+      const size_t src = base + (size_t)key * 64 + ch * 8;
+      const int dst = row * 128 + ((ch ^ (row & 7)) << 4);
+      cp_async16(&tiles[stage][0][dst], kc + src);
+      cp_async16(&tiles[stage][1][dst], vc + src);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  load_tile(0, 0);
+  for (int kt = 0; kt < nkt; ++kt) {
+    const int stage = kt & 1;
+    if (kt + 1 < nkt) {
+      load_tile(kt + 1, stage ^ 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+    const uint8_t* sK = tiles[stage][0];
+    const uint8_t* sV = tiles[stage][1];
+    float s[8][4];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+      uint32_t kb[8];
+      const int row = j * 8 + (lane & 7);
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int ch = half * 4 + (lane >> 3);
+        ldmatrix_x4(&kb[half * 4], sK + row * 128 + ((ch ^ (row & 7)) << 4));
+      }
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) mma_bf16_16816(s[j], qf[kk], kb[2 * kk], kb[2 * kk + 1]);
+    }
+    float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int key = kt * 64 + j * 8 + 2 * t + (r & 1);
+        const int qrow = q0 + g + (r >> 1) * 8;
+        float v = s[j][r] * 0.125f;
+        if (key >= T || (CAUSAL && key > qrow)) v = -CUDART_INF_F;
+        s[j][r] = v;
+      }
+      mx0 = fmaxf(mx0, fmaxf(s[j][0], s[j][1]));
+      mx1 = fmaxf(mx1, fmaxf(s[j][2], s[j][3]));
+    }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    // key 0 is visible to every row in tile 0, so the running maxima are finite from the first tile on
+    const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
+    const float c0 = __expf(m0 - mn0), c1 = __expf(m1 - mn1);
+    l0 *= c0; l1 *= c1;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { o[j][0] *= c0; o[j][1] *= c0; o[j][2] *= c1; o[j][3] *= c1; }
+    uint32_t pa[4][4];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float p0 = __expf(s[j][0] - mn0), p1 = __expf(s[j][1] - mn0);
+      const float p2 = __expf(s[j][2] - mn1), p3 = __expf(s[j][3] - mn1);
+      l0 += p0 + p1; l1 += p2 + p3;
+      pa[j >> 1][(j & 1) * 2] = pack_bf16x2(p0, p1);
+      pa[j >> 1][(j & 1) * 2 + 1] = pack_bf16x2(p2, p3);
+    }
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+#pragma unroll
+      for (int jp = 0; jp < 4; ++jp) {
+        const int mi = lane >> 3;
+        const int krow = kk * 16 + (mi & 1) * 8 + (lane & 7);
+        const int ch = 2 * jp + (mi >> 1);
+        uint32_t vb[4];
+        ldmatrix_x4_trans(vb, sV + krow * 128 + ((ch ^ (krow & 7)) << 4));
+        mma_bf16_16816(o[2 * jp], pa[kk], vb[0], vb[1]);
+        mma_bf16_16816(o[2 * jp + 1], pa[kk], vb[2], vb[3]);
+      }
+    }
+    m0 = mn0; m1 = mn1;
+    __syncthreads();  // everyone is done with this stage before the next iteration's cp.async refills it
+  }
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+  const float i0 = 1.0f / l0, i1 = 1.0f / l1;
+  const int r0 = q0 + g, r1 = q0 + g + 8;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (r0 < T)
+      *reinterpret_cast<uint32_t*>(out + ((size_t)b * T + r0) * d + h * 64 + j * 8 + 2 * t) =
+          pack_bf16x2(o[j][0] * i0, o[j][1] * i0);
+    if (r1 < T)
+      *reinterpret_cast<uint32_t*>(out + ((size_t)b * T + r1) * d + h * 64 + j * 8 + 2 * t) =
+          pack_bf16x2(o[j][2] * i1, o[j][3] * i1);
+  }
+}
+
 }  // namespace
 
 int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int kv_dtype, void* out, int out_dtype,
@@ -299,9 +461,15 @@ int k_attn_prefill(const void* q, int q_dtype, const void* k, const void* v, int
   if (q_dtype == DT_F32 && kv_dtype == DT_F32 && out_dtype == DT_F32)
     attn_prefill_kernel<float, float, float, false><<<grid, block, 0, st>>>(
         (const float*)q, (const float*)k, (const float*)v, (float*)out, H, T, Smax, causal);
-  else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16)
-    attn_prefill_kernel<bf16, bf16, bf16, true><<<grid, block, 0, st>>>(
-        (const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)out, H, T, Smax, causal);
+  else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16) {
+    dim3 g2(ceil_div(T, 64), H, B);
+    if (causal)
+      attn_prefill_mma_kernel<true><<<g2, 128, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)out, H, T,
+                                                        Smax);
+    else
+      attn_prefill_mma_kernel<false><<<g2, 128, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)out, H,
+                                                         T, Smax);
+  }
   else {
     tutor_set_error("attn_prefill: unsupported dtype combination q=%d kv=%d out=%d", q_dtype, kv_dtype, out_dtype);
     return TUTOR_ERR_ARG;

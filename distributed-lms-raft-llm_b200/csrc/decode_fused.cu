@@ -27,8 +27,16 @@ __global__ void __launch_bounds__(256) reduce_bias_residual_ln_kernel(
   pdl_launch_dependents();
   pdl_wait();
   const int m = blockIdx.x;
-  float4 v[2];
+  float4 v[2], gm[2], bt[2];  // gamma/beta are fetched with the first wave of loads, not after the reductions
   float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int c = (threadIdx.x + j * 256) * 4;
+    if (c < N) {
+      gm[j] = *reinterpret_cast<const float4*>(gamma + c);
+      bt[j] = *reinterpret_cast<const float4*>(beta + c);
+    }
+  }
 #pragma unroll
   for (int j = 0; j < 2; ++j) {
     const int c = (threadIdx.x + j * 256) * 4;
@@ -61,7 +69,7 @@ __global__ void __launch_bounds__(256) reduce_bias_residual_ln_kernel(
   for (int j = 0; j < 2; ++j) {
     const int c = (threadIdx.x + j * 256) * 4;
     if (c < N) {
-      const float4 g = *reinterpret_cast<const float4*>(gamma + c), b = *reinterpret_cast<const float4*>(beta + c);
+      const float4 g = gm[j], b = bt[j];
       float4 o;
       o.x = (v[j].x - mean) * rstd * g.x + b.x;
       o.y = (v[j].y - mean) * rstd * g.y + b.y;

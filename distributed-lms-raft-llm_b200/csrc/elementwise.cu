@@ -31,6 +31,10 @@ __global__ void gpt2_embed_kernel(const int32_t* __restrict__ ids, int ids_ld, c
 
 // ---- LayerNorm over the last axis, biased variance, two-pass on a register-resident row.
 // in row r is read from x[(r*in_stride + in_offset)*d]; optional fp32 and bf16 outputs.
+// NV4 = float4 slots per lane (d <= 128*NV4); every load (row, gamma, beta) is issued up front so the kernel
+// pays one memory round trip, not one per slot (the first version loaded gamma/beta inside the output loop:
+// 3.0 us for 64 rows; see profiles/README.md).
+template <int NV4>
 __global__ void layernorm_kernel(const float* __restrict__ x, int in_stride, int in_offset,
                                  const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                                  float* __restrict__ out_f32, bf16* __restrict__ out_bf16, int M, int d) {
@@ -40,40 +44,44 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int in_stride, int
   if (r >= M) return;
   int lane = threadIdx.x & 31;
   const float* xr = x + ((size_t)r * in_stride + in_offset) * d;
-  float v[LN_MAX_PER_LANE];
+  float4 v[NV4], g[NV4], b[NV4];
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int j = 0; j < NV4; ++j) {
+    const int i = lane * 4 + j * 128;
+    const bool ok = i < d;
+    v[j] = ok ? load4(xr + i) : zero;
+    g[j] = ok ? load4(gamma + i) : zero;
+    b[j] = ok ? load4(beta + i) : zero;
+  }
   float s = 0.f;
 #pragma unroll
-  for (int j = 0; j < LN_V4; ++j) {
-    int i = lane * 4 + j * 128;
-    float4 a = (i < d) ? load4(xr + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-    v[4 * j] = a.x; v[4 * j + 1] = a.y; v[4 * j + 2] = a.z; v[4 * j + 3] = a.w;
-    s += (a.x + a.y) + (a.z + a.w);
-  }
-  float mean = warp_sum(s) / d;
+  for (int j = 0; j < NV4; ++j) s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+  const float mean = warp_sum(s) / d;
   float q = 0.f;
 #pragma unroll
-  for (int j = 0; j < LN_V4; ++j) {
+  for (int j = 0; j < NV4; ++j) {
     if (lane * 4 + j * 128 < d) {
-#pragma unroll
-      for (int k = 0; k < 4; ++k) { float c = v[4 * j + k] - mean; q += c * c; }
+      const float a0 = v[j].x - mean, a1 = v[j].y - mean, a2 = v[j].z - mean, a3 = v[j].w - mean;
+      q += (a0 * a0 + a1 * a1) + (a2 * a2 + a3 * a3);
     }
   }
-  float rstd = 1.0f / sqrtf(warp_sum(q) / d + eps);
+  const float rstd = 1.0f / sqrtf(warp_sum(q) / d + eps);
 #pragma unroll
-  for (int j = 0; j < LN_V4; ++j) {
-    const int i = lane * 4 + j * 128, nv = 4 * j;
-    if (i >= d) break;
-    float4 g = load4(gamma + i), b = load4(beta + i);
-    float4 o;
-    o.x = (v[nv] - mean) * rstd * g.x + b.x;
-    o.y = (v[nv + 1] - mean) * rstd * g.y + b.y;
-    o.z = (v[nv + 2] - mean) * rstd * g.z + b.z;
-    o.w = (v[nv + 3] - mean) * rstd * g.w + b.w;
-    if (out_f32) *reinterpret_cast<float4*>(out_f32 + (size_t)r * d + i) = o;
-    if (out_bf16) {
-      __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
-      uint2 pk = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
-      *reinterpret_cast<uint2*>(out_bf16 + (size_t)r * d + i) = pk;
+  for (int j = 0; j < NV4; ++j) {
+    const int i = lane * 4 + j * 128;
+    if (i < d) {
+      float4 o;
+      o.x = (v[j].x - mean) * rstd * g[j].x + b[j].x;
+      o.y = (v[j].y - mean) * rstd * g[j].y + b[j].y;
+      o.z = (v[j].z - mean) * rstd * g[j].z + b[j].z;
+      o.w = (v[j].w - mean) * rstd * g[j].w + b[j].w;
+      if (out_f32) *reinterpret_cast<float4*>(out_f32 + (size_t)r * d + i) = o;
+      if (out_bf16) {
+        __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
+        *reinterpret_cast<uint2*>(out_bf16 + (size_t)r * d + i) =
+            make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+      }
     }
   }
 }
@@ -195,8 +203,15 @@ int k_layernorm(const float* x, int in_stride, int in_offset, const float* gamma
                 float* out_f32, bf16* out_bf16, int M, int d, cudaStream_t st) {
   ARG_CHECK(d % 4 == 0 && d <= 32 * LN_MAX_PER_LANE, "layernorm: unsupported d=%d", d);
   if (M == 0) return TUTOR_OK;
-  CUDA_TRY(tutor_launch(layernorm_kernel, dim3(ceil_div(M, 4)), dim3(128), 0, st, x, in_stride, in_offset, gamma, beta,
-                        eps, out_f32, out_bf16, M, d));
+  const dim3 grid(ceil_div(M, 4)), block(128);
+#define LN_LAUNCH(NV4)                                                                                              \
+  CUDA_TRY(tutor_launch(layernorm_kernel<NV4>, grid, block, 0, st, x, in_stride, in_offset, gamma, beta, eps, out_f32, \
+                        out_bf16, M, d))
+  if (d <= 128) LN_LAUNCH(1);
+  else if (d <= 768) LN_LAUNCH(6);
+  else if (d <= 1280) LN_LAUNCH(10);
+  else LN_LAUNCH(16);
+#undef LN_LAUNCH
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }

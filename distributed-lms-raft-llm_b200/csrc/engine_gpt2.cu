@@ -40,14 +40,22 @@ struct tutor_gpt2 {
   // decode state
   int32_t* ids = nullptr;
   int ids_ld = 0;
-  int* counters = nullptr;  // [0]=len [1]=stop_len
+  int* counters = nullptr;  // per decode lane i: [2i]=len [2i+1]=stop_len (lane 0 is also what prefill updates)
   uint32_t* seen = nullptr;
   int seen_words = 0;
   int* finished = nullptr;
   void* lm_scratch = nullptr;
-  float* partial = nullptr;   // split-K partial sums of the decode GEMMs (bf16 mode), [ks][B][N] fp32
+  float* partial = nullptr;   // split-K partial sums of the decode GEMMs (bf16 mode), [ks][B][N] fp32, one slice per lane
+  size_t partial_lane_elems = 0, lm_scratch_lane_bytes = 0;
   int num_sms = 148;
   bool use_fused = true, use_pdl = true;
+  // Decode lanes: the batch is cut into micro-batches whose kernel chains run concurrently (own stream, own
+  // length counter), so one lane's latency-bound GEMM/reduce chain overlaps the other's bandwidth-bound attention.
+  static constexpr int MAX_LANES = 4;
+  int cfg_lanes = 1, nlanes = 1;  // TUTOR_LANES=2|4 measured slower than 1 on B200 (profiles/README.md)
+  cudaStream_t lane_stream[MAX_LANES] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_fork = nullptr, ev_join[MAX_LANES] = {nullptr, nullptr, nullptr, nullptr};
+  int lane_b0(int i) const { return (int)((long long)cur_B * i / nlanes); }
   int* h_counters = nullptr;  // pinned
   // current generation
   int cur_B = 0, cur_T = 0, cur_total = 0;
@@ -65,10 +73,10 @@ struct tutor_gpt2 {
   void* vcache(int l) const {
     return (uint8_t*)kv + (size_t)(2 * l + 1) * Bcap * H * Smax * 64 * esz();
   }
-  DecodeState dstate() const {
+  DecodeState dstate(int lane = 0, int b0 = 0) const {
     DecodeState ds{};
-    ds.ids = ids; ds.ids_ld = ids_ld; ds.len = counters; ds.stop_len = counters + 1;
-    ds.seen = seen; ds.seen_words = seen_words; ds.finished = finished;
+    ds.ids = ids + (size_t)b0 * ids_ld; ds.ids_ld = ids_ld; ds.len = counters + 2 * lane; ds.stop_len = counters + 2 * lane + 1;
+    ds.seen = seen + (size_t)b0 * seen_words; ds.seen_words = seen_words; ds.finished = finished + b0;
     ds.penalty = cur_penalty; ds.eos_id = cur_eos; ds.pad_id = cur_pad;
     return ds;
   }
@@ -128,46 +136,67 @@ int forward(tutor_gpt2* e, int B, int T, bool decode) {
   return TUTOR_OK;
 }
 
-// One decode forward (T == 1) in bf16 mode, B <= 128: every GEMM is split along K over ~all SMs and leaves raw
-// partials in L2; the reductions are fused with the work that follows (QKV -> attention prologue + cache append,
-// c_proj -> bias + residual + next LayerNorm, c_fc -> bias + gelu_new).  8 launches per layer, all deterministic.
-int forward_decode_fused(tutor_gpt2* e, int B) {
+// One decode forward (T == 1) in bf16 mode for the rows [b0, b0+B) of one lane: every GEMM is split along K over
+// ~all SMs and leaves raw partials in L2; the reductions are fused with the work that follows (QKV -> attention
+// prologue + cache append, c_proj -> bias + residual + next LayerNorm, c_fc -> bias + gelu_new).
+// 8 launches per layer, all deterministic.
+int forward_decode_fused(tutor_gpt2* e, int lane, int b0, int B) {
   const int d = e->d;
-  cudaStream_t st = e->stream;
+  cudaStream_t st = e->lane_stream[lane];
   const float eps = e->cfg.layer_norm_epsilon;
-  bf16* xn = (bf16*)e->xn;
-  TRY(k_gpt2_embed(e->ids, e->ids_ld, e->counters, 1, e->wte, e->dt, e->wpe, d, e->x, B, st));
-  TRY(k_layernorm(e->x, 1, 0, e->layers[0].ln1_g, e->layers[0].ln1_b, eps, nullptr, xn, B, d, st));
+  const int* len = e->counters + 2 * lane;
+  float* x = e->x + (size_t)b0 * d;
+  bf16* xn = (bf16*)e->xn + (size_t)b0 * d;
+  bf16* att = (bf16*)e->att + (size_t)b0 * d;
+  bf16* hb = (bf16*)e->hbuf + (size_t)b0 * 4 * d;
+  bf16* xl = (bf16*)e->xn_last + (size_t)b0 * d;
+  float* partial = e->partial + (size_t)lane * e->partial_lane_elems;
+  const size_t kv_off = (size_t)b0 * e->H * e->Smax * 64 * e->esz();
+  TRY(k_gpt2_embed(e->ids + (size_t)b0 * e->ids_ld, e->ids_ld, len, 1, e->wte, e->dt, e->wpe, d, x, B, st));
+  TRY(k_layernorm(x, 1, 0, e->layers[0].ln1_g, e->layers[0].ln1_b, eps, nullptr, xn, B, d, st));
   for (int l = 0; l < e->L; ++l) {
     const Gpt2Layer& w = e->layers[l];
+    void* kc = (uint8_t*)e->kcache(l) + kv_off;
+    void* vc = (uint8_t*)e->vcache(l) + kv_off;
     int ks = k_pick_splitk(3 * d, d, e->num_sms);
-    TRY(k_gemm_bf16_splitk(xn, (const bf16*)w.qkv.w, B, 3 * d, d, ks, e->partial, st));
-    TRY(k_attn_decode_fused(e->partial, ks, w.qkv.b, e->kcache(l), e->vcache(l), DT_BF16, e->att, DT_BF16, B, e->H,
-                            e->Smax, e->counters, 0, st));
+    TRY(k_gemm_bf16_splitk(xn, (const bf16*)w.qkv.w, B, 3 * d, d, ks, partial, st));
+    TRY(k_attn_decode_fused(partial, ks, w.qkv.b, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0, st));
     ks = k_pick_splitk(d, d, e->num_sms);
-    TRY(k_gemm_bf16_splitk((const bf16*)e->att, (const bf16*)w.proj.w, B, d, d, ks, e->partial, st));
-    TRY(k_reduce_bias_residual_ln(e->partial, ks, B, d, w.proj.b, e->x, w.ln2_g, w.ln2_b, eps, nullptr, xn, st));
+    TRY(k_gemm_bf16_splitk(att, (const bf16*)w.proj.w, B, d, d, ks, partial, st));
+    TRY(k_reduce_bias_residual_ln(partial, ks, B, d, w.proj.b, x, w.ln2_g, w.ln2_b, eps, nullptr, xn, st));
     ks = k_pick_splitk(4 * d, d, e->num_sms);
-    TRY(k_gemm_bf16_splitk(xn, (const bf16*)w.fc.w, B, 4 * d, d, ks, e->partial, st));
-    TRY(k_reduce_bias_act(e->partial, ks, B, 4 * d, w.fc.b, ACT_GELU_TANH, (bf16*)e->hbuf, st));
+    TRY(k_gemm_bf16_splitk(xn, (const bf16*)w.fc.w, B, 4 * d, d, ks, partial, st));
+    TRY(k_reduce_bias_act(partial, ks, B, 4 * d, w.fc.b, ACT_GELU_TANH, hb, st));
     ks = k_pick_splitk(d, 4 * d, e->num_sms);
-    TRY(k_gemm_bf16_splitk((const bf16*)e->hbuf, (const bf16*)w.proj2.w, B, d, 4 * d, ks, e->partial, st));
+    TRY(k_gemm_bf16_splitk(hb, (const bf16*)w.proj2.w, B, d, 4 * d, ks, partial, st));
     const bool last = l + 1 == e->L;  // the last block's residual feeds ln_f, every other one the next ln_1
-    TRY(k_reduce_bias_residual_ln(e->partial, ks, B, d, w.proj2.b, e->x, last ? e->lnf_g : e->layers[l + 1].ln1_g,
-                                  last ? e->lnf_b : e->layers[l + 1].ln1_b, eps, nullptr,
-                                  last ? (bf16*)e->xn_last : xn, st));
+    TRY(k_reduce_bias_residual_ln(partial, ks, B, d, w.proj2.b, x, last ? e->lnf_g : e->layers[l + 1].ln1_g,
+                                  last ? e->lnf_b : e->layers[l + 1].ln1_b, eps, nullptr, last ? xl : xn, st));
   }
-  return k_lmhead_argmax(e->xn_last, e->dt, e->wte, e->dt, B, e->V, d, e->dstate(), e->lm_scratch, st);
+  return k_lmhead_argmax(xl, e->dt, e->wte, e->dt, B, e->V, d, e->dstate(lane, b0),
+                         (uint8_t*)e->lm_scratch + (size_t)lane * e->lm_scratch_lane_bytes, st);
 }
 
 int decode_forward(tutor_gpt2* e, int B) {
-  if (e->dt == DT_BF16 && e->use_fused && B <= 128) {
-    tutor_pdl_enabled = e->use_pdl;  // every kernel on this path waits (griddepcontrol.wait) before dependent accesses
-    int rc = forward_decode_fused(e, B);
-    tutor_pdl_enabled = false;
-    return rc;
+  if (!(e->dt == DT_BF16 && e->use_fused && B <= 128)) return forward(e, B, 1, true);
+  // fork: lanes 1.. wait for everything already queued on the main stream, then all chains run concurrently
+  if (e->nlanes > 1) {
+    CUDA_TRY(cudaEventRecord(e->ev_fork, e->stream));
+    for (int i = 1; i < e->nlanes; ++i) CUDA_TRY(cudaStreamWaitEvent(e->lane_stream[i], e->ev_fork, 0));
   }
-  return forward(e, B, 1, true);
+  tutor_pdl_enabled = e->use_pdl;  // every kernel on this path waits (griddepcontrol.wait) before dependent accesses
+  int rc = TUTOR_OK;
+  for (int i = 0; i < e->nlanes && rc == TUTOR_OK; ++i) {
+    const int b0 = e->lane_b0(i), b1 = e->lane_b0(i + 1);
+    rc = forward_decode_fused(e, i, b0, b1 - b0);
+  }
+  tutor_pdl_enabled = false;
+  if (rc != TUTOR_OK) return rc;
+  for (int i = 1; i < e->nlanes; ++i) {  // join
+    CUDA_TRY(cudaEventRecord(e->ev_join[i], e->lane_stream[i]));
+    CUDA_TRY(cudaStreamWaitEvent(e->stream, e->ev_join[i], 0));
+  }
+  return TUTOR_OK;
 }
 
 int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
@@ -193,14 +222,16 @@ int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
         const size_t n = (size_t)k_pick_splitk(s[0], s[1], e->num_sms) * nb * s[0];
         if (n > elems) elems = n;
       }
-      TRY(dev_alloc(&e->partial, elems * sizeof(float)));
+      e->partial_lane_elems = elems;  // every lane slice can hold the whole batch (lanes only ever hold a part of it)
+      TRY(dev_alloc(&e->partial, tutor_gpt2::MAX_LANES * elems * sizeof(float)));
     }
     e->ids_ld = ns;
     e->seen_words = ceil_div(e->V, 32);
     TRY(dev_alloc(&e->ids, (size_t)nb * ns * sizeof(int32_t)));
     TRY(dev_alloc(&e->seen, (size_t)nb * e->seen_words * sizeof(uint32_t)));
     TRY(dev_alloc(&e->finished, (size_t)nb * sizeof(int)));
-    TRY(dev_alloc(&e->lm_scratch, k_lmhead_scratch_bytes(nb, e->V)));
+    e->lm_scratch_lane_bytes = k_lmhead_scratch_bytes(nb, e->V);
+    TRY(dev_alloc(&e->lm_scratch, tutor_gpt2::MAX_LANES * e->lm_scratch_lane_bytes));
     TRY(dev_alloc(&e->xn_last, (size_t)nb * e->d * 4));
     e->Bcap = nb; e->Smax = ns;
   }
@@ -234,7 +265,10 @@ int check_args(tutor_gpt2* e, int B, int T, int total) {
 
 // common prologue once the prompt is in e->ids (device, int32, row stride ids_ld)
 int start_generation(tutor_gpt2* e, int B, int T, int total, float penalty, int eos, int pad) {
-  if (penalty != e->cur_penalty || eos != e->cur_eos || pad != e->cur_pad || B != e->cur_B) drop_graph(e);
+  const int nl = (e->dt == DT_BF16 && e->use_fused && B <= 128) ? (B >= 2 * e->cfg_lanes ? e->cfg_lanes : 1) : 1;
+  if (penalty != e->cur_penalty || eos != e->cur_eos || pad != e->cur_pad || B != e->cur_B || nl != e->nlanes)
+    drop_graph(e);
+  e->nlanes = nl;
   e->cur_B = B; e->cur_T = T; e->cur_total = total; e->cur_penalty = penalty; e->cur_eos = eos; e->cur_pad = pad;
   cudaStream_t st = e->stream;
   e->h_counters[0] = T; e->h_counters[1] = 0;
@@ -243,8 +277,13 @@ int start_generation(tutor_gpt2* e, int B, int T, int total, float penalty, int 
   CUDA_TRY(cudaMemsetAsync(e->seen, 0, (size_t)B * e->seen_words * sizeof(uint32_t), st));
   // the penalty covers every id so far, prompt included (logits_process.py:404-410)
   TRY(k_seen_bitmap(e->ids, e->ids_ld, T, e->seen, e->seen_words, B, st));
-  return forward(e, B, T, false);  // selects token T, len becomes T+1
+  TRY(forward(e, B, T, false));  // selects token T, len becomes T+1
+  for (int i = 1; i < e->nlanes; ++i)  // every lane continues from the same length with its own counter pair
+    CUDA_TRY(cudaMemcpyAsync(e->counters + 2 * i, e->counters, 2 * sizeof(int), cudaMemcpyDeviceToDevice, st));
+  return TUTOR_OK;
 }
+
+int read_counters(tutor_gpt2* e, int* len, int* stop_len);
 
 int run_steps(tutor_gpt2* e, int n_steps, bool poll_eos) {
   const int B = e->cur_B;
@@ -272,19 +311,27 @@ int run_steps(tutor_gpt2* e, int n_steps, bool poll_eos) {
       }
     }
     if (poll_eos && e->cur_eos >= 0 && (i % 32) == 31 && i + 1 < n_steps) {
-      CUDA_TRY(cudaMemcpyAsync(e->h_counters, e->counters, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
-      CUDA_TRY(cudaStreamSynchronize(st));
-      if (e->h_counters[1] != 0) break;  // every row has produced EOS (utils.py:2804-2805)
+      int len, stop;
+      TRY(read_counters(e, &len, &stop));
+      if (stop != 0) break;  // every row has produced EOS (utils.py:2804-2805)
     }
   }
   return TUTOR_OK;
 }
 
+// len is common to all lanes; generation has stopped once every lane has recorded its stop length, and the
+// sequence ends where the last of them finished
 int read_counters(tutor_gpt2* e, int* len, int* stop_len) {
-  CUDA_TRY(cudaMemcpyAsync(e->h_counters, e->counters, 2 * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+  CUDA_TRY(cudaMemcpyAsync(e->h_counters, e->counters, 2 * tutor_gpt2::MAX_LANES * sizeof(int), cudaMemcpyDeviceToHost,
+                           e->stream));
   CUDA_TRY(cudaStreamSynchronize(e->stream));
   *len = e->h_counters[0];
-  *stop_len = e->h_counters[1];
+  int stop = 0;
+  for (int i = 0; i < e->nlanes; ++i) {
+    if (e->h_counters[2 * i + 1] == 0) { stop = 0; break; }
+    if (e->h_counters[2 * i + 1] > stop) stop = e->h_counters[2 * i + 1];
+  }
+  *stop_len = stop;
   return TUTOR_OK;
 }
 
@@ -336,9 +383,17 @@ int tutor_gpt2_create(const tutor_gpt2_config* cfg, int device, tutor_gpt2_t** o
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) e->num_sms = prop.multiProcessorCount;
   }
-  if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaMalloc(&e->counters, 2 * sizeof(int)) != cudaSuccess ||
-      cudaMallocHost(&e->h_counters, 2 * sizeof(int)) != cudaSuccess) {
+  if (const char* nl = getenv("TUTOR_LANES")) e->cfg_lanes = atoi(nl);
+  if (e->cfg_lanes < 1) e->cfg_lanes = 1;
+  if (e->cfg_lanes > tutor_gpt2::MAX_LANES) e->cfg_lanes = tutor_gpt2::MAX_LANES;
+  bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess;
+  e->lane_stream[0] = e->stream;
+  for (int i = 1; i < tutor_gpt2::MAX_LANES && ok; ++i)
+    ok = cudaStreamCreateWithFlags(&e->lane_stream[i], cudaStreamNonBlocking) == cudaSuccess &&
+         cudaEventCreateWithFlags(&e->ev_join[i], cudaEventDisableTiming) == cudaSuccess;
+  ok = ok && cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming) == cudaSuccess;
+  if (!ok || cudaMalloc(&e->counters, 2 * tutor_gpt2::MAX_LANES * sizeof(int)) != cudaSuccess ||
+      cudaMallocHost(&e->h_counters, 2 * tutor_gpt2::MAX_LANES * sizeof(int)) != cudaSuccess) {
     int rc = tutor_cuda_fail(cudaGetLastError(), "gpt2_create", __FILE__, __LINE__);
     delete e;
     return rc;
@@ -362,6 +417,11 @@ void tutor_gpt2_destroy(tutor_gpt2_t* e) {
   dev_free(e->xn_last); dev_free(e->ids); dev_free(e->counters); dev_free(e->seen); dev_free(e->finished);
   dev_free(e->lm_scratch); dev_free(e->partial);
   if (e->h_counters) cudaFreeHost(e->h_counters);
+  for (int i = 1; i < tutor_gpt2::MAX_LANES; ++i) {
+    if (e->lane_stream[i]) cudaStreamDestroy(e->lane_stream[i]);
+    if (e->ev_join[i]) cudaEventDestroy(e->ev_join[i]);
+  }
+  if (e->ev_fork) cudaEventDestroy(e->ev_fork);
   cudaStreamDestroy(e->stream);
   delete e;
 }

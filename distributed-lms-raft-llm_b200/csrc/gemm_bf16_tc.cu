@@ -24,6 +24,17 @@ constexpr int BM = 128, BK = 64, UMMA_K = 16;
 constexpr int NTHREADS = 192;
 enum { EPI_ROWMAJOR = 0, EPI_SWAPPED = 1, EPI_ARGMAX = 2, EPI_PARTIAL = 3 };
 
+// Phase timestamps of CTA (0,0,0) for tools/microbench.cu (compiled in only with -DTUTOR_TRACE)
+#ifdef TUTOR_TRACE
+__device__ long long g_gemm_trace[8];
+#define TRACE(i)                                                              \
+  do {                                                                        \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) g_gemm_trace[i] = clock64(); \
+  } while (0)
+#else
+#define TRACE(i)
+#endif
+
 struct ArgmaxArgs {
   const uint32_t* seen;  // [B][seen_words]
   int seen_words;
@@ -72,6 +83,13 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
           smem_u32(dst)),
       "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // writes performed before the CTA may exit
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -193,6 +211,7 @@ __device__ __forceinline__ void store_run32(const GemmEpilogue& e, int m, int n0
 template <int BN, int EPI>
 __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                       const __grid_constant__ CUtensorMap tmB,
+                                                                      const __grid_constant__ CUtensorMap tmC,
                                                                       int rowsA, int rowsB, int K, GemmEpilogue epi,
                                                                       ArgmaxArgs am) {
   using L = SmemLayout<BN>;
@@ -209,6 +228,7 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
   // split-K: blockIdx.z owns k-blocks [kb0, kb0 + nk); gridDim.z == 1 for the unsplit flavours
   const int nk = (K / BK) / (int)gridDim.z;
   const int kb0 = (int)blockIdx.z * nk;
+  if (threadIdx.x == 0) TRACE(0);
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
@@ -228,6 +248,7 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) TRACE(1);
 
   pdl_launch_dependents();
   if (warp == 0) {
@@ -244,6 +265,7 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
       pdl_wait();
       for (int kb = 0; kb < pre; ++kb)
         tma_load_2d(tiles + kb * L::STAGE_BYTES + L::A_BYTES, &tmB, &full_bar[kb], (kb0 + kb) * BK, b_row0);
+      TRACE(2);
       for (int kb = pre; kb < nk; ++kb) {
         const int s = kb % L::STAGES;
         const uint32_t ph = (kb / L::STAGES) & 1;
@@ -263,6 +285,7 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
         const uint32_t ph = (kb / L::STAGES) & 1;
         mbar_wait(&full_bar[s], ph, 1);
         tc_fence_after();
+        if (kb == 0) TRACE(3);
         const uint32_t sa = smem_u32(tiles + s * L::STAGE_BYTES);
         const uint32_t sb = sa + L::A_BYTES;
 #pragma unroll
@@ -274,6 +297,7 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
         tc_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
       }
       tc_commit(tmem_full_bar);    // accumulator complete
+      TRACE(4);
     }
   } else {
     // ===== epilogue: 4 warps, each owns the 32 TMEM lanes of its quadrant =====
@@ -281,6 +305,7 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
     const int row = a_row0 + quad * 32 + lane;  // index along A's rows
     mbar_wait(tmem_full_bar, 0, 2);
     tc_fence_after();
+    if (threadIdx.x == 64) TRACE(5);
     pdl_wait();  // outputs may overwrite buffers the predecessor kernel still reads (already satisfied by now)
     const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16);
     if (EPI == EPI_ARGMAX) {
@@ -332,15 +357,13 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
         tc_ld32(taddr + c0, v);  // warp-collective: executed by all lanes even for out-of-range rows
         if (EPI == EPI_ROWMAJOR) {
           if (row < rowsA && b_row0 + c0 < rowsB) store_run32(epi, row, b_row0 + c0, rowsB, v);
-        } else if (EPI == EPI_PARTIAL) {  // raw fp32 partial sums [z][m][n] for the fused reduce kernels
-          if (row < rowsA) {
-            float* dst = epi.out_f32 + (size_t)blockIdx.z * rowsB * rowsA + row;
+        } else if (EPI == EPI_PARTIAL) {
+          // raw fp32 partial sums: staged [batch][128 n] in the (now idle) pipeline smem, then ONE bulk tensor
+          // store per CTA - 64 scattered STG per thread cost ~4000 cycles here, the TMA store a few hundred
+          float* stage = reinterpret_cast<float*>(tiles);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-              const int m = b_row0 + c0 + i;
-              if (c0 + i < BN && m < rowsB) dst[(size_t)m * rowsA] = v[i];
-            }
-          }
+          for (int i = 0; i < 32; ++i)
+            if (c0 + i < BN) stage[(c0 + i) * BM + quad * 32 + lane] = v[i];
         } else {  // EPI_SWAPPED: lane = output column n, TMEM column = batch row m
           if (row < rowsA) {
 #pragma unroll
@@ -351,11 +374,18 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
           }
         }
       }
+      if (EPI == EPI_PARTIAL) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> async proxy
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (threadIdx.x == 64) tma_store_3d(&tmC, tiles, a_row0, b_row0, (int)blockIdx.z);  // OOB rows/cols clipped
+      }
     }
   }
 
+  if (threadIdx.x == 64) TRACE(6);
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) TRACE(7);
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
   }
@@ -401,6 +431,24 @@ int make_map(CUtensorMap* map, const bf16* ptr, int rows, int K, int box_rows) {
   return TUTOR_OK;
 }
 
+// fp32 partial tensor [ks][M][N] for the EPI_PARTIAL bulk store; box = [1][box_m][128], no swizzle
+int make_map_out(CUtensorMap* map, float* ptr, int N, int M, int ks, int box_m) {
+  TRY(get_encoder());
+  ARG_CHECK((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && N % 4 == 0, "gemm_bf16: partial buffer misaligned");
+  cuuint64_t dims[3] = {(cuuint64_t)N, (cuuint64_t)M, (cuuint64_t)ks};
+  cuuint64_t strides[2] = {(cuuint64_t)N * 4, (cuuint64_t)M * N * 4};
+  cuuint32_t box[3] = {(cuuint32_t)BM, (cuuint32_t)box_m, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, ptr, dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    tutor_set_error("cuTensorMapEncodeTiled (partials) failed (%d) N=%d M=%d ks=%d", (int)r, N, M, ks);
+    return TUTOR_ERR_CUDA;
+  }
+  return TUTOR_OK;
+}
+
 template <int BN, int EPI>
 int launch(const bf16* A, int rowsA, const bf16* B, int rowsB, int K, const GemmEpilogue& epi, const ArgmaxArgs& am,
            cudaStream_t st, int ks = 1) {
@@ -411,12 +459,14 @@ int launch(const bf16* A, int rowsA, const bf16* B, int rowsB, int K, const Gemm
                                   L::TOTAL));
     attr_done = true;
   }
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, tc;
   TRY(make_map(&ta, A, rowsA, K, BM));
   TRY(make_map(&tb, B, rowsB, K, BN));
+  if (EPI == EPI_PARTIAL) TRY(make_map_out(&tc, epi.out_f32, rowsA, rowsB, ks, BN));
+  else tc = ta;  // unused
   dim3 grid(ceil_div(rowsA, BM), ceil_div(rowsB, BN), ks);
-  CUDA_TRY(tutor_launch(gemm_bf16_tcgen05_kernel<BN, EPI>, grid, dim3(NTHREADS), (size_t)L::TOTAL, st, ta, tb, rowsA, rowsB,
-                        K, epi, am));
+  CUDA_TRY(tutor_launch(gemm_bf16_tcgen05_kernel<BN, EPI>, grid, dim3(NTHREADS), (size_t)L::TOTAL, st, ta, tb, tc, rowsA,
+                        rowsB, K, epi, am));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }
@@ -457,7 +507,8 @@ int k_gemm_bf16_splitk(const bf16* X, const bf16* W, int M, int N, int K, int ks
 int k_pick_splitk(int N, int K, int num_sms) {
   const int tiles = ceil_div(N, BM), nk = K / BK;
   int best = 1;
-  for (int ks = 1; ks <= nk && ks <= 32; ++ks)
+  // capped at 12: beyond that the fp32 partials (ks*M*N*4 B written, then read) outweigh the shorter weight stream
+  for (int ks = 1; ks <= nk && ks <= 12; ++ks)
     if (nk % ks == 0 && tiles * ks <= num_sms) best = ks;
   return best;
 }
