@@ -42,7 +42,8 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
                                                           OT* __restrict__ out, int H, int Smax,
                                                           const int* __restrict__ len_dev, int len_host,
                                                           const float* __restrict__ qkv_partial, int ks,
-                                                          const float* __restrict__ qkv_bias, int B) {
+                                                          const float* __restrict__ qkv_bias, int B,
+                                                          float* split_scratch, int* split_counters) {
   constexpr int EPL = Vec16<KT>::N;  // elements per lane
   constexpr int LPR = 64 / EPL;      // lanes per key row
   constexpr int KPW = 32 / LPR;      // keys per warp-wide load
@@ -50,7 +51,10 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
   constexpr int UNR = 4;
   pdl_launch_dependents();
   pdl_wait();
-  const int h = blockIdx.x, b = blockIdx.y;
+  // gridDim.z > 1: the key range is cut into gridDim.z splits so that B*H*splits CTAs spread evenly over the SMs
+  // (768 CTAs on 148 SMs leave some SMs with 6 and some with 5: a 14 % tail); the last CTA to finish a (b,h)
+  // merges the split states in split order, so the result does not depend on which one that is.
+  const int h = blockIdx.x, b = blockIdx.y, z = blockIdx.z, nsplit = gridDim.z;
   const int len = len_dev ? *len_dev : len_host;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = warp * KPW + lane / LPR;  // this lane's group
@@ -68,12 +72,12 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
       const int n = which * d + h * 64 + i;
       float acc = qkv_bias[n];
 #pragma unroll 8
-      for (int z = 0; z < ks; ++z) acc += qkv_partial[((size_t)z * B + b) * (3 * d) + n];
+      for (int zz = 0; zz < ks; ++zz) acc += qkv_partial[((size_t)zz * B + b) * (3 * d) + n];
       if (which == 0) {
         s_new[0][i] = acc;
       } else {
         const KT st = from_f32<KT>(acc);
-        (which == 1 ? kc : vc)[base + (size_t)(len - 1) * 64 + i] = st;
+        if (z == 0) (which == 1 ? kc : vc)[base + (size_t)(len - 1) * 64 + i] = st;  // one split appends the row
         s_new[which][i] = to_f32(st);
       }
     }
@@ -90,9 +94,12 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
   for (int i = 0; i < EPL; ++i) o[i] = 0.f;
 
   // FUSED: the row this CTA just appended (position len-1) is taken from shared memory after the loop
-  const int nkeys = FUSED ? len - 1 : len;
+  const int nk_all = FUSED ? len - 1 : len;
+  const int per = (nk_all + nsplit - 1) / nsplit;
+  const int kbeg = z * per;
+  const int nkeys = min(nk_all, kbeg + per);  // this split covers keys [kbeg, nkeys)
   // trip count is uniform per warp (the shuffles below need every lane); groups past the end are masked
-  for (int jw = warp * KPW; jw < nkeys; jw += NG * UNR) {
+  for (int jw = kbeg + warp * KPW; jw < nkeys; jw += NG * UNR) {
     const int j0 = jw + lane / LPR;
     float kf[UNR][EPL], s[UNR];
 #pragma unroll
@@ -134,7 +141,7 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
     m = mn;
   }
 
-  if (FUSED) {  // the current token's own key/value, folded into group 0's running softmax
+  if (FUSED && z == nsplit - 1) {  // the current token's own key/value, folded into group 0 of the last split
     float d = 0.f;
 #pragma unroll
     for (int i = 0; i < EPL; ++i) d = fmaf(qv[i], s_new[1][e0 + i], d);
@@ -166,7 +173,229 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
       num = fmaf(w, sm_o[s2][threadIdx.x], num);
       den = fmaf(w, sm_l[s2], den);
     }
-    out[((size_t)b * H + h) * 64 + threadIdx.x] = from_f32<OT>(num / den);
+    if (nsplit == 1) {
+      out[((size_t)b * H + h) * 64 + threadIdx.x] = from_f32<OT>(num / den);
+    } else {  // publish this split's state: [max, denominator, 64 numerators]
+      float* st = split_scratch + (((size_t)b * H + h) * nsplit + z) * 66;
+      if (threadIdx.x == 0) { st[0] = M; st[1] = den; }
+      st[2 + threadIdx.x] = num;
+      __threadfence();
+    }
+  }
+  if (nsplit > 1) {
+    __shared__ int is_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const int done = atomicAdd(&split_counters[b * H + h], 1);
+      is_last = (done == nsplit - 1);
+      if (is_last) split_counters[b * H + h] = 0;  // ready for the next launch
+    }
+    __syncthreads();
+    if (is_last && threadIdx.x < 64) {
+      __threadfence();
+      const float* st = split_scratch + ((size_t)b * H + h) * nsplit * 66;
+      float M = -CUDART_INF_F;
+      for (int s2 = 0; s2 < nsplit; ++s2) M = fmaxf(M, __ldcg(st + s2 * 66));
+      float num = 0.f, den = 0.f;
+      for (int s2 = 0; s2 < nsplit; ++s2) {  // fixed split order: deterministic
+        const float ms = __ldcg(st + s2 * 66);
+        const float w = (ms == -CUDART_INF_F) ? 0.f : exp_sel<FAST>(ms - M);
+        num = fmaf(w, __ldcg(st + s2 * 66 + 2 + threadIdx.x), num);
+        den = fmaf(w, __ldcg(st + s2 * 66 + 1), den);
+      }
+      out[((size_t)b * H + h) * 64 + threadIdx.x] = from_f32<OT>(num / den);
+    }
+  }
+}
+
+// ------------------------------------------------------------------- decode, bulk-copy pipelined (bf16)
+// Same math and the same 16 independent lane-group softmax states as attn_decode_kernel, but the KV stream is
+// decoupled from the arithmetic: a producer warp moves 64-key chunks (8 KB of K + 8 KB of V, contiguous in the
+// [S][64] cache) into a two-stage shared-memory ring with cp.async.bulk (UBLKCP) signalled through mbarriers,
+// and the four consumer warps read 16-byte vectors from shared memory.  The producer starts before the
+// programmatic-launch wait: cache rows [0, len-1) were written by earlier steps, so they stream in while the
+// preceding c_attn GEMM is still finishing.  grid (H, B), 160 threads, 32 KB smem -> one wave at B*H = 768.
+constexpr int DK_THREADS = 160;
+
+__device__ __forceinline__ uint32_t dk_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ bool dk_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(dk_smem(bar)), "r"(parity) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void dk_wait(uint64_t* bar, uint32_t parity) {
+  if (dk_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!dk_try_wait(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) {  // a protocol bug must abort the launch, not hang the GPU
+      printf("tutor_b200 attn_decode: mbarrier wait timed out (block %d,%d)\n", blockIdx.x, blockIdx.y);
+      __trap();
+    }
+  }
+}
+
+// DK_CHUNK keys per stage, DK_STAGES stages; MATH=false (microbench only) drains the ring without the arithmetic
+template <bool FUSED, int DK_CHUNK, int DK_STAGES, bool MATH>
+__global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf16* __restrict__ q, bf16* kc, bf16* vc,
+                                                                    bf16* __restrict__ out, int H, int Smax,
+                                                                    const int* __restrict__ len_dev, int len_host,
+                                                                    const float* __restrict__ qkv_partial, int ks,
+                                                                    const float* __restrict__ qkv_bias, int B) {
+  constexpr int EPL = 8, LPR = 8, KPW = 4, NG = 16, UNR = DK_CHUNK / NG;
+  __shared__ __align__(128) bf16 sK[DK_STAGES][DK_CHUNK * 64];
+  __shared__ __align__(128) bf16 sV[DK_STAGES][DK_CHUNK * 64];
+  __shared__ __align__(8) uint64_t full_bar[DK_STAGES], empty_bar[DK_STAGES];
+  __shared__ float s_new[3][64];
+  __shared__ float sm_m[NG], sm_l[NG], sm_o[NG][64];
+  const int h = blockIdx.x, b = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int len = len_dev ? *len_dev : len_host;  // written by a kernel that finished long before this launch
+  const size_t base = ((size_t)b * H + h) * Smax * 64;
+  const int nkeys = FUSED ? len - 1 : len;
+  const int nchunks = (nkeys + DK_CHUNK - 1) / DK_CHUNK;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < DK_STAGES; ++s) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dk_smem(&full_bar[s])), "r"(1));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dk_smem(&empty_bar[s])), "r"(4));
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  pdl_launch_dependents();
+
+  if (warp == 4) {
+    // ===== producer: one lane streams the cache rows of this (b,h) =====
+    if (lane == 0) {
+      for (int c = 0; c < nchunks; ++c) {
+        const int s = c % DK_STAGES;
+        const uint32_t ph = (c / DK_STAGES) & 1;
+        dk_wait(&empty_bar[s], ph ^ 1);
+        const int rows = min(DK_CHUNK, nkeys - c * DK_CHUNK);
+        const uint32_t bytes = (uint32_t)rows * 128;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dk_smem(&full_bar[s])),
+                     "r"(2 * bytes) : "memory");
+        const size_t off = base + (size_t)c * DK_CHUNK * 64;
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         dk_smem(&sK[s][0])), "l"(kc + off), "r"(bytes), "r"(dk_smem(&full_bar[s])) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         dk_smem(&sV[s][0])), "l"(vc + off), "r"(bytes), "r"(dk_smem(&full_bar[s])) : "memory");
+      }
+    }
+  } else {
+    // ===== consumers =====
+    pdl_wait();  // q (or the c_attn partials) come from the preceding kernel
+    const int g = warp * KPW + lane / LPR;
+    const int e0 = (lane % LPR) * EPL;
+    float qv[EPL];
+    if (FUSED) {
+      const int d = H * 64;
+      for (int e = threadIdx.x; e < 192; e += 128) {
+        const int which = e >> 6, i = e & 63;
+        const int n = which * d + h * 64 + i;
+        float acc = qkv_bias[n];
+#pragma unroll 8
+        for (int zz = 0; zz < ks; ++zz) acc += qkv_partial[((size_t)zz * B + b) * (3 * d) + n];
+        if (which == 0) {
+          s_new[0][i] = acc;
+        } else {
+          const bf16 st = __float2bfloat16_rn(acc);
+          (which == 1 ? kc : vc)[base + (size_t)(len - 1) * 64 + i] = st;  // cache append (no torch.cat)
+          s_new[which][i] = __bfloat162float(st);
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // consumer warps only
+#pragma unroll
+      for (int i = 0; i < EPL; ++i) qv[i] = s_new[0][e0 + i] * 0.125f;
+    } else {
+      const bf16* qp = q + ((size_t)b * H + h) * 64 + e0;
+#pragma unroll
+      for (int i = 0; i < EPL; ++i) qv[i] = __bfloat162float(qp[i]) * 0.125f;
+    }
+    float m = -CUDART_INF_F, l = 0.f, o[EPL];
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) o[i] = 0.f;
+
+    for (int c = 0; c < nchunks; ++c) {
+      const int s = c % DK_STAGES;
+      dk_wait(&full_bar[s], (c / DK_STAGES) & 1);
+      const int valid_rows = min(DK_CHUNK, nkeys - c * DK_CHUNK);
+      float kf[UNR][EPL], vf[UNR][EPL], sc[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        const int kk = u * NG + g;
+        const int row = kk < valid_rows ? kk : 0;  // rows past the end are masked; row 0 of a chunk always exists
+        unpack_bf16x8(*reinterpret_cast<const uint4*>(&sK[s][row * 64 + e0]), kf[u]);
+        unpack_bf16x8(*reinterpret_cast<const uint4*>(&sV[s][row * 64 + e0]), vf[u]);
+      }
+      __syncwarp();
+      if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(dk_smem(&empty_bar[s])) : "memory");
+      if (!MATH) {
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) o[u % EPL] += kf[u][0] + vf[u][1];
+        continue;
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        float d = 0.f;
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) d = fmaf(qv[i], kf[u][i], d);
+#pragma unroll
+        for (int off = LPR / 2; off > 0; off >>= 1) d += __shfl_xor_sync(0xffffffffu, d, off);
+        sc[u] = (u * NG + g < valid_rows) ? d : -CUDART_INF_F;
+      }
+      float mn = m;
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) mn = fmaxf(mn, sc[u]);
+      if (mn == -CUDART_INF_F) continue;
+      const float corr = __expf(m - mn);
+      l *= corr;
+#pragma unroll
+      for (int i = 0; i < EPL; ++i) o[i] *= corr;
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        const float p = __expf(sc[u] - mn);
+        l += p;
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) o[i] = fmaf(p, vf[u][i], o[i]);
+      }
+      m = mn;
+    }
+    if (FUSED) {  // the current token's own key/value, folded into group 0
+      float d = 0.f;
+#pragma unroll
+      for (int i = 0; i < EPL; ++i) d = fmaf(qv[i], s_new[1][e0 + i], d);
+#pragma unroll
+      for (int off = LPR / 2; off > 0; off >>= 1) d += __shfl_xor_sync(0xffffffffu, d, off);
+      if (g == 0) {
+        const float mn = fmaxf(m, d);
+        const float corr = __expf(m - mn), p = __expf(d - mn);
+        l = l * corr + p;
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) o[i] = fmaf(p, s_new[2][e0 + i], o[i] * corr);
+        m = mn;
+      }
+    }
+    if (lane % LPR == 0) { sm_m[g] = m; sm_l[g] = l; }
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) sm_o[g][e0 + i] = o[i];
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (threadIdx.x < 64) {
+      float M = -CUDART_INF_F;
+#pragma unroll
+      for (int s2 = 0; s2 < NG; ++s2) M = fmaxf(M, sm_m[s2]);
+      float num = 0.f, den = 0.f;
+#pragma unroll
+      for (int s2 = 0; s2 < NG; ++s2) {
+        const float w = (sm_m[s2] == -CUDART_INF_F) ? 0.f : __expf(sm_m[s2] - M);
+        num = fmaf(w, sm_o[s2][threadIdx.x], num);
+        den = fmaf(w, sm_l[s2], den);
+      }
+      out[((size_t)b * H + h) * 64 + threadIdx.x] = __float2bfloat16_rn(num / den);
+    }
   }
 }
 
@@ -420,6 +649,16 @@ __global__ void __launch_bounds__(128) attn_prefill_mma_kernel(const bf16* __res
 
 }  // namespace
 
+// number of key-range splits: enough CTAs for ~8 per SM, at least 64 keys per split
+int k_attn_decode_splits(int B, int H, int len_hint, int num_sms) {
+  // measured on B200: at B*H = 768 one CTA per (b,h) beats 2 or 4 splits (0.730 vs 0.859 / 0.867 ms per decode
+  // forward); splitting only pays when there are fewer CTAs than SMs
+  int n = 1;
+  while (n < 8 && B * H * n < num_sms && len_hint / (2 * n) >= 64) n *= 2;
+  return n;
+}
+size_t k_attn_decode_scratch_bytes(int B, int H) { return (size_t)B * H * (8 * 66 * sizeof(float) + sizeof(int)); }
+
 int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int kv_dtype, void* out, int out_dtype,
                   int B, int H, int Smax, const int* len_dev, int len_host, cudaStream_t st) {
   if (B == 0) return TUTOR_OK;
@@ -427,10 +666,11 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
   dim3 grid(H, B), block(128);
   if (q_dtype == DT_F32 && kv_dtype == DT_F32 && out_dtype == DT_F32)
     attn_decode_kernel<float, float, float, false, false><<<grid, block, 0, st>>>(
-        (const float*)q, (float*)k, (float*)v, (float*)out, H, Smax, len_dev, len_host, nullptr, 0, nullptr, B);
+        (const float*)q, (float*)k, (float*)v, (float*)out, H, Smax, len_dev, len_host, nullptr, 0, nullptr, B, nullptr,
+        nullptr);
   else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16)
-    attn_decode_kernel<bf16, bf16, bf16, true, false><<<grid, block, 0, st>>>(
-        (const bf16*)q, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, nullptr, 0, nullptr, B);
+    attn_decode_tma_kernel<false, 64, 2, true><<<grid, DK_THREADS, 0, st>>>((const bf16*)q, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax,
+                                                               len_dev, len_host, nullptr, 0, nullptr, B);
   else {
     tutor_set_error("attn_decode: unsupported dtype combination q=%d kv=%d out=%d", q_dtype, kv_dtype, out_dtype);
     return TUTOR_ERR_ARG;
@@ -441,14 +681,23 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
 
 int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias, void* k, void* v, int kv_dtype,
                         void* out, int out_dtype, int B, int H, int Smax, const int* len_dev, int len_host,
-                        cudaStream_t st) {
+                        int nsplit, void* split_scratch, cudaStream_t st) {
   if (B == 0) return TUTOR_OK;
   ARG_CHECK(kv_dtype == DT_BF16 && out_dtype == DT_BF16, "attn_decode_fused: bf16 cache and output only");
   ARG_CHECK(qkv_partial && qkv_bias && ks >= 1, "attn_decode_fused: bad partials");
   ARG_CHECK(len_dev || (len_host >= 1 && len_host <= Smax), "attn_decode_fused: len %d outside [1,%d]", len_host, Smax);
-  CUDA_TRY(tutor_launch(attn_decode_kernel<bf16, bf16, bf16, true, true>, dim3(H, B), dim3(128), 0, st,
+  ARG_CHECK(nsplit >= 1 && nsplit <= 8 && (nsplit == 1 || split_scratch), "attn_decode_fused: bad split setup");
+  if (nsplit == 1) {
+    CUDA_TRY(tutor_launch(attn_decode_tma_kernel<true, 64, 2, true>, dim3(H, B), dim3(DK_THREADS), 0, st, (const bf16*)nullptr,
+                          (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B));
+    KERNEL_LAUNCHED();
+    return TUTOR_OK;
+  }
+  float* sc = reinterpret_cast<float*>(split_scratch);
+  int* counters = reinterpret_cast<int*>(sc + (size_t)B * H * 8 * 66);  // zeroed by the owner; self-resetting
+  CUDA_TRY(tutor_launch(attn_decode_kernel<bf16, bf16, bf16, true, true>, dim3(H, B, nsplit), dim3(128), 0, st,
                         (const bf16*)nullptr, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks,
-                        qkv_bias, B));
+                        qkv_bias, B, sc, counters));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }

@@ -45,6 +45,9 @@ struct tutor_gpt2 {
   int seen_words = 0;
   int* finished = nullptr;
   void* lm_scratch = nullptr;
+  void* attn_scratch = nullptr;  // split states + arrival counters of the decode attention, one slice per lane
+  size_t attn_scratch_lane_bytes = 0;
+  int attn_splits = 1;
   float* partial = nullptr;   // split-K partial sums of the decode GEMMs (bf16 mode), [ks][B][N] fp32, one slice per lane
   size_t partial_lane_elems = 0, lm_scratch_lane_bytes = 0;
   int num_sms = 148;
@@ -160,7 +163,8 @@ int forward_decode_fused(tutor_gpt2* e, int lane, int b0, int B) {
     void* vc = (uint8_t*)e->vcache(l) + kv_off;
     int ks = k_pick_splitk(3 * d, d, e->num_sms);
     TRY(k_gemm_bf16_splitk(xn, (const bf16*)w.qkv.w, B, 3 * d, d, ks, partial, st));
-    TRY(k_attn_decode_fused(partial, ks, w.qkv.b, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0, st));
+    TRY(k_attn_decode_fused(partial, ks, w.qkv.b, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
+                            e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, st));
     ks = k_pick_splitk(d, d, e->num_sms);
     TRY(k_gemm_bf16_splitk(att, (const bf16*)w.proj.w, B, d, d, ks, partial, st));
     TRY(k_reduce_bias_residual_ln(partial, ks, B, d, w.proj.b, x, w.ln2_g, w.ln2_b, eps, nullptr, xn, st));
@@ -213,7 +217,10 @@ int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
     // rows past the current length are read (masked) by the attention kernels: they must hold finite values
     CUDA_TRY(cudaMemsetAsync(e->kv, 0, bytes, e->stream));
     dev_free(e->ids); dev_free(e->seen); dev_free(e->finished); dev_free(e->lm_scratch); dev_free(e->xn_last);
-    dev_free(e->partial);
+    dev_free(e->partial); dev_free(e->attn_scratch);
+    e->attn_scratch_lane_bytes = round_up(k_attn_decode_scratch_bytes(nb, e->H), 256);
+    TRY(dev_alloc(&e->attn_scratch, tutor_gpt2::MAX_LANES * e->attn_scratch_lane_bytes));
+    CUDA_TRY(cudaMemsetAsync(e->attn_scratch, 0, tutor_gpt2::MAX_LANES * e->attn_scratch_lane_bytes, e->stream));
     if (e->dt == DT_BF16) {  // largest [ks][B][N] any decode GEMM of this model writes
       const int d = e->d;
       const int shapes[4][2] = {{3 * d, d}, {d, d}, {4 * d, d}, {d, 4 * d}};
@@ -269,6 +276,10 @@ int start_generation(tutor_gpt2* e, int B, int T, int total, float penalty, int 
   if (penalty != e->cur_penalty || eos != e->cur_eos || pad != e->cur_pad || B != e->cur_B || nl != e->nlanes)
     drop_graph(e);
   e->nlanes = nl;
+  int splits = k_attn_decode_splits((B + nl - 1) / nl, e->H, (T + total) / 2, e->num_sms);
+  if (const char* sv = getenv("TUTOR_ATTN_SPLITS")) splits = atoi(sv) < 1 ? 1 : (atoi(sv) > 8 ? 8 : atoi(sv));
+  if (splits != e->attn_splits) drop_graph(e);
+  e->attn_splits = splits;
   e->cur_B = B; e->cur_T = T; e->cur_total = total; e->cur_penalty = penalty; e->cur_eos = eos; e->cur_pad = pad;
   cudaStream_t st = e->stream;
   e->h_counters[0] = T; e->h_counters[1] = 0;
@@ -415,7 +426,7 @@ void tutor_gpt2_destroy(tutor_gpt2_t* e) {
   }
   dev_free(e->kv); dev_free(e->x); dev_free(e->xn); dev_free(e->q); dev_free(e->att); dev_free(e->hbuf);
   dev_free(e->xn_last); dev_free(e->ids); dev_free(e->counters); dev_free(e->seen); dev_free(e->finished);
-  dev_free(e->lm_scratch); dev_free(e->partial);
+  dev_free(e->lm_scratch); dev_free(e->partial); dev_free(e->attn_scratch);
   if (e->h_counters) cudaFreeHost(e->h_counters);
   for (int i = 1; i < tutor_gpt2::MAX_LANES; ++i) {
     if (e->lane_stream[i]) cudaStreamDestroy(e->lane_stream[i]);

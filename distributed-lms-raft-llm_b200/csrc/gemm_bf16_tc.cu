@@ -89,7 +89,8 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void*
                "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
                : "memory");
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // writes performed before the CTA may exit
+  // the CTA only has to outlive the read of its shared memory; the global writes are complete at grid end
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }

@@ -182,3 +182,16 @@ def test_fused_decode_path_matches_unfused(pkg, tiny_hf, monkeypatch):
     a = fused.generate(ids, max_new_tokens=24, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
     b = plain.generate(ids, max_new_tokens=24, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
     assert (a == b).float().mean().item() > 0.9
+    # key-range splits of the decode attention (last-arriving CTA merges): same numbers as one CTA per (b,h)
+    long_ids = rp.gpt2_prompt_ids(3, 150, seed=12, vocab=1000)
+    outs = []
+    for splits in ("1", "4"):
+        monkeypatch.setenv("TUTOR_ATTN_SPLITS", splits)
+        eng = pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="bf16")
+        eng.prefill(long_ids, max_new_tokens=40, eos_token_id=999, pad_token_id=999)
+        eng.step(20)
+        outs.append((eng.last_logits().float().cpu(), eng.read_ids()))
+    monkeypatch.delenv("TUTOR_ATTN_SPLITS")
+    err = ((outs[0][0] - outs[1][0]).abs().max() / outs[0][0].abs().max()).item()
+    print(f"attention splits 1 vs 4: relative logit difference {err:.3e}")
+    assert err < 5e-3 and (outs[0][1] == outs[1][1]).float().mean().item() > 0.95

@@ -9,6 +9,7 @@
 #include "kernels.h"
 #ifdef TUTOR_TRACE
 #include "gemm_bf16_tc.cu"  // traced copy of the GEMM overrides the library's
+#include "attention.cu"     // direct access to the decode-attention template variants
 #endif
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA %s at %d\n", cudaGetErrorString(e_), __LINE__); exit(1); } } while (0)
@@ -32,6 +33,36 @@ __global__ void k_syncs(int* out, int n) {
   int v = threadIdx.x;
   for (int k = 0; k < n; ++k) { if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v; __syncthreads(); v += sm[k & 7]; __syncthreads(); }
   out[threadIdx.x + blockIdx.x * blockDim.x] = v;
+}
+
+// pure streaming reads shaped like the decode attention: nstreams contiguous regions per CTA, 16 B per thread per load
+__global__ void k_stream(const uint4* __restrict__ base, size_t region_vec, int nstreams, int nvec, uint4* sink) {
+  const uint4* p = base + (size_t)blockIdx.x * nstreams * region_vec;
+  uint4 acc = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x; i < nvec; i += blockDim.x * 4) {
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+      if (s >= nstreams) break;
+      const uint4* q = p + (size_t)s * region_vec;
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { int j = i + u * blockDim.x; v[u] = j < nvec ? q[j] : make_uint4(0, 0, 0, 0); }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { acc.x ^= v[u].x; acc.y ^= v[u].y; acc.z ^= v[u].z; acc.w ^= v[u].w; }
+    }
+  }
+  if (acc.x == 0x12345678u) sink[blockIdx.x] = acc;  // never true for our data; keeps the loads alive
+}
+__global__ void k_flat(const uint4* __restrict__ base, size_t nvec, uint4* sink) {
+  uint4 acc = make_uint4(0, 0, 0, 0);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x * 4) {
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { size_t j = i + (size_t)u * gridDim.x * blockDim.x; v[u] = j < nvec ? base[j] : make_uint4(0, 0, 0, 0); }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { acc.x ^= v[u].x; acc.y ^= v[u].y; acc.z ^= v[u].z; acc.w ^= v[u].w; }
+  }
+  if (acc.x == 0x12345678u) sink[blockIdx.x] = acc;
 }
 
 static float time_graph(cudaStream_t st, int chain, bool pdl, const std::function<void(int)>& launch_one) {
@@ -67,6 +98,42 @@ int main() {
   CK(cudaMemset(x, 0, (size_t)B * 4 * d * 2)); CK(cudaMemset(w, 0, (size_t)12 * 4 * d * d * 2));
   CK(cudaMemset(partial, 0, (size_t)32 * B * 4 * d * 4)); CK(cudaMemset(xf, 0, (size_t)B * d * 4));
   CK(cudaMemset(bias, 0, 4 * d * 4)); CK(cudaMemset(gam, 0, 4 * d * 4));
+  {  // streaming-read patterns, 12 rotating "layers" of 2 x 98 KB x 768 regions (1.8 GB, larger than L2)
+    const size_t region = 768 * 64 * 2 / 16;  // one (b,h) stream at Smax=768 in 16-byte vectors
+    const int used = 640 * 64 * 2 / 16;        // S = 640 rows actually read
+    uint4* big; CK(cudaMalloc(&big, (size_t)12 * 768 * 2 * region * 16)); CK(cudaMemset(big, 1, (size_t)12 * 768 * 2 * region * 16));
+    uint4* sink; CK(cudaMalloc(&sink, 4096 * 16));
+    const double mb = 768.0 * 2 * used * 16 / 1e6;
+    struct { const char* n; int threads, nstreams; } pats[] = {{"768 CTAs x 128 thr, K and V streams", 128, 2}, {"768 CTAs x 256 thr, K and V streams", 256, 2}};
+    for (auto& pt : pats) {
+      float t = time_graph(st, 48, false, [&](int i) { k_stream<<<768, pt.threads, 0, st>>>(big + (size_t)(i % 12) * 768 * 2 * region, region, pt.nstreams, used, sink); });
+      printf("stream %-40s %6.2f us  %7.1f GB/s\n", pt.n, t, mb / t * 1e-3 * 1e3);
+    }
+    float t = time_graph(st, 48, false, [&](int i) { k_stream<<<1536, 128, 0, st>>>(big + (size_t)(i % 12) * 768 * 2 * region, region, 1, used, sink); });
+    printf("stream %-40s %6.2f us  %7.1f GB/s\n", "1536 CTAs x 128 thr, one stream each", t, mb / t * 1e-3 * 1e3);
+    for (int ctas : {148 * 4, 148 * 8, 148 * 16}) {
+      t = time_graph(st, 48, false, [&](int i) { k_flat<<<ctas, 256, 0, st>>>(big + (size_t)(i % 12) * 768 * 2 * region, (size_t)768 * 2 * used, sink); });
+      printf("flat grid-stride read, %4d CTAs x 256 thr            %6.2f us  %7.1f GB/s\n", ctas, t, mb / t * 1e-3 * 1e3);
+    }
+#ifdef TUTOR_TRACE
+    {
+      bf16 *qq, *oo; CK(cudaMalloc(&qq, 64 * 768 * 2)); CK(cudaMalloc(&oo, 64 * 768 * 2)); CK(cudaMemset(qq, 0, 64 * 768 * 2));
+      const size_t layer = (size_t)768 * 2 * region * 8;  // bf16 elements per "layer" (K block then V block)
+      auto kp = [&](int i) { return (bf16*)big + (size_t)(i % 12) * layer; };
+      auto vp = [&](int i) { return (bf16*)big + (size_t)(i % 12) * layer + layer / 2; };
+#define ATT(NAME, ...)                                                                                              \
+      t = time_graph(st, 48, false, [&](int i) { __VA_ARGS__; });                                                    \
+      printf("attn %-42s %6.2f us  %7.2f TB/s\n", NAME, t, mb / t * 1e-3);
+      ATT("register kernel (128 thr)", (attn_decode_kernel<bf16, bf16, bf16, true, false><<<dim3(12, 64), 128, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, nullptr)));
+      ATT("ring chunk 64 x 2 stages", (attn_decode_tma_kernel<false, 64, 2, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64)));
+      ATT("ring chunk 64 x 2 stages, no math", (attn_decode_tma_kernel<false, 64, 2, false><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64)));
+      ATT("ring chunk 32 x 4 stages", (attn_decode_tma_kernel<false, 32, 4, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64)));
+      ATT("ring chunk 32 x 4 stages, no math", (attn_decode_tma_kernel<false, 32, 4, false><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64)));
+      ATT("ring chunk 16 x 8 stages", (attn_decode_tma_kernel<false, 16, 8, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64)));
+    }
+#endif
+    cudaFree(big); cudaFree(sink);
+  }
   for (int pdl = 0; pdl < 2; ++pdl) {
     printf("--- PDL %s\n", pdl ? "on" : "off");
     float t = time_graph(st, 96, pdl, [&](int) { CK(tutor_launch(k_empty, dim3(64), dim3(128), 0, st, cnt)); });
