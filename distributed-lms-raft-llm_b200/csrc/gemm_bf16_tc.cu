@@ -145,7 +145,8 @@ template <int BN> struct SmemLayout {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN >= 128) ? 4 : 6;
+  // sized so that two CTAs fit one SM (<= ~100 KB each): one CTA's epilogue overlaps the other's mainloop
+  static constexpr int STAGES = (BN >= 128) ? 3 : (BN >= 64 ? 4 : 5);
   static constexpr int TILE_BYTES = STAGES * STAGE_BYTES;
   static constexpr int BAR_BYTES = 256;
   static constexpr int TOTAL = TILE_BYTES + BAR_BYTES + 1024;  // +1024: manual 1 KB alignment of the tiles
@@ -310,9 +311,10 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
     pdl_wait();  // outputs may overwrite buffers the predecessor kernel still reads (already satisfied by now)
     const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16);
     if (EPI == EPI_ARGMAX) {
-      // per-tile argmax over the 128 vocabulary rows for every batch column
-      float* red_val = reinterpret_cast<float*>(tiles);  // pipeline smem is idle now: [4][BN] + [4][BN]
-      int* red_idx = reinterpret_cast<int*>(tiles + 4 * BN * sizeof(float));
+      // per-tile argmax over the 128 vocabulary rows for every batch column: penalised scores are transposed
+      // through the (now idle) pipeline smem as [column][128 rows]; then each warp reduces whole columns -
+      // 4 conflict-free loads + one 5-round shuffle arg-max per column instead of one per (row-quadrant, column)
+      float* stage = reinterpret_cast<float*>(tiles);
       const int wslot = warp - 2;
       for (int c0 = 0; c0 < BN; c0 += 32) {
         float v[32];
@@ -322,35 +324,35 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
           if (c0 + i >= BN) break;  // BN = 16: only half of the 32-column load is real
           const int b = b_row0 + c0 + i;
           float val = v[i];
-          int idx = row;
           if (b < am.B && am.penalty != 1.0f) {
             // 32 lanes = 32 consecutive vocabulary rows = one word of the seen-bitmap
             uint32_t w = am.seen[(size_t)b * am.seen_words + (row >> 5)];
             if ((w >> (row & 31)) & 1u) val = (val < 0.f) ? val * am.penalty : val / am.penalty;
           }
           if (row >= am.V) val = -CUDART_INF_F;
-#pragma unroll
-          for (int o = 16; o > 0; o >>= 1) {
-            float ov = __shfl_xor_sync(0xffffffffu, val, o);
-            int oi = __shfl_xor_sync(0xffffffffu, idx, o);
-            if (ov > val || (ov == val && oi < idx)) { val = ov; idx = oi; }
-          }
-          if (lane == 0) { red_val[wslot * BN + c0 + i] = val; red_idx[wslot * BN + c0 + i] = idx; }
+          stage[(c0 + i) * BM + quad * 32 + lane] = val;
         }
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
-      const int c = threadIdx.x - 64;
-      if (c < BN && b_row0 + c < am.B) {
-        float val = red_val[c];
-        int idx = red_idx[c];
+      for (int c = wslot; c < BN; c += 4) {
+        if (b_row0 + c >= am.B) break;
+        float val = stage[c * BM + lane];
+        int idx = lane;
 #pragma unroll
-        for (int w = 1; w < 4; ++w) {
-          float ov = red_val[w * BN + c];
-          int oi = red_idx[w * BN + c];
+        for (int r = 1; r < 4; ++r) {
+          const float ov = stage[c * BM + r * 32 + lane];
+          if (ov > val) { val = ov; idx = r * 32 + lane; }  // ascending rows: strict > keeps the lowest index
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const float ov = __shfl_xor_sync(0xffffffffu, val, o);
+          const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
           if (ov > val || (ov == val && oi < idx)) { val = ov; idx = oi; }
         }
-        am.part_val[(size_t)blockIdx.x * am.B + b_row0 + c] = val;
-        am.part_idx[(size_t)blockIdx.x * am.B + b_row0 + c] = idx;
+        if (lane == 0) {
+          am.part_val[(size_t)blockIdx.x * am.B + b_row0 + c] = val;
+          am.part_idx[(size_t)blockIdx.x * am.B + b_row0 + c] = a_row0 + idx;
+        }
       }
     } else {
       for (int c0 = 0; c0 < BN; c0 += 32) {
