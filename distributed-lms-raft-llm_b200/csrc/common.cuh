@@ -103,6 +103,27 @@ __device__ __forceinline__ float apply_act(float x, int act) {
   return x;
 }
 
+// bf16 throughput mode only: one-instruction tanh (MUFU.TANH, |err| ~ 5e-4) and a 7-term erf (Abramowitz-Stegun
+// 7.1.26, |err| < 1.5e-7); the results are rounded to bf16 (2^-9 relative) right after, so neither shows.
+// The accurate tanhf/erff above cost 30-40 instructions per element - more than the MMA time of a 128x128 tile.
+__device__ __forceinline__ float gelu_tanh_fast(float x) {
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.7978845608028654f * (x + 0.044715f * x * x * x)));
+  return 0.5f * x * (1.0f + t);
+}
+__device__ __forceinline__ float gelu_erf_fast(float x) {
+  const float z = fabsf(x) * 0.7071067811865476f;
+  const float t = __fdividef(1.0f, 1.0f + 0.3275911f * z);
+  const float poly = t * (0.254829592f + t * (-0.284496736f + t * (1.421413741f + t * (-1.453152027f + t * 1.061405429f))));
+  const float erf_abs = 1.0f - poly * __expf(-z * z);
+  return 0.5f * x * (1.0f + copysignf(erf_abs, x));
+}
+__device__ __forceinline__ float apply_act_fast(float x, int act) {
+  if (act == ACT_GELU_TANH) return gelu_tanh_fast(x);
+  if (act == ACT_GELU_ERF) return gelu_erf_fast(x);
+  return x;
+}
+
 // 8 packed bf16 (one 16-byte vector) -> 8 floats
 __device__ __forceinline__ void unpack_bf16x8(const uint4& v, float* f) {
   const uint32_t w[4] = {v.x, v.y, v.z, v.w};
@@ -146,9 +167,13 @@ struct GemmEpilogue {
   const int* pos_dev;  // if non-null: position = *pos_dev - 1 (decode step; T must be 1)
 };
 
+// everything after bias + activation: residual add and the store (plain or QKV scatter)
+__device__ __forceinline__ void epilogue_finish(const GemmEpilogue& e, int m, int n, float v);
 __device__ __forceinline__ void epilogue_store(const GemmEpilogue& e, int m, int n, float v) {
   if (e.bias) v += e.bias[n];
-  v = apply_act(v, e.act);
+  epilogue_finish(e, m, n, apply_act(v, e.act));
+}
+__device__ __forceinline__ void epilogue_finish(const GemmEpilogue& e, int m, int n, float v) {
   if (!e.qkv_mode) {
     size_t o = (size_t)m * e.ldo + n;
     if (e.residual) v += e.residual[o];

@@ -14,6 +14,7 @@
 #include <cuda.h>
 #include <math_constants.h>
 
+#include <cstdlib>
 #include <mutex>
 
 #include "kernels.h"
@@ -21,7 +22,8 @@
 namespace {
 
 constexpr int BM = 128, BK = 64, UMMA_K = 16;
-constexpr int NTHREADS = 192;
+constexpr int NTHREADS = 192;        // decode flavours: TMA warp, MMA warp, 4 epilogue warps
+constexpr int NTHREADS_WIDE = 320;   // row-major (prefill) flavour: 8 epilogue warps, two per TMEM lane quadrant
 enum { EPI_ROWMAJOR = 0, EPI_SWAPPED = 1, EPI_ARGMAX = 2, EPI_PARTIAL = 3 };
 
 // Phase timestamps of CTA (0,0,0) for tools/microbench.cu (compiled in only with -DTUTOR_TRACE)
@@ -146,7 +148,7 @@ template <int BN> struct SmemLayout {
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   // sized so that two CTAs fit one SM (<= ~100 KB each): one CTA's epilogue overlaps the other's mainloop
-  static constexpr int STAGES = (BN >= 128) ? 3 : (BN >= 64 ? 4 : 5);
+  static constexpr int STAGES = (BN >= 256) ? 2 : (BN >= 128) ? 3 : (BN >= 64 ? 4 : 5);
   static constexpr int TILE_BYTES = STAGES * STAGE_BYTES;
   static constexpr int BAR_BYTES = 256;
   static constexpr int TOTAL = TILE_BYTES + BAR_BYTES + 1024;  // +1024: manual 1 KB alignment of the tiles
@@ -167,7 +169,7 @@ __device__ __forceinline__ void store_run32(const GemmEpilogue& e, int m, int n0
   }
   if (e.act != ACT_NONE) {
 #pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = apply_act(v[i], e.act);
+    for (int i = 0; i < 32; ++i) v[i] = apply_act_fast(v[i], e.act);  // bf16 mode: see common.cuh
   }
   float* of = nullptr;
   bf16* ob = nullptr;
@@ -211,7 +213,7 @@ __device__ __forceinline__ void store_run32(const GemmEpilogue& e, int m, int n0
 }
 
 template <int BN, int EPI>
-__global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
+__global__ void __launch_bounds__(EPI == EPI_ROWMAJOR ? NTHREADS_WIDE : NTHREADS) gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                       const __grid_constant__ CUtensorMap tmB,
                                                                       const __grid_constant__ CUtensorMap tmC,
                                                                       int rowsA, int rowsB, int K, GemmEpilogue epi,
@@ -355,10 +357,16 @@ __global__ void __launch_bounds__(NTHREADS) gemm_bf16_tcgen05_kernel(const __gri
         }
       }
     } else {
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      // row-major flavour: warps 2-5 take the first half of the columns, warps 6-9 the second half of the same
+      // TMEM lanes (the epilogue, not the MMA, bounds a 128xBN tile: ~25 instructions per output element)
+      const int c_begin = (EPI == EPI_ROWMAJOR) ? ((warp - 2) >> 2) * (BN / 2) : 0;
+      const int c_end = (EPI == EPI_ROWMAJOR) ? c_begin + BN / 2 : BN;
+      for (int c0 = c_begin; c0 < c_end; c0 += 32) {
         float v[32];
         tc_ld32(taddr + c0, v);  // warp-collective: executed by all lanes even for out-of-range rows
         if (EPI == EPI_ROWMAJOR) {
+          // (a per-warp smem transpose for row-coalesced stores was tried and measured 2.4x slower than these
+          // per-thread 16-byte vector stores: 32 scalar row passes cost more than the uncoalesced sectors save)
           if (row < rowsA && b_row0 + c0 < rowsB) store_run32(epi, row, b_row0 + c0, rowsB, v);
         } else if (EPI == EPI_PARTIAL) {
           // raw fp32 partial sums: staged [batch][128 n] in the (now idle) pipeline smem, then ONE bulk tensor
@@ -468,7 +476,8 @@ int launch(const bf16* A, int rowsA, const bf16* B, int rowsB, int K, const Gemm
   if (EPI == EPI_PARTIAL) TRY(make_map_out(&tc, epi.out_f32, rowsA, rowsB, ks, BN));
   else tc = ta;  // unused
   dim3 grid(ceil_div(rowsA, BM), ceil_div(rowsB, BN), ks);
-  CUDA_TRY(tutor_launch(gemm_bf16_tcgen05_kernel<BN, EPI>, grid, dim3(NTHREADS), (size_t)L::TOTAL, st, ta, tb, tc, rowsA,
+  CUDA_TRY(tutor_launch(gemm_bf16_tcgen05_kernel<BN, EPI>, grid, dim3(EPI == EPI_ROWMAJOR ? NTHREADS_WIDE : NTHREADS),
+                        (size_t)L::TOTAL, st, ta, tb, tc, rowsA,
                         rowsB, K, epi, am));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
@@ -491,6 +500,10 @@ int k_gemm_bf16(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpi
   if (M == 0 || N == 0) return TUTOR_OK;
   ArgmaxArgs am{};
   if (M <= 128) return launch_swapped<EPI_SWAPPED>(W, N, A, M, K, epi, am, st);
+  // 128x256 tiles halve the operand bytes per FLOP of 128x128 ones (the 128x128 kernel measured L2-bandwidth
+  // bound: 32 KB of operands per 4 MMAs = 6.2 TB/s at 410 TFLOP/s); two 97 KB CTAs still share an SM
+  static const bool wide = getenv("TUTOR_GEMM_BN128") == nullptr;
+  if (wide && N >= 256) return launch<256, EPI_ROWMAJOR>(A, M, W, N, K, epi, am, st);
   return launch<128, EPI_ROWMAJOR>(A, M, W, N, K, epi, am, st);
 }
 

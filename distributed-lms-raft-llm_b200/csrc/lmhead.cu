@@ -72,7 +72,8 @@ __global__ void __launch_bounds__(256) lmhead_argmax_simt_kernel(const float* __
   }
 }
 
-// one warp per batch row scans the partials (independent loads in flight instead of one dependent chain)
+// 16 threads per batch row scan the partials (independent loads in flight), so that 64 rows are reduced and
+// book-kept in one pass of one 1024-thread CTA instead of two rows at a time per warp
 __global__ void __launch_bounds__(1024) argmax_finalize_kernel(const float* __restrict__ part_val,
                                                                const int* __restrict__ part_idx, int nparts, int B,
                                                                DecodeState ds) {
@@ -82,23 +83,26 @@ __global__ void __launch_bounds__(1024) argmax_finalize_kernel(const float* __re
   if (threadIdx.x == 0) all_finished = 1;
   __syncthreads();
   const int len = ds.plain_out ? 0 : *ds.len;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-  for (int b = warp; b < B; b += nwarps) {
+  const int sub = threadIdx.x & 15, grp = threadIdx.x >> 4, ngrp = blockDim.x >> 4;
+  for (int b0 = 0; b0 < B; b0 += ngrp) {  // uniform trip count: the shuffles below need whole warps
+    const int b = b0 + grp;
     float bv = -CUDART_INF_F;
     int bi = 0x7fffffff;
+    if (b < B) {
 #pragma unroll 4
-    for (int p = lane; p < nparts; p += 32) {
-      float v = part_val[(size_t)p * B + b];
-      int i = part_idx[(size_t)p * B + b];
-      if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; }
+      for (int p = sub; p < nparts; p += 16) {
+        const float v = part_val[(size_t)p * B + b];
+        const int i = part_idx[(size_t)p * B + b];
+        if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; }
+      }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-      int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    for (int o = 8; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
       if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
     }
-    if (lane != 0) continue;
+    if (sub != 0 || b >= B) continue;
     if (bi == 0x7fffffff) bi = 0;  // all-NaN row: stay in range
     if (ds.plain_out) { ds.plain_out[b] = bi; continue; }
     int fin = ds.finished[b];

@@ -86,7 +86,6 @@ __device__ void select_topk(float* sv, const int32_t* sidx, int n, int k, float*
                             int idx_base) {
   __shared__ float rv[32];
   __shared__ int ri[32];
-  __shared__ int winner;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   for (int round = 0; round < k; ++round) {
     float bv = -CUDART_INF_F;
@@ -113,7 +112,6 @@ __device__ void select_topk(float* sv, const int32_t* sidx, int n, int k, float*
         if (ov > bv || (ov == bv && op < bp)) { bv = ov; bp = op; }
       }
       if (lane == 0) {
-        winner = bp;
         if (bp != 0x7fffffff) {
           out_v[round] = bv;
           out_i[round] = sidx ? sidx[bp] : idx_base + bp;
@@ -125,7 +123,6 @@ __device__ void select_topk(float* sv, const int32_t* sidx, int n, int k, float*
       }
     }
     __syncthreads();
-    (void)winner;
   }
 }
 

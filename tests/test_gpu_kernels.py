@@ -80,7 +80,9 @@ def test_linear_bf16(pkg, lib, M, N, K, impl):
     pkg._lib.check(lib.tutor_linear(BF16, ptr(A), ptr(W), ptr(bias), ptr(res), ptr(out), 1, M, N, K, 1, impl, None))
     sync()
     ref = _linear_ref(A.double(), W.double(), bias.double(), res.double(), 1).float()
-    assert rel_err(out, ref) < 1e-5  # bf16 inputs are exact in fp32; only the accumulation order differs
+    # bf16 inputs are exact in fp32, so only the accumulation order differs - except that the tcgen05 kernel's
+    # row-major (M > 128) epilogue uses the one-instruction tanh (|err| ~ 5e-4), stated tolerance 2e-3
+    assert rel_err(out, ref) < (2e-3 if impl == 0 and M > 128 else 1e-5)
     outb = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
     pkg._lib.check(lib.tutor_linear(BF16, ptr(A), ptr(W), ptr(bias), None, ptr(outb), 0, M, N, K, 2, impl, None))
     sync()
