@@ -165,8 +165,11 @@ def attn_kernel_roofline(lib, check, torch, hbm_peak, peak_src):
     us = e0.elapsed_time(e1) * 1e3 / (reps * L)
     bytes_per_launch = B * H * S * 64 * 2 * 2 + 2 * B * H * 64 * 2  # K+V rows read, q read, out written
     achieved = bytes_per_launch / (us * 1e-6) / 1e9
-    return {"kernel": "attn_decode_kernel<bf16>", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-            "frac": achieved / hbm_peak, "traffic": None, "us_per_launch": us, "bytes_per_launch": bytes_per_launch,
+    return {"kernel": "attn_decode_tma_kernel<bf16> (cp.async.bulk + mbarrier ring)", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+            "frac": achieved / hbm_peak,
+            # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this kernel at
+            # this shape (profiles/r1d_ncu_attn_decode_tma_full.txt): 125.95 MB read + 5.5 MB written
+            "traffic": 131.5e6, "us_per_launch": us, "bytes_per_launch": bytes_per_launch,
             "peak_source": peak_src, "shape": f"B={B} H={H} S={S} hd=64 bf16"}
 
 
@@ -305,16 +308,49 @@ def extras(pkg, rp, torch, hf_small, tc_peak, hbm_peak):
     bert_hf = rp.build_bert(seed=0)
     bert = pkg.B200BertModel.from_hf(bert_hf, dtype="bf16")
     q, a = rp.bert_ids(32, 128, seed=2), rp.bert_ids(32, 512, seed=5)
-    def gate():
+    qd, ad = q.cuda(), a.cuda()
+    def gate_dev():
+        return pkg.cosine_similarity_batch(bert.embed(qd), bert.embed(ad))
+    def gate_host():
         return pkg.cosine_similarity_batch(bert.embed(q), bert.embed(a))
     for _ in range(3):
-        gate()
+        gate_dev(); gate_host()
+    torch.cuda.synchronize()
+    n = 10
     t0 = time.perf_counter()
     for _ in range(n):
-        gate()
+        gate_dev()
+    torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / n
-    res["cfg1_bert_base_bf16_32pairs"] = {"queries_per_s": 32 / dt, "ms_per_batch": dt * 1e3, "timing": "host wall, e2e",
+    t0 = time.perf_counter()
+    for _ in range(n):
+        gate_host()
+    dt_host = (time.perf_counter() - t0) / n
+    res["cfg1_bert_base_bf16_32pairs"] = {"queries_per_s": 32 / dt, "ms_per_batch": dt * 1e3,
+                                           "e2e_queries_per_s": 32 / dt_host, "e2e_ms_per_batch": dt_host * 1e3,
+                                           "timing": "host wall around synchronous calls; ids resident in HBM / e2e from host ids",
                                            "tflops": 3.81 / dt, "frac_of_bf16_peak": 3.81 / dt / tc_peak}
+    del bert
+    # configs[4]: 1M x 768 fp32 corpus on one GPU, 32 queries, top-10 (the 8-GPU form shards the rows)
+    g = torch.Generator(device="cuda").manual_seed(3)
+    corpus = torch.randn(1_000_000, 768, device="cuda", generator=g)
+    shard = pkg.CorpusShard(corpus)
+    qs = torch.randn(32, 768, device="cuda", generator=g)
+    for _ in range(3):
+        shard.topk(qs, 10)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n = 5
+    e0.record()
+    for _ in range(n):
+        shard.topk(qs, 10)
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / n
+    gbs = 1_000_000 * 768 * 4 / (us * 1e-6) / 1e9
+    res["cfg4_corpus_1M_x768_fp32_32q_top10"] = {"us_per_search": us, "queries_per_s": 32 / (us * 1e-6), "achieved_gbs": gbs,
+                                                  "frac_of_hbm_peak": gbs / hbm_peak, "timing": "CUDA events"}
+    del corpus, shard
     return res
 
 

@@ -2,6 +2,7 @@
 // declared in include/tutor_b200.h.
 #include <atomic>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "engine_common.h"
@@ -151,27 +152,34 @@ int tutor_cosine_pairs(const float* a, const float* b, float* out, int B, int d,
   return k_cosine_pairs(a, b, out, B, d, 1e-8f, (cudaStream_t)stream);
 }
 
+// grow-only device staging for the host-pointer cosine (cudaMalloc/cudaFree per call cost ~14 ms per relevance batch)
+namespace {
+std::mutex g_cos_mu;
+float* g_cos_buf = nullptr;
+size_t g_cos_floats = 0;
+int g_cos_dev = -1;
+}  // namespace
+
 int tutor_cosine_pairs_host(const float* a, const float* b, float* out, int B, int d) {
   ARG_CHECK(a && b && out && B >= 1 && d >= 1, "cosine_pairs_host: bad argument");
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
   TRY(tutor_require_device(dev));
-  float *da = nullptr, *db = nullptr, *dout = nullptr;
-  const size_t n = (size_t)B * d * sizeof(float);
-  int rc = TUTOR_OK;
-  if ((rc = dev_alloc(&da, n)) == TUTOR_OK && (rc = dev_alloc(&db, n)) == TUTOR_OK &&
-      (rc = dev_alloc(&dout, B * sizeof(float))) == TUTOR_OK) {
-    cudaError_t e = cudaMemcpy(da, a, n, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMemcpy(db, b, n, cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) rc = tutor_cuda_fail(e, "cudaMemcpy", __FILE__, __LINE__);
-    if (rc == TUTOR_OK) rc = k_cosine_pairs(da, db, dout, B, d, 1e-8f, nullptr);
-    if (rc == TUTOR_OK) {
-      e = cudaMemcpy(out, dout, B * sizeof(float), cudaMemcpyDeviceToHost);
-      if (e != cudaSuccess) rc = tutor_cuda_fail(e, "cudaMemcpy", __FILE__, __LINE__);
-    }
+  std::lock_guard<std::mutex> lock(g_cos_mu);
+  const size_t n = (size_t)B * d, need = 2 * n + B;
+  if (need > g_cos_floats || dev != g_cos_dev) {
+    if (g_cos_buf) cudaFree(g_cos_buf);
+    g_cos_buf = nullptr; g_cos_floats = 0;
+    TRY(dev_alloc(&g_cos_buf, need * sizeof(float)));
+    g_cos_floats = need; g_cos_dev = dev;
   }
-  dev_free(da); dev_free(db); dev_free(dout);
-  return rc;
+  float *da = g_cos_buf, *db = g_cos_buf + n, *dout = g_cos_buf + 2 * n;
+  CUDA_TRY(cudaMemcpyAsync(da, a, n * sizeof(float), cudaMemcpyHostToDevice, nullptr));
+  CUDA_TRY(cudaMemcpyAsync(db, b, n * sizeof(float), cudaMemcpyHostToDevice, nullptr));
+  TRY(k_cosine_pairs(da, db, dout, B, d, 1e-8f, nullptr));
+  CUDA_TRY(cudaMemcpyAsync(out, dout, B * sizeof(float), cudaMemcpyDeviceToHost, nullptr));
+  CUDA_TRY(cudaStreamSynchronize(nullptr));
+  return TUTOR_OK;
 }
 
 int tutor_row_inv_norm(const float* corpus, float* inv_norm, int N, int d, void* stream) {

@@ -195,3 +195,27 @@ def test_fused_decode_path_matches_unfused(pkg, tiny_hf, monkeypatch):
     err = ((outs[0][0] - outs[1][0]).abs().max() / outs[0][0].abs().max()).item()
     print(f"attention splits 1 vs 4: relative logit difference {err:.3e}")
     assert err < 5e-3 and (outs[0][1] == outs[1][1]).float().mean().item() > 0.95
+
+
+def test_cfg3_gpt2_large_prefill_heavy(pkg, golden):
+    """configs[3]: GPT-2 large (774M), B=16, 896-token prompts + 128 new tokens = 1024 positions (the most GPT-2 has),
+    bf16 tcgen05 prefill.  Against the fp32 oracle's ids (committed golden): step-0 logits of row 0 within the stated
+    bf16 tolerance (5e-2 relative), first generated token agreement >= 0.8; prompt preserved; deterministic."""
+    g = golden("gpt2_cfg3")
+    hf = rp.build_gpt2("large", seed=0)
+    eng = pkg.B200GPT2LMHeadModel.from_hf(hf, dtype="bf16")
+    del hf
+    ids = rp.gpt2_prompt_ids(16, 896, seed=1)
+    out = eng.generate(ids, max_new_tokens=128, repetition_penalty=1.0)
+    assert tuple(out.shape) == (16, 1024) and torch.equal(out[:, :896], ids)
+    same = out[:, 896:].numpy() == g["ids_p10"]
+    print(f"cfg3 bf16 vs fp32 oracle: first-token agreement {same[:, 0].mean():.3f}, overall {same.mean():.3f}")
+    assert same[:, 0].mean() >= 0.8
+    assert torch.equal(out, eng.generate(ids, max_new_tokens=128, repetition_penalty=1.0))
+    eng.prefill(ids, max_new_tokens=128)
+    logits = eng.last_logits()[0].float().cpu().numpy()
+    err = float(np.abs(logits - g["logits_step0_row0"]).max() / np.abs(g["logits_step0_row0"]).max())
+    print(f"cfg3 bf16 step-0 relative logit error {err:.3e}")
+    assert err < 5e-2
+    with pytest.raises(Exception, match="n_positions"):
+        eng.generate(rp.gpt2_prompt_ids(1, 1000, seed=2), max_new_tokens=128)  # would index past wpe
