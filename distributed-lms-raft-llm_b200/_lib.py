@@ -39,6 +39,8 @@ SIGNATURES = {
     "tutor_gpt2_load_tensor": (c_int, [c_void_p, c_char_p, c_void_p, P(C.c_int64), c_int]),
     "tutor_gpt2_check_loaded": (c_int, [c_void_p]),
     "tutor_gpt2_generate": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_int, c_void_p, P(c_int)]),
+    "tutor_gpt2_generate_padded": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_int,
+                                           c_void_p, P(c_int)]),
     "tutor_gpt2_generate_dev": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_int, c_void_p,
                                         P(c_int)]),
     "tutor_gpt2_prefill": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_int]),

@@ -43,7 +43,8 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
                                                           const int* __restrict__ len_dev, int len_host,
                                                           const float* __restrict__ qkv_partial, int ks,
                                                           const float* __restrict__ qkv_bias, int B,
-                                                          float* split_scratch, int* split_counters) {
+                                                          float* split_scratch, int* split_counters,
+                                                          const int* __restrict__ npad) {
   constexpr int EPL = Vec16<KT>::N;  // elements per lane
   constexpr int LPR = 64 / EPL;      // lanes per key row
   constexpr int KPW = 32 / LPR;      // keys per warp-wide load
@@ -60,8 +61,9 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
   const int g = warp * KPW + lane / LPR;  // this lane's group
   const int e0 = (lane % LPR) * EPL;      // first element of the row this lane owns
   const size_t base = ((size_t)b * H + h) * Smax * 64;
-  const KT* kb = kc + base + e0;
-  const KT* vb = vc + base + e0;
+  const int kp = npad ? npad[b] : 0;  // left padding: cache rows [0, kp) of this sequence are never attended to
+  const KT* kb = kc + base + (size_t)kp * 64 + e0;
+  const KT* vb = vc + base + (size_t)kp * 64 + e0;
 
   __shared__ float s_new[3][64];  // FUSED: q, and the K/V row of the current token (as stored, i.e. rounded to KT)
   float qv[EPL];
@@ -94,7 +96,7 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
   for (int i = 0; i < EPL; ++i) o[i] = 0.f;
 
   // FUSED: the row this CTA just appended (position len-1) is taken from shared memory after the loop
-  const int nk_all = FUSED ? len - 1 : len;
+  const int nk_all = (FUSED ? len - 1 : len) - kp;  // rows are counted from the first real token
   const int per = (nk_all + nsplit - 1) / nsplit;
   const int kbeg = z * per;
   const int nkeys = min(nk_all, kbeg + per);  // this split covers keys [kbeg, nkeys)
@@ -244,7 +246,8 @@ __global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf
                                                                     bf16* __restrict__ out, int H, int Smax,
                                                                     const int* __restrict__ len_dev, int len_host,
                                                                     const float* __restrict__ qkv_partial, int ks,
-                                                                    const float* __restrict__ qkv_bias, int B) {
+                                                                    const float* __restrict__ qkv_bias, int B,
+                                                                    const int* __restrict__ npad) {
   constexpr int EPL = 8, LPR = 8, KPW = 4, NG = 16, UNR = DK_CHUNK / NG;
   __shared__ __align__(128) bf16 sK[DK_STAGES][DK_CHUNK * 64];
   __shared__ __align__(128) bf16 sV[DK_STAGES][DK_CHUNK * 64];
@@ -255,7 +258,8 @@ __global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int len = len_dev ? *len_dev : len_host;  // written by a kernel that finished long before this launch
   const size_t base = ((size_t)b * H + h) * Smax * 64;
-  const int nkeys = FUSED ? len - 1 : len;
+  const int kp = npad ? npad[b] : 0;  // left padding: the stream starts at the first real token's row
+  const int nkeys = (FUSED ? len - 1 : len) - kp;
   const int nchunks = (nkeys + DK_CHUNK - 1) / DK_CHUNK;
   if (threadIdx.x == 0) {
     for (int s = 0; s < DK_STAGES; ++s) {
@@ -278,7 +282,7 @@ __global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf
         const uint32_t bytes = (uint32_t)rows * 128;
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dk_smem(&full_bar[s])),
                      "r"(2 * bytes) : "memory");
-        const size_t off = base + (size_t)c * DK_CHUNK * 64;
+        const size_t off = base + ((size_t)kp + (size_t)c * DK_CHUNK) * 64;
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                          dk_smem(&sK[s][0])), "l"(kc + off), "r"(bytes), "r"(dk_smem(&full_bar[s])) : "memory");
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
@@ -408,7 +412,7 @@ constexpr int PF_Q = 64, PF_KT = 32;
 template <typename QT, typename KT, typename OT, bool FAST>
 __global__ void __launch_bounds__(PF_Q) attn_prefill_kernel(const QT* __restrict__ q, const KT* __restrict__ kc,
                                                             const KT* __restrict__ vc, OT* __restrict__ out, int H,
-                                                            int T, int Smax, int causal) {
+                                                            int T, int Smax, int causal, const int* __restrict__ npad) {
   __shared__ __align__(16) float Ks[PF_KT][64];
   __shared__ __align__(16) float Vs[PF_KT][64];
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
@@ -416,6 +420,10 @@ __global__ void __launch_bounds__(PF_Q) attn_prefill_kernel(const QT* __restrict
   const int qi = qt * PF_Q + tid;
   const int qc = min(qi, T - 1);
   const int d = H * 64;
+  // left padding: a real token (index >= kp) never sees the pad slots [0, kp); a pad slot keeps plain causal
+  // visibility so that its (unused) row stays finite
+  const int kp = npad ? npad[b] : 0;
+  const int kmin = qc >= kp ? kp : 0;
   float qv[64], o[64];
   {
     const QT* qp = q + ((size_t)b * T + qc) * d + h * 64;
@@ -454,7 +462,7 @@ __global__ void __launch_bounds__(PF_Q) attn_prefill_kernel(const QT* __restrict
           acc = fmaf(qv[i + 2], kk.z, acc); acc = fmaf(qv[i + 3], kk.w, acc);
         }
         int j = k0 + sub + jj;
-        bool ok = (j < T) && (!causal || j <= qc);
+        bool ok = (j < T) && (!causal || j <= qc) && j >= kmin;
         s[jj] = ok ? acc : -CUDART_INF_F;
         mn = fmaxf(mn, s[jj]);
       }
@@ -519,7 +527,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 template <bool CAUSAL>
 __global__ void __launch_bounds__(128) attn_prefill_mma_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc,
                                                                 const bf16* __restrict__ vc, bf16* __restrict__ out,
-                                                                int H, int T, int Smax) {
+                                                                int H, int T, int Smax, const int* __restrict__ npad) {
   __shared__ __align__(128) uint8_t tiles[2][2][64 * 128];  // [stage][K|V][64 keys x 128 B], 16-byte chunks XOR-swizzled
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
@@ -544,6 +552,7 @@ __global__ void __launch_bounds__(128) attn_prefill_mma_kernel(const bf16* __res
   const size_t base = ((size_t)b * H + h) * Smax * 64;
   const int nkt_all = (T + 63) / 64;
   const int nkt = CAUSAL ? min(qt + 1, nkt_all) : nkt_all;
+  const int kp = npad ? npad[b] : 0;  // left padding, see attn_prefill_kernel
 
   auto load_tile = [&](int kt, int stage) {
 #pragma unroll
@@ -593,7 +602,7 @@ __global__ void __launch_bounds__(128) attn_prefill_mma_kernel(const bf16* __res
         const int key = kt * 64 + j * 8 + 2 * t + (r & 1);
         const int qrow = q0 + g + (r >> 1) * 8;
         float v = s[j][r] * 0.125f;
-        if (key >= T || (CAUSAL && key > qrow)) v = -CUDART_INF_F;
+        if (key >= T || (CAUSAL && key > qrow) || (key < kp && qrow >= kp)) v = -CUDART_INF_F;
         s[j][r] = v;
       }
       mx0 = fmaxf(mx0, fmaxf(s[j][0], s[j][1]));
@@ -660,17 +669,17 @@ int k_attn_decode_splits(int B, int H, int len_hint, int num_sms) {
 size_t k_attn_decode_scratch_bytes(int B, int H) { return (size_t)B * H * (8 * 66 * sizeof(float) + sizeof(int)); }
 
 int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int kv_dtype, void* out, int out_dtype,
-                  int B, int H, int Smax, const int* len_dev, int len_host, cudaStream_t st) {
+                  int B, int H, int Smax, const int* len_dev, int len_host, const int* npad, cudaStream_t st) {
   if (B == 0) return TUTOR_OK;
   ARG_CHECK(len_dev || (len_host >= 1 && len_host <= Smax), "attn_decode: len %d outside [1,%d]", len_host, Smax);
   dim3 grid(H, B), block(128);
   if (q_dtype == DT_F32 && kv_dtype == DT_F32 && out_dtype == DT_F32)
     attn_decode_kernel<float, float, float, false, false><<<grid, block, 0, st>>>(
         (const float*)q, (float*)k, (float*)v, (float*)out, H, Smax, len_dev, len_host, nullptr, 0, nullptr, B, nullptr,
-        nullptr);
+        nullptr, npad);
   else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16)
     attn_decode_tma_kernel<false, 64, 2, true><<<grid, DK_THREADS, 0, st>>>((const bf16*)q, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax,
-                                                               len_dev, len_host, nullptr, 0, nullptr, B);
+                                                               len_dev, len_host, nullptr, 0, nullptr, B, npad);
   else {
     tutor_set_error("attn_decode: unsupported dtype combination q=%d kv=%d out=%d", q_dtype, kv_dtype, out_dtype);
     return TUTOR_ERR_ARG;
@@ -681,7 +690,7 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
 
 int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias, void* k, void* v, int kv_dtype,
                         void* out, int out_dtype, int B, int H, int Smax, const int* len_dev, int len_host,
-                        int nsplit, void* split_scratch, cudaStream_t st) {
+                        int nsplit, void* split_scratch, const int* npad, cudaStream_t st) {
   if (B == 0) return TUTOR_OK;
   ARG_CHECK(kv_dtype == DT_BF16 && out_dtype == DT_BF16, "attn_decode_fused: bf16 cache and output only");
   ARG_CHECK(qkv_partial && qkv_bias && ks >= 1, "attn_decode_fused: bad partials");
@@ -689,7 +698,8 @@ int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias,
   ARG_CHECK(nsplit >= 1 && nsplit <= 8 && (nsplit == 1 || split_scratch), "attn_decode_fused: bad split setup");
   if (nsplit == 1) {
     CUDA_TRY(tutor_launch(attn_decode_tma_kernel<true, 64, 2, true>, dim3(H, B), dim3(DK_THREADS), 0, st, (const bf16*)nullptr,
-                          (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B));
+                          (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B,
+                          npad));
     KERNEL_LAUNCHED();
     return TUTOR_OK;
   }
@@ -697,27 +707,27 @@ int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias,
   int* counters = reinterpret_cast<int*>(sc + (size_t)B * H * 8 * 66);  // zeroed by the owner; self-resetting
   CUDA_TRY(tutor_launch(attn_decode_kernel<bf16, bf16, bf16, true, true>, dim3(H, B, nsplit), dim3(128), 0, st,
                         (const bf16*)nullptr, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks,
-                        qkv_bias, B, sc, counters));
+                        qkv_bias, B, sc, counters, npad));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }
 
 int k_attn_prefill(const void* q, int q_dtype, const void* k, const void* v, int kv_dtype, void* out, int out_dtype,
-                   int B, int H, int T, int Smax, int causal, cudaStream_t st) {
+                   int B, int H, int T, int Smax, int causal, const int* npad, cudaStream_t st) {
   if (B == 0 || T == 0) return TUTOR_OK;
   ARG_CHECK(T <= Smax, "attn_prefill: T=%d > Smax=%d", T, Smax);
   dim3 grid(ceil_div(T, PF_Q), H, B), block(PF_Q);
   if (q_dtype == DT_F32 && kv_dtype == DT_F32 && out_dtype == DT_F32)
     attn_prefill_kernel<float, float, float, false><<<grid, block, 0, st>>>(
-        (const float*)q, (const float*)k, (const float*)v, (float*)out, H, T, Smax, causal);
+        (const float*)q, (const float*)k, (const float*)v, (float*)out, H, T, Smax, causal, npad);
   else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16) {
     dim3 g2(ceil_div(T, 64), H, B);
     if (causal)
       attn_prefill_mma_kernel<true><<<g2, 128, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)out, H, T,
-                                                        Smax);
+                                                        Smax, npad);
     else
       attn_prefill_mma_kernel<false><<<g2, 128, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)out, H,
-                                                         T, Smax);
+                                                         T, Smax, npad);
   }
   else {
     tutor_set_error("attn_prefill: unsupported dtype combination q=%d kv=%d out=%d", q_dtype, kv_dtype, out_dtype);

@@ -119,13 +119,13 @@ int tutor_linear(int dtype, const void* A, const void* W, const float* bias, con
 int tutor_attn_prefill(int dtype, const void* q, const void* k, const void* v, void* out, int B, int H, int T, int Smax,
                        int causal, void* stream) {
   ARG_CHECK(q && k && v && out, "attn_prefill: null argument");
-  return k_attn_prefill(q, dtype, k, v, dtype, out, dtype, B, H, T, Smax, causal, (cudaStream_t)stream);
+  return k_attn_prefill(q, dtype, k, v, dtype, out, dtype, B, H, T, Smax, causal, nullptr, (cudaStream_t)stream);
 }
 
 int tutor_attn_decode(int dtype, const void* q, const void* k, const void* v, void* out, int B, int H, int Smax, int len,
                       void* stream) {
   ARG_CHECK(q && k && v && out, "attn_decode: null argument");
-  return k_attn_decode(q, dtype, k, v, dtype, out, dtype, B, H, Smax, nullptr, len, (cudaStream_t)stream);
+  return k_attn_decode(q, dtype, k, v, dtype, out, dtype, B, H, Smax, nullptr, len, nullptr, (cudaStream_t)stream);
 }
 
 size_t tutor_lmhead_scratch_bytes(int B) { return k_lmhead_scratch_bytes(B, 0); }

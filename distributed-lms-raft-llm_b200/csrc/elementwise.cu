@@ -11,7 +11,7 @@ constexpr int LN_MAX_PER_LANE = 4 * LN_V4;  // fully unrolled so the row stays i
 template <typename WT>
 __global__ void gpt2_embed_kernel(const int32_t* __restrict__ ids, int ids_ld, const int* __restrict__ len_dev,
                                   int T, const WT* __restrict__ wte, const float* __restrict__ wpe, int d,
-                                  float* __restrict__ x, int M) {
+                                  float* __restrict__ x, int M, const int* __restrict__ npad) {
   pdl_launch_dependents();
   pdl_wait();
   int m = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -21,7 +21,10 @@ __global__ void gpt2_embed_kernel(const int32_t* __restrict__ ids, int ids_ld, c
   int pos = len_dev ? (*len_dev - 1) : t;  // decode: the last token written; prefill: 0..T-1
   int id = ids[(size_t)b * ids_ld + pos];
   const WT* e = wte + (size_t)id * d;
-  const float* p = wpe + (size_t)pos * d;
+  // left-padded rows: position_ids = cumsum(attention_mask) - 1 (HF/generation/utils.py:718-721), i.e. the index
+  // among the real tokens; pad slots themselves are never attended to, any in-range position does for them
+  const int pe = npad ? max(pos - npad[b], 0) : pos;
+  const float* p = wpe + (size_t)pe * d;
   float* o = x + (size_t)m * d;
   for (int i = lane * 4; i < d; i += 128) {
     float4 a = load4(e + i), c = load4(p + i);
@@ -186,15 +189,15 @@ __global__ void seen_bitmap_kernel(const int32_t* __restrict__ ids, int ids_ld, 
 }  // namespace
 
 int k_gpt2_embed(const int32_t* ids, int ids_ld, const int* len_dev, int T, const void* wte, int wdtype,
-                 const float* wpe, int d, float* x, int M, cudaStream_t st) {
+                 const float* wpe, int d, float* x, int M, const int* npad, cudaStream_t st) {
   ARG_CHECK(d % 4 == 0, "embed: d %% 4 != 0");
   dim3 grid(ceil_div(M, 8)), block(256);
   if (wdtype == DT_F32)
     CUDA_TRY(tutor_launch(gpt2_embed_kernel<float>, grid, block, 0, st, ids, ids_ld, len_dev, T, (const float*)wte, wpe,
-                          d, x, M));
+                          d, x, M, npad));
   else
     CUDA_TRY(tutor_launch(gpt2_embed_kernel<bf16>, grid, block, 0, st, ids, ids_ld, len_dev, T, (const bf16*)wte, wpe,
-                          d, x, M));
+                          d, x, M, npad));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }

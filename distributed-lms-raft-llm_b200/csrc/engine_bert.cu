@@ -86,7 +86,7 @@ int forward(tutor_bert* e, int B, int T) {
     qe.ldo = d; qe.qkv_mode = 1; qe.kv_dtype = dt; qe.kcache = e->kbuf; qe.vcache = e->vbuf;
     qe.d = d; qe.H = e->H; qe.Smax = T; qe.T = T; qe.pos0 = 0;
     TRY(gemm(e, w.qkv, M, qe, e->x, e->xb));
-    TRY(k_attn_prefill(e->q, dt, e->kbuf, e->vbuf, dt, e->att, dt, B, e->H, T, T, /*causal=*/0, st));
+    TRY(k_attn_prefill(e->q, dt, e->kbuf, e->vbuf, dt, e->att, dt, B, e->H, T, T, /*causal=*/0, nullptr, st));
     GemmEpilogue oe{};  // BertSelfOutput: dense + residual, then LayerNorm (modeling_bert.py:294-298)
     oe.bias = w.attn_out.b; oe.residual = e->x; oe.out_f32 = e->tmp; oe.ldo = d;
     TRY(gemm(e, w.attn_out, M, oe, e->att, e->att));

@@ -44,6 +44,8 @@ struct tutor_gpt2 {
   uint32_t* seen = nullptr;
   int seen_words = 0;
   int* finished = nullptr;
+  int* npad = nullptr;     // [B] leading pad slots per row (left-padded batches); all zero otherwise
+  bool padded = false;
   void* lm_scratch = nullptr;
   void* attn_scratch = nullptr;  // split states + arrival counters of the decode attention, one slice per lane
   size_t attn_scratch_lane_bytes = 0;
@@ -103,7 +105,8 @@ int forward(tutor_gpt2* e, int B, int T, bool decode) {
   const int* len_dev = decode ? e->counters : nullptr;
   float* xn_f = dt == DT_F32 ? (float*)e->xn : nullptr;
   bf16* xn_b = dt == DT_BF16 ? (bf16*)e->xn : nullptr;
-  TRY(k_gpt2_embed(e->ids, e->ids_ld, len_dev, T, e->wte, dt, e->wpe, d, e->x, M, st));
+  const int* npad = e->padded ? e->npad : nullptr;
+  TRY(k_gpt2_embed(e->ids, e->ids_ld, len_dev, T, e->wte, dt, e->wpe, d, e->x, M, npad, st));
   for (int l = 0; l < e->L; ++l) {
     const Gpt2Layer& w = e->layers[l];
     TRY(k_layernorm(e->x, 1, 0, w.ln1_g, w.ln1_b, e->cfg.layer_norm_epsilon, xn_f, xn_b, M, d, st));
@@ -116,9 +119,9 @@ int forward(tutor_gpt2* e, int B, int T, bool decode) {
     qe.d = d; qe.H = e->H; qe.Smax = e->Smax; qe.T = T; qe.pos0 = 0; qe.pos_dev = len_dev;
     TRY(gemm(e, e->xn, w.qkv, M, qe));
     if (decode)
-      TRY(k_attn_decode(e->q, dt, e->kcache(l), e->vcache(l), dt, e->att, dt, B, e->H, e->Smax, e->counters, 0, st));
+      TRY(k_attn_decode(e->q, dt, e->kcache(l), e->vcache(l), dt, e->att, dt, B, e->H, e->Smax, e->counters, 0, npad, st));
     else
-      TRY(k_attn_prefill(e->q, dt, e->kcache(l), e->vcache(l), dt, e->att, dt, B, e->H, T, e->Smax, 1, st));
+      TRY(k_attn_prefill(e->q, dt, e->kcache(l), e->vcache(l), dt, e->att, dt, B, e->H, T, e->Smax, 1, npad, st));
     GemmEpilogue pe{};  // attn c_proj + residual (modeling_gpt2.py:223, 282)
     pe.bias = w.proj.b; pe.residual = e->x; pe.out_f32 = e->x; pe.ldo = d;
     TRY(gemm(e, e->att, w.proj, M, pe));
@@ -155,7 +158,8 @@ int forward_decode_fused(tutor_gpt2* e, int lane, int b0, int B) {
   bf16* xl = (bf16*)e->xn_last + (size_t)b0 * d;
   float* partial = e->partial + (size_t)lane * e->partial_lane_elems;
   const size_t kv_off = (size_t)b0 * e->H * e->Smax * 64 * e->esz();
-  TRY(k_gpt2_embed(e->ids + (size_t)b0 * e->ids_ld, e->ids_ld, len, 1, e->wte, e->dt, e->wpe, d, x, B, st));
+  const int* npad = e->padded ? e->npad + b0 : nullptr;
+  TRY(k_gpt2_embed(e->ids + (size_t)b0 * e->ids_ld, e->ids_ld, len, 1, e->wte, e->dt, e->wpe, d, x, B, npad, st));
   TRY(k_layernorm(x, 1, 0, e->layers[0].ln1_g, e->layers[0].ln1_b, eps, nullptr, xn, B, d, st));
   for (int l = 0; l < e->L; ++l) {
     const Gpt2Layer& w = e->layers[l];
@@ -164,7 +168,7 @@ int forward_decode_fused(tutor_gpt2* e, int lane, int b0, int B) {
     int ks = k_pick_splitk(3 * d, d, e->num_sms);
     TRY(k_gemm_bf16_splitk(xn, (const bf16*)w.qkv.w, B, 3 * d, d, ks, partial, st));
     TRY(k_attn_decode_fused(partial, ks, w.qkv.b, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
-                            e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, st));
+                            e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, npad, st));
     ks = k_pick_splitk(d, d, e->num_sms);
     TRY(k_gemm_bf16_splitk(att, (const bf16*)w.proj.w, B, d, d, ks, partial, st));
     TRY(k_reduce_bias_residual_ln(partial, ks, B, d, w.proj.b, x, w.ln2_g, w.ln2_b, eps, nullptr, xn, st));
@@ -217,7 +221,8 @@ int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
     // rows past the current length are read (masked) by the attention kernels: they must hold finite values
     CUDA_TRY(cudaMemsetAsync(e->kv, 0, bytes, e->stream));
     dev_free(e->ids); dev_free(e->seen); dev_free(e->finished); dev_free(e->lm_scratch); dev_free(e->xn_last);
-    dev_free(e->partial); dev_free(e->attn_scratch);
+    dev_free(e->partial); dev_free(e->npad);
+    TRY(dev_alloc(&e->npad, (size_t)nb * sizeof(int))); dev_free(e->attn_scratch);
     e->attn_scratch_lane_bytes = round_up(k_attn_decode_scratch_bytes(nb, e->H), 256);
     TRY(dev_alloc(&e->attn_scratch, tutor_gpt2::MAX_LANES * e->attn_scratch_lane_bytes));
     CUDA_TRY(cudaMemsetAsync(e->attn_scratch, 0, tutor_gpt2::MAX_LANES * e->attn_scratch_lane_bytes, e->stream));
@@ -271,10 +276,22 @@ int check_args(tutor_gpt2* e, int B, int T, int total) {
 }
 
 // common prologue once the prompt is in e->ids (device, int32, row stride ids_ld)
-int start_generation(tutor_gpt2* e, int B, int T, int total, float penalty, int eos, int pad) {
+int start_generation(tutor_gpt2* e, int B, int T, int total, float penalty, int eos, int pad,
+                     const int32_t* npad_host = nullptr) {
   const int nl = (e->dt == DT_BF16 && e->use_fused && B <= 128) ? (B >= 2 * e->cfg_lanes ? e->cfg_lanes : 1) : 1;
-  if (penalty != e->cur_penalty || eos != e->cur_eos || pad != e->cur_pad || B != e->cur_B || nl != e->nlanes)
+  bool padded = false;
+  if (npad_host) {
+    for (int b = 0; b < B; ++b) {
+      ARG_CHECK(npad_host[b] >= 0 && npad_host[b] < T, "gpt2.generate: row %d has %d pad slots in a %d-token prompt", b,
+                npad_host[b], T);
+      padded = padded || npad_host[b] > 0;
+    }
+    if (padded) CUDA_TRY(cudaMemcpy(e->npad, npad_host, (size_t)B * sizeof(int), cudaMemcpyHostToDevice));
+  }
+  if (penalty != e->cur_penalty || eos != e->cur_eos || pad != e->cur_pad || B != e->cur_B || nl != e->nlanes ||
+      padded != e->padded)
     drop_graph(e);
+  e->padded = padded;
   e->nlanes = nl;
   int splits = k_attn_decode_splits((B + nl - 1) / nl, e->H, (T + total) / 2, e->num_sms);
   if (const char* sv = getenv("TUTOR_ATTN_SPLITS")) splits = atoi(sv) < 1 ? 1 : (atoi(sv) > 8 ? 8 : atoi(sv));
@@ -426,7 +443,7 @@ void tutor_gpt2_destroy(tutor_gpt2_t* e) {
   }
   dev_free(e->kv); dev_free(e->x); dev_free(e->xn); dev_free(e->q); dev_free(e->att); dev_free(e->hbuf);
   dev_free(e->xn_last); dev_free(e->ids); dev_free(e->counters); dev_free(e->seen); dev_free(e->finished);
-  dev_free(e->lm_scratch); dev_free(e->partial); dev_free(e->attn_scratch);
+  dev_free(e->lm_scratch); dev_free(e->partial); dev_free(e->attn_scratch); dev_free(e->npad);
   if (e->h_counters) cudaFreeHost(e->h_counters);
   for (int i = 1; i < tutor_gpt2::MAX_LANES; ++i) {
     if (e->lane_stream[i]) cudaStreamDestroy(e->lane_stream[i]);
@@ -547,6 +564,11 @@ int tutor_gpt2_read_ids(tutor_gpt2_t* e, int64_t* out_host, int cap, int* out_le
 
 int tutor_gpt2_generate(tutor_gpt2_t* e, const int64_t* ids_host, int B, int T, int total, float penalty, int eos,
                         int pad, int64_t* out_host, int* out_len) {
+  return tutor_gpt2_generate_padded(e, ids_host, nullptr, B, T, total, penalty, eos, pad, out_host, out_len);
+}
+
+int tutor_gpt2_generate_padded(tutor_gpt2_t* e, const int64_t* ids_host, const int32_t* npad_host, int B, int T,
+                               int total, float penalty, int eos, int pad, int64_t* out_host, int* out_len) {
   TRY(check_args(e, B, T, total));
   ARG_CHECK(ids_host && out_host && out_len, "gpt2.generate: null argument");
   std::lock_guard<std::mutex> lock(e->mu);  // held to the end: 10 gRPC handler threads share one engine
@@ -554,7 +576,7 @@ int tutor_gpt2_generate(tutor_gpt2_t* e, const int64_t* ids_host, int B, int T, 
   TRY(tutor_gpt2_check_loaded(e));
   TRY(ensure_capacity(e, B, T, total));
   TRY(upload_prompt(e, ids_host, B, T));
-  TRY(start_generation(e, B, T, total, penalty, eos, pad));
+  TRY(start_generation(e, B, T, total, penalty, eos, pad, npad_host));
   TRY(run_steps(e, total - T - 1, true));
   return read_ids_locked(e, out_host, B * total, out_len, nullptr);
 }

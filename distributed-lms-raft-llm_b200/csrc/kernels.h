@@ -5,7 +5,7 @@
 
 // ---- elementwise.cu
 int k_gpt2_embed(const int32_t* ids, int ids_ld, const int* len_dev, int T, const void* wte, int wdtype,
-                 const float* wpe, int d, float* x, int M, cudaStream_t st);
+                 const float* wpe, int d, float* x, int M, const int* npad, cudaStream_t st);
 int k_layernorm(const float* x, int in_stride, int in_offset, const float* gamma, const float* beta, float eps,
                 float* out_f32, bf16* out_bf16, int M, int d, cudaStream_t st);
 int k_bert_embed_ln(const int32_t* ids, int T, const void* word, int wdtype, const float* pos, const float* type0,
@@ -27,18 +27,19 @@ int k_gemm_bf16_legacy(const bf16* A, const bf16* W, int M, int N, int K, const 
 
 // ---- attention.cu : head_dim is 64 for every model on this path
 // q [B*T, H*64] (fp32 or bf16), K/V [B][H][Smax][64] of kv_dtype, out [B*T, H*64]
+// npad (nullable, [B]): leading pad slots of each left-padded sequence - real tokens never attend to them
 int k_attn_prefill(const void* q, int q_dtype, const void* k, const void* v, int kv_dtype, void* out, int out_dtype,
-                   int B, int H, int T, int Smax, int causal, cudaStream_t st);
+                   int B, int H, int T, int Smax, int causal, const int* npad, cudaStream_t st);
 // one query per (b,h) against cache positions [0, len): len = *len_dev if non-null else len_host
 int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int kv_dtype, void* out, int out_dtype,
-                  int B, int H, int Smax, const int* len_dev, int len_host, cudaStream_t st);
+                  int B, int H, int Smax, const int* len_dev, int len_host, const int* npad, cudaStream_t st);
 
 // fused QKV reduce + cache append + attention for the split-K decode path (bf16): qkv_partial [ks][B][3*H*64]
 // nsplit > 1 cuts the key range over gridDim.z CTAs per (b,h) (better SM balance); split_scratch holds
 // k_attn_decode_scratch_bytes(B,H) bytes laid out for B rows, zero-initialised once by the owner
 int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias, void* k, void* v, int kv_dtype,
                         void* out, int out_dtype, int B, int H, int Smax, const int* len_dev, int len_host,
-                        int nsplit, void* split_scratch, cudaStream_t st);
+                        int nsplit, void* split_scratch, const int* npad, cudaStream_t st);
 int k_attn_decode_splits(int B, int H, int len_hint, int num_sms);
 size_t k_attn_decode_scratch_bytes(int B, int H);
 

@@ -92,22 +92,30 @@ class B200GPT2LMHeadModel:
             raise ValueError("Greedy methods without beam search do not support `num_return_sequences` different than 1")
         if kwargs.get("num_beams", 1) != 1:
             raise NotImplementedError("beam search is not on the reference path")
-        if attention_mask is not None and not bool(torch.all(attention_mask == 1)):
-            raise NotImplementedError("padded batches (attention_mask with zeros) are not supported yet")
         B, T = inputs.shape
+        npad = None
+        if attention_mask is not None and not bool(torch.all(attention_mask == 1)):
+            # left padding only (what decoder-only generation requires; transformers warns about right padding)
+            mask = attention_mask.to("cpu", torch.int64)
+            npad = (mask == 0).sum(dim=1)
+            expect = (torch.arange(T)[None, :] >= npad[:, None]).to(torch.int64)
+            if tuple(mask.shape) != (B, T) or not torch.equal(mask, expect) or bool(torch.any(npad >= T)):
+                raise NotImplementedError("only left-padded batches are supported (attention_mask = zeros then ones)")
+            npad = npad.to(torch.int32).contiguous()
         total, eos, pad = self._resolve(T, max_length, max_new_tokens, eos_token_id, pad_token_id)
         n = C.c_int(0)
-        if inputs.is_cuda:
+        if inputs.is_cuda and npad is None:
             ids = inputs.to(torch.int32).contiguous()
             out = torch.empty((B, total), dtype=torch.int32, device=inputs.device)
             torch.cuda.current_stream(inputs.device).synchronize()
             _lib.check(self.lib.tutor_gpt2_generate_dev(self._h, ids.data_ptr(), B, T, total, float(repetition_penalty),
                                                         eos, pad, out.data_ptr(), C.byref(n)))
             return out[:, :n.value].to(torch.int64)
-        ids = inputs.to(torch.int64).contiguous()
+        ids = inputs.to("cpu", torch.int64).contiguous()
         out = torch.empty((B * total,), dtype=torch.int64)
-        _lib.check(self.lib.tutor_gpt2_generate(self._h, ids.data_ptr(), B, T, total, float(repetition_penalty), eos, pad,
-                                                out.data_ptr(), C.byref(n)))
+        _lib.check(self.lib.tutor_gpt2_generate_padded(self._h, ids.data_ptr(), None if npad is None else npad.data_ptr(),
+                                                       B, T, total, float(repetition_penalty), eos, pad, out.data_ptr(),
+                                                       C.byref(n)))
         return out[:B * n.value].view(B, n.value)
 
     # ------------------------------------------------------------------ stepwise (tests, profiling)

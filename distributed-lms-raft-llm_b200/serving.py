@@ -99,3 +99,137 @@ def call(address, token, query, timeout=60.0):
         rpc = channel.unary_unary(FULL_METHOD, request_serializer=QueryRequest.SerializeToString,
                                   response_deserializer=QueryResponse.FromString)
         return rpc(QueryRequest(token=token, query=query), timeout=timeout)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# the product's real traffic is batch-1 requests on 10 gRPC handler threads
+# (REF/tutoring_server.py:40).  BatchingModel coalesces concurrent `generate` calls into one left-padded batch so the
+# batched decode kernels see a batch, and hands every caller exactly what its own batch-1 call would have returned.
+import threading
+import time
+from collections import OrderedDict
+
+
+class BatchingModel:
+    """Drop-in for the tutoring server's `model`: `generate(inputs[1,T], **kwargs)` from many threads.
+
+    Requests that arrive within `max_wait_ms` of each other (and share repetition_penalty / eos / pad) run as one
+    batch: rows are left-padded to the longest prompt, the engine masks the pad slots and numbers positions from the
+    first real token (tutor_gpt2_generate_padded), and each caller gets `[1, its own length]` back - its prompt, its
+    own `max_length` budget, cut after its first EOS.  Pad slots are filled with the row's own first token, so the
+    repetition penalty sees exactly the ids a batch-1 call would see.
+    """
+
+    def __init__(self, engine, max_batch: int = 64, max_wait_ms: float = 4.0):
+        self.engine, self.max_batch, self.max_wait = engine, max_batch, max_wait_ms / 1e3
+        self._cv = threading.Condition()
+        self._queue = []
+        self._stop = False
+        self.batches = []  # sizes of the batches actually run (observability / tests)
+        self._worker = threading.Thread(target=self._run, daemon=True)
+        self._worker.start()
+
+    def close(self):
+        with self._cv:
+            self._stop = True
+            self._cv.notify_all()
+        self._worker.join(timeout=5)
+
+    def generate(self, inputs, max_length=None, max_new_tokens=None, repetition_penalty=1.0, eos_token_id=None,
+                 pad_token_id=None, **kwargs):
+        if inputs.dim() != 2 or inputs.shape[0] != 1:
+            return self.engine.generate(inputs, max_length=max_length, max_new_tokens=max_new_tokens,
+                                        repetition_penalty=repetition_penalty, eos_token_id=eos_token_id,
+                                        pad_token_id=pad_token_id, **kwargs)
+        T = inputs.shape[1]
+        total, eos, pad = self.engine._resolve(T, max_length, max_new_tokens, eos_token_id, pad_token_id)  # may raise
+        req = dict(ids=inputs[0].to("cpu"), new=total - T, key=(float(repetition_penalty), eos, pad),
+                   done=threading.Event(), out=None, err=None)
+        with self._cv:
+            self._queue.append(req)
+            self._cv.notify_all()
+        req["done"].wait()
+        if req["err"] is not None:
+            raise req["err"]
+        return req["out"]
+
+    def _run(self):
+        import torch
+        while True:
+            with self._cv:
+                while not self._queue and not self._stop:
+                    self._cv.wait()
+                if self._stop and not self._queue:
+                    return
+                deadline = time.monotonic() + self.max_wait
+                while len(self._queue) < self.max_batch and time.monotonic() < deadline and not self._stop:
+                    self._cv.wait(timeout=max(0.0, deadline - time.monotonic()))
+                key = self._queue[0]["key"]
+                batch = [r for r in self._queue if r["key"] == key][:self.max_batch]
+                self._queue = [r for r in self._queue if all(r is not b for b in batch)]
+            try:
+                pen, eos, pad = key
+                T = max(r["ids"].numel() for r in batch)
+                new = max(r["new"] for r in batch)
+                ids = torch.empty((len(batch), T), dtype=torch.int64)
+                mask = torch.ones((len(batch), T), dtype=torch.int64)
+                for b, r in enumerate(batch):
+                    p = T - r["ids"].numel()
+                    ids[b, :p] = r["ids"][0]  # pad with the row's own first token: invisible to the repetition penalty
+                    ids[b, p:] = r["ids"]
+                    mask[b, :p] = 0
+                out = self.engine.generate(ids, attention_mask=mask, max_new_tokens=new, repetition_penalty=pen,
+                                           eos_token_id=None if eos < 0 else eos, pad_token_id=pad)
+                self.batches.append(len(batch))
+                for b, r in enumerate(batch):
+                    p, t = T - r["ids"].numel(), r["ids"].numel()
+                    row = out[b, p:min(out.shape[1], T + r["new"])]
+                    gen = row[t:]
+                    hit = (gen == eos).nonzero()
+                    if eos >= 0 and hit.numel():
+                        row = row[:t + int(hit[0]) + 1]  # a batch-1 call stops right after its first EOS
+                    r["out"] = row.clone()[None]
+            except Exception as e:  # every waiting caller sees the failure, like a batch-1 call would
+                for r in batch:
+                    r["err"] = e
+            for r in batch:
+                r["done"].set()
+
+
+# ------------------------------------------------------------------------------------------------------------
+# SURVEY.md §8f rank 2: the reference reloads BERT from disk and re-embeds the (unchanged) assignment text on every
+# request (REF/lms_server.py:1258-1263).  RelevanceGate loads once and caches assignment embeddings.
+class RelevanceGate:
+    """`check(query, assignment_text)` = REF/lms_server.py:1262-1269 with one BERT forward per request instead of a
+    model load plus two forwards.  Same functions underneath (compute_embeddings, cosine_similarity), same 0.6."""
+
+    def __init__(self, model, tokenizer, threshold: float = 0.6, cache_size: int = 1024):
+        from . import bert as _bert
+        self._bert = _bert
+        self.model, self.tokenizer, self.threshold = model, tokenizer, threshold
+        self._cache, self._cache_size, self._lock = OrderedDict(), cache_size, threading.Lock()
+        self.hits = self.misses = 0
+
+    def assignment_embedding(self, text):
+        with self._lock:
+            if text in self._cache:
+                self._cache.move_to_end(text)
+                self.hits += 1
+                return self._cache[text]
+        emb = self._bert.compute_embeddings(text, self.model, self.tokenizer)
+        with self._lock:
+            self.misses += 1
+            self._cache[text] = emb
+            while len(self._cache) > self._cache_size:
+                self._cache.popitem(last=False)
+        return emb
+
+    def check(self, query, assignment_text):
+        q = self._bert.compute_embeddings(query, self.model, self.tokenizer)
+        similarity = self._bert.cosine_similarity(q, self.assignment_embedding(assignment_text))
+        return (not (similarity < self.threshold)), similarity
+
+    def answer(self, query, assignment_text, ask_tutor):
+        """The tail of LMSService.GetLLMAnswer (REF/lms_server.py:1266-1274): canned reply or forward to the tutor."""
+        relevant, _ = self.check(query, assignment_text)
+        return ask_tutor(query) if relevant else self._bert.NOT_RELATED_MESSAGE

@@ -72,7 +72,15 @@ int tutor_gpt2_check_loaded(tutor_gpt2_t* h);
  * the device-side finished flag every 32 steps).                                                              */
 int tutor_gpt2_generate(tutor_gpt2_t* h, const int64_t* ids_host, int B, int T, int max_total_len,
                         float repetition_penalty, int eos_id, int pad_id, int64_t* out_host, int* out_len);
-/* Same, with the prompt and the result resident in device memory (int32): ids_dev [B,T], out_dev
+/* Left-padded batches (what a tokenizer with padding_side="left" produces for prompts of different lengths, and what
+ * the micro-batching queue in serving.py builds): npad_host[b] = number of leading pad slots of row b (its
+ * attention_mask is npad zeros followed by ones).  Real tokens never attend to the pad slots and take
+ * position_ids = cumsum(mask)-1 (transformers/generation/utils.py:718-721); everything else as tutor_gpt2_generate.
+ * npad_host may be null (no padding).                                                                           */
+int tutor_gpt2_generate_padded(tutor_gpt2_t* h, const int64_t* ids_host, const int32_t* npad_host, int B, int T,
+                               int max_total_len, float repetition_penalty, int eos_id, int pad_id,
+                               int64_t* out_host, int* out_len);
+/* Same as tutor_gpt2_generate, with the prompt and the result resident in device memory (int32): ids_dev [B,T], out_dev
  * [B, max_total_len] written with row stride max_total_len.                                                   */
 int tutor_gpt2_generate_dev(tutor_gpt2_t* h, const int32_t* ids_dev, int B, int T, int max_total_len,
                             float repetition_penalty, int eos_id, int pad_id, int32_t* out_dev, int* out_len);

@@ -199,7 +199,29 @@ def make_cfg3(tut, lms):
                         logits_step0_row0=logits[0, 0].numpy())
 
 
-MAKERS = dict(cfg0=make_cfg0, as_written=make_as_written, tiny=make_tiny, bert=make_bert, bert_tiny=make_bert_tiny,
+def make_padded(tut, lms):
+    """Left-padded batch (prompts of different lengths, as the micro-batching queue builds them): HF generate with
+    attention_mask, position_ids = cumsum(mask)-1; plus each row generated alone, unpadded."""
+    model = rp.build_gpt2("tiny", seed=3)
+    T, npad = 12, [0, 3, 7, 1]
+    ids = rp.gpt2_prompt_ids(4, T, seed=21, vocab=1000)
+    mask = torch.ones_like(ids)
+    for b, p in enumerate(npad):
+        ids[b, :p] = 999
+        mask[b, :p] = 0
+    out = {"ids": ids.numpy(), "mask": mask.numpy(), "npad": np.array(npad)}
+    for name, pen in (("p10", 1.0), ("p12", 1.2)):
+        out[f"batch_{name}"] = rp.generate(model, ids, attention_mask=mask, max_new_tokens=20, repetition_penalty=pen,
+                                           eos_token_id=999, pad_token_id=999).numpy()
+        for b, p in enumerate(npad):
+            out[f"row{b}_{name}"] = rp.generate(model, ids[b:b + 1, p:], max_new_tokens=20, repetition_penalty=pen,
+                                                eos_token_id=999, pad_token_id=999).numpy()
+    same = [np.array_equal(out["batch_p10"][b, npad[b]:], out[f"row{b}_p10"][0]) for b in range(4)]
+    print("padded batch rows equal their unpadded bs-1 generation (HF itself):", same)
+    np.savez_compressed(os.path.join(OUT, "gpt2_padded.npz"), **out)
+
+
+MAKERS = dict(padded=make_padded, cfg0=make_cfg0, as_written=make_as_written, tiny=make_tiny, bert=make_bert, bert_tiny=make_bert_tiny,
               cfg2=make_cfg2, cfg3=make_cfg3)
 
 

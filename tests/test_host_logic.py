@@ -30,7 +30,7 @@ def test_generate_rejects_what_the_reference_never_does(pkg):
     with pytest.raises(ValueError):
         m.generate(ids, max_length=8, num_return_sequences=2)
     with pytest.raises(NotImplementedError):
-        m.generate(ids, max_length=8, attention_mask=torch.tensor([[0, 1, 1, 1]]))
+        m.generate(ids, max_length=8, attention_mask=torch.tensor([[1, 1, 1, 0]]))  # right padding (left is supported)
 
 
 @pytest.mark.parametrize("n,ws", [(1_000_000, 8), (10, 3), (7, 8), (0, 2)])

@@ -81,3 +81,115 @@ def test_grpc_drop_in_with_engine(pkg, golden):
             assert r.success and r.response == str(g[f"text_{i % 3}"])  # identical to the unmodified reference's text
     finally:
         server.stop(0)
+
+
+class RowModel:
+    """CPU stand-in with the engine's generate contract for left-padded batches: row-wise deterministic 'generation'
+    (next token = (sum of the row's real tokens + step) % 50), EOS = 7."""
+    def __init__(self):
+        from types import SimpleNamespace
+        self.generation_config = SimpleNamespace(max_length=20, eos_token_id=7, pad_token_id=None)
+        self.calls = []
+
+    def _resolve(self, T, max_length, max_new_tokens, eos, pad):
+        import lms_b200
+        return lms_b200.B200GPT2LMHeadModel._resolve(self, T, max_length, max_new_tokens, eos, pad)
+
+    def generate(self, ids, attention_mask=None, max_new_tokens=None, max_length=None, repetition_penalty=1.0,
+                 eos_token_id=None, pad_token_id=None, **kw):
+        import torch
+        B, T = ids.shape
+        mask = attention_mask if attention_mask is not None else torch.ones_like(ids)
+        new = max_new_tokens if max_new_tokens is not None else max_length - T
+        self.calls.append(B)
+        out = torch.full((B, T + new), 7, dtype=torch.int64)
+        out[:, :T] = ids
+        for b in range(B):
+            base = int((ids[b] * mask[b]).sum())
+            done = False
+            for s in range(new):
+                tok = 7 if done else (base + s) % 50
+                out[b, T + s] = tok
+                done = done or tok == 7
+        return out
+
+
+def test_batching_queue_returns_batch1_results(pkg):
+    """10 concurrent batch-1 callers with different prompt lengths and budgets: coalesced into few batches, each
+    caller gets exactly what its own batch-1 call returns (own length, cut after its EOS)."""
+    import torch
+    from concurrent.futures import ThreadPoolExecutor
+    from importlib import import_module
+    serving = import_module("distributed-lms-raft-llm_b200.serving")
+    eng = RowModel()
+    bm = serving.BatchingModel(eng, max_batch=16, max_wait_ms=150)
+    prompts = [torch.randint(1, 40, (1, n), generator=torch.Generator().manual_seed(n)) for n in (3, 9, 5, 12, 7, 4, 11, 6, 8, 10)]
+    def one(p):
+        return bm.generate(p, max_length=30, num_return_sequences=1, temperature=0.7, top_k=50, top_p=0.9,
+                           repetition_penalty=1.2)
+    try:
+        with ThreadPoolExecutor(10) as ex:
+            outs = list(ex.map(one, prompts))
+    finally:
+        bm.close()
+    assert sum(bm.batches) == 10 and len(bm.batches) <= 3  # coalesced
+    solo = RowModel()
+    for p, o in zip(prompts, outs):
+        ref = solo.generate(p, max_length=30)[0]
+        hit = (ref[p.shape[1]:] == 7).nonzero()
+        ref = ref[:p.shape[1] + int(hit[0]) + 1] if hit.numel() else ref
+        assert o.shape[0] == 1 and torch.equal(o[0], ref)
+    with pytest.raises(ValueError, match="max_length"):
+        serving.BatchingModel(RowModel()).generate(torch.ones((1, 30), dtype=torch.int64), max_length=30)
+
+
+def test_relevance_gate_caches_assignment_embedding(pkg):
+    import torch
+    from importlib import import_module
+    serving = import_module("distributed-lms-raft-llm_b200.serving")
+    calls = []
+    class Tok:
+        def __call__(self, text, **kw):
+            ids = rp.bert_ids(1, 6 + len(text) % 5, seed=len(text), vocab=2000)
+            return {"input_ids": ids, "token_type_ids": torch.zeros_like(ids), "attention_mask": torch.ones_like(ids)}
+    hf = rp.build_bert(seed=6, hidden_size=128, num_hidden_layers=2, num_attention_heads=2, intermediate_size=512,
+                       vocab_size=2000, max_position_embeddings=128)
+    class Counting:
+        def __call__(self, **inputs):
+            calls.append(inputs["input_ids"].shape[1])
+            return hf(**inputs)
+    gate = serving.RelevanceGate(Counting(), Tok(), threshold=0.6)
+    gate._bert = type("B", (), dict(compute_embeddings=staticmethod(rp.compute_embeddings),
+                                    cosine_similarity=staticmethod(rp.cosine_similarity),
+                                    NOT_RELATED_MESSAGE=rp.NOT_RELATED_MESSAGE))
+    text = "the assignment text " * 3
+    r1 = gate.check("first question", text)
+    r2 = gate.check("second question?", text)
+    assert len(calls) == 3 and gate.hits == 1 and gate.misses == 1  # assignment embedded once, two query forwards
+    ref = rp.cosine_similarity(rp.compute_embeddings("first question", hf, Tok()), rp.compute_embeddings(text, hf, Tok()))
+    assert abs(r1[1] - ref) < 1e-6 and r1[0] == rp.relevance_decision(ref)
+    assert gate.answer("q", text, lambda q: "tutor says hi") in ("tutor says hi", rp.NOT_RELATED_MESSAGE)
+    gate.threshold = 2.0  # nothing is relevant: the canned reply of REF/lms_server.py:1270
+    assert gate.answer("q", text, lambda q: "tutor says hi") == rp.NOT_RELATED_MESSAGE
+
+
+@pytest.mark.gpu
+def test_batching_queue_with_engine_equals_batch1(pkg):
+    """Engine behind the queue: every caller's ids equal its own batch-1 engine call (fp32 mode)."""
+    import torch
+    from concurrent.futures import ThreadPoolExecutor
+    from importlib import import_module
+    serving = import_module("distributed-lms-raft-llm_b200.serving")
+    eng = pkg.B200GPT2LMHeadModel.from_hf(rp.build_gpt2("tiny", seed=3), dtype="fp32")
+    eng.generation_config.eos_token_id = 999
+    prompts = [rp.gpt2_prompt_ids(1, n, seed=40 + n, vocab=1000) for n in (5, 17, 9, 30, 12, 8)]
+    solo = [eng.generate(p, max_length=48, repetition_penalty=1.2) for p in prompts]
+    bm = serving.BatchingModel(eng, max_batch=8, max_wait_ms=300)
+    try:
+        with ThreadPoolExecutor(6) as ex:
+            outs = list(ex.map(lambda p: bm.generate(p, max_length=48, repetition_penalty=1.2), prompts))
+    finally:
+        bm.close()
+    assert sum(bm.batches) == 6 and len(bm.batches) <= 2
+    for o, s in zip(outs, solo):
+        assert torch.equal(o, s)
