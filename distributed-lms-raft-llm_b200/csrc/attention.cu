@@ -247,7 +247,7 @@ __global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf
                                                                     const int* __restrict__ len_dev, int len_host,
                                                                     const float* __restrict__ qkv_partial, int ks,
                                                                     const float* __restrict__ qkv_bias, int B,
-                                                                    const int* __restrict__ npad) {
+                                                                    const int* __restrict__ npad, int safe_rows) {
   constexpr int EPL = 8, LPR = 8, KPW = 4, NG = 16, UNR = DK_CHUNK / NG;
   __shared__ __align__(128) bf16 sK[DK_STAGES][DK_CHUNK * 64];
   __shared__ __align__(128) bf16 sV[DK_STAGES][DK_CHUNK * 64];
@@ -256,11 +256,12 @@ __global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf
   __shared__ float sm_m[NG], sm_l[NG], sm_o[NG][64];
   const int h = blockIdx.x, b = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int len = len_dev ? *len_dev : len_host;  // written by a kernel that finished long before this launch
+  // The length counter is bumped by the previous token's finalize kernel, which under programmatic dependent
+  // launch may still be running when this kernel starts: it is read only AFTER the wait.  What may be streamed
+  // before the wait are rows the host knows to be final: [0, safe_rows) (the prompt, written by prefill).
   const size_t base = ((size_t)b * H + h) * Smax * 64;
   const int kp = npad ? npad[b] : 0;  // left padding: the stream starts at the first real token's row
-  const int nkeys = (FUSED ? len - 1 : len) - kp;
-  const int nchunks = (nkeys + DK_CHUNK - 1) / DK_CHUNK;
+  const int early = min(DK_STAGES, max(0, safe_rows - kp) / DK_CHUNK);  // whole chunks that are safe to prefetch
   if (threadIdx.x == 0) {
     for (int s = 0; s < DK_STAGES; ++s) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dk_smem(&full_bar[s])), "r"(1));
@@ -274,11 +275,8 @@ __global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf
   if (warp == 4) {
     // ===== producer: one lane streams the cache rows of this (b,h) =====
     if (lane == 0) {
-      for (int c = 0; c < nchunks; ++c) {
+      auto copy_chunk = [&](int c, int rows) {
         const int s = c % DK_STAGES;
-        const uint32_t ph = (c / DK_STAGES) & 1;
-        dk_wait(&empty_bar[s], ph ^ 1);
-        const int rows = min(DK_CHUNK, nkeys - c * DK_CHUNK);
         const uint32_t bytes = (uint32_t)rows * 128;
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dk_smem(&full_bar[s])),
                      "r"(2 * bytes) : "memory");
@@ -287,11 +285,23 @@ __global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf
                          dk_smem(&sK[s][0])), "l"(kc + off), "r"(bytes), "r"(dk_smem(&full_bar[s])) : "memory");
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                          dk_smem(&sV[s][0])), "l"(vc + off), "r"(bytes), "r"(dk_smem(&full_bar[s])) : "memory");
+      };
+      for (int c = 0; c < early; ++c) copy_chunk(c, DK_CHUNK);  // the ring is empty: no wait needed
+      pdl_wait();
+      const int len = len_dev ? *len_dev : len_host;
+      const int nkeys = (FUSED ? len - 1 : len) - kp;
+      const int nchunks = (nkeys + DK_CHUNK - 1) / DK_CHUNK;
+      for (int c = early; c < nchunks; ++c) {
+        dk_wait(&empty_bar[c % DK_STAGES], ((c / DK_STAGES) & 1) ^ 1);
+        copy_chunk(c, min(DK_CHUNK, nkeys - c * DK_CHUNK));
       }
     }
   } else {
     // ===== consumers =====
-    pdl_wait();  // q (or the c_attn partials) come from the preceding kernel
+    pdl_wait();  // q (or the c_attn partials) come from the preceding kernel; the length counter is final now
+    const int len = len_dev ? *len_dev : len_host;
+    const int nkeys = (FUSED ? len - 1 : len) - kp;
+    const int nchunks = (nkeys + DK_CHUNK - 1) / DK_CHUNK;
     const int g = warp * KPW + lane / LPR;
     const int e0 = (lane % LPR) * EPL;
     float qv[EPL];
@@ -679,7 +689,7 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
         nullptr, npad);
   else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16)
     attn_decode_tma_kernel<false, 64, 2, true><<<grid, DK_THREADS, 0, st>>>((const bf16*)q, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax,
-                                                               len_dev, len_host, nullptr, 0, nullptr, B, npad);
+                                                               len_dev, len_host, nullptr, 0, nullptr, B, npad, 0);
   else {
     tutor_set_error("attn_decode: unsupported dtype combination q=%d kv=%d out=%d", q_dtype, kv_dtype, out_dtype);
     return TUTOR_ERR_ARG;
@@ -690,7 +700,7 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
 
 int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias, void* k, void* v, int kv_dtype,
                         void* out, int out_dtype, int B, int H, int Smax, const int* len_dev, int len_host,
-                        int nsplit, void* split_scratch, const int* npad, cudaStream_t st) {
+                        int nsplit, void* split_scratch, const int* npad, int safe_rows, cudaStream_t st) {
   if (B == 0) return TUTOR_OK;
   ARG_CHECK(kv_dtype == DT_BF16 && out_dtype == DT_BF16, "attn_decode_fused: bf16 cache and output only");
   ARG_CHECK(qkv_partial && qkv_bias && ks >= 1, "attn_decode_fused: bad partials");
@@ -699,7 +709,7 @@ int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias,
   if (nsplit == 1) {
     CUDA_TRY(tutor_launch(attn_decode_tma_kernel<true, 64, 2, true>, dim3(H, B), dim3(DK_THREADS), 0, st, (const bf16*)nullptr,
                           (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B,
-                          npad));
+                          npad, safe_rows));
     KERNEL_LAUNCHED();
     return TUTOR_OK;
   }

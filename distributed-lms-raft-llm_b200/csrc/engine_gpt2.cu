@@ -168,7 +168,8 @@ int forward_decode_fused(tutor_gpt2* e, int lane, int b0, int B) {
     int ks = k_pick_splitk(3 * d, d, e->num_sms);
     TRY(k_gemm_bf16_splitk(xn, (const bf16*)w.qkv.w, B, 3 * d, d, ks, partial, st));
     TRY(k_attn_decode_fused(partial, ks, w.qkv.b, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
-                            e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, npad, st));
+                            e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, npad,
+                            e->cur_T, st));
     ks = k_pick_splitk(d, d, e->num_sms);
     TRY(k_gemm_bf16_splitk(att, (const bf16*)w.proj.w, B, d, d, ks, partial, st));
     TRY(k_reduce_bias_residual_ln(partial, ks, B, d, w.proj.b, x, w.ln2_g, w.ln2_b, eps, nullptr, xn, st));
@@ -186,7 +187,14 @@ int forward_decode_fused(tutor_gpt2* e, int lane, int b0, int B) {
 }
 
 int decode_forward(tutor_gpt2* e, int B) {
-  if (!(e->dt == DT_BF16 && e->use_fused && B <= 128)) return forward(e, B, 1, true);
+  if (!(e->dt == DT_BF16 && e->use_fused && B <= 128)) {
+    // parity (fp32) path: same kernel chain as prefill, with PDL when every GEMM is the weight-streaming GEMV
+    // (M <= 8), all of whose kernels wait before touching dependent data
+    tutor_pdl_enabled = e->use_pdl && e->dt == DT_F32 && B <= 8;
+    int rc = forward(e, B, 1, true);
+    tutor_pdl_enabled = false;
+    return rc;
+  }
   // fork: lanes 1.. wait for everything already queued on the main stream, then all chains run concurrently
   if (e->nlanes > 1) {
     CUDA_TRY(cudaEventRecord(e->ev_fork, e->stream));

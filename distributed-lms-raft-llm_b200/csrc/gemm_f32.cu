@@ -12,8 +12,12 @@ __global__ void __launch_bounds__(256) gemv_f32_kernel(const float* __restrict__
                                                         int M0, int N, int K, GemmEpilogue epi) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = blockIdx.x * 8 + warp;
-  if (n >= N) return;
+  pdl_launch_dependents();
+  if (n >= N) { pdl_wait(); return; }
   const float* w = W + (size_t)n * K;
+  // PDL: the weight row does not depend on the predecessor kernel - pull it towards L2 before waiting for it
+  for (int off = lane * 32; off < K; off += 1024) asm volatile("prefetch.global.L2 [%0];" ::"l"(w + off));
+  pdl_wait();
   float acc[MB];
 #pragma unroll
   for (int m = 0; m < MB; ++m) acc[m] = 0.f;
@@ -109,16 +113,12 @@ int k_gemm_f32(const float* A, const float* W, int M, int N, int K, const GemmEp
   if (M == 0 || N == 0) return TUTOR_OK;
   if (M <= 8 && K % 128 == 0) {
     dim3 grid(ceil_div(N, 8)), block(256);
+#define GEMV_CASE(n) case n: CUDA_TRY(tutor_launch(gemv_f32_kernel<n>, grid, block, 0, st, A, W, 0, N, K, epi)); break;
     switch (M) {
-      case 1: gemv_f32_kernel<1><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
-      case 2: gemv_f32_kernel<2><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
-      case 3: gemv_f32_kernel<3><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
-      case 4: gemv_f32_kernel<4><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
-      case 5: gemv_f32_kernel<5><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
-      case 6: gemv_f32_kernel<6><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
-      case 7: gemv_f32_kernel<7><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
-      default: gemv_f32_kernel<8><<<grid, block, 0, st>>>(A, W, 0, N, K, epi); break;
+      GEMV_CASE(1) GEMV_CASE(2) GEMV_CASE(3) GEMV_CASE(4) GEMV_CASE(5) GEMV_CASE(6) GEMV_CASE(7)
+      default: CUDA_TRY(tutor_launch(gemv_f32_kernel<8>, grid, block, 0, st, A, W, 0, N, K, epi)); break;
     }
+#undef GEMV_CASE
   } else {
     ARG_CHECK(K % BK == 0, "gemm_f32: K=%d must be a multiple of %d", K, BK);
     dim3 grid(ceil_div(N, BN), ceil_div(M, BM)), block(256);

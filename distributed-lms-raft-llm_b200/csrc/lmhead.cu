@@ -27,6 +27,8 @@ __global__ void __launch_bounds__(256) lmhead_argmax_simt_kernel(const float* __
                                                                   float* __restrict__ part_val,
                                                                   int* __restrict__ part_idx) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();
+  pdl_wait();
   float best[MB];
   int besti[MB];
 #pragma unroll
@@ -126,8 +128,8 @@ int launch_simt(const float* x, const WT* wte, int B, int V, int d, const Decode
     const int mb = (B - b0 < 8) ? (B - b0) : 8;
 #define LM_CASE(n)                                                                                              \
   case n:                                                                                                       \
-    lmhead_argmax_simt_kernel<WT, n><<<nblocks, 256, 0, st>>>(x, wte, b0, B, V, d, ds.seen, ds.seen_words,      \
-                                                              ds.penalty, pv, pi);                              \
+    CUDA_TRY(tutor_launch(lmhead_argmax_simt_kernel<WT, n>, dim3(nblocks), dim3(256), 0, st, x, wte, b0, B, V, d,   \
+                          (const uint32_t*)ds.seen, ds.seen_words, ds.penalty, pv, pi));                       \
     break;
     switch (mb) {
       LM_CASE(1) LM_CASE(2) LM_CASE(3) LM_CASE(4) LM_CASE(5) LM_CASE(6) LM_CASE(7) LM_CASE(8)

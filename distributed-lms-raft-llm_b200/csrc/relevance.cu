@@ -67,6 +67,88 @@ __global__ void __launch_bounds__(256, 1) cosine_scan_kernel(const float* __rest
   }
 }
 
+// Second-generation scan: no cross-lane reduction at all.  Every lane owns two corpus rows and 2x32 accumulators;
+// a warp stages [64 rows][16 dims] tiles of its rows in shared memory with cp.async (3 stages) and every query
+// vector read from shared memory (a broadcast LDS.128) feeds 8 FMAs.  fp32 FMA only - the index sets are gated
+// bit-for-bit against the CPU oracle, so no TF32.  QMAX = 32 queries per pass.
+constexpr int SC_ROWS = 64, SC_K = 16, SC_LD = 20, SC_STAGES = 3, SC_QMAX = 32;
+
+__global__ void __launch_bounds__(256, 1) cosine_scan2_kernel(const float* __restrict__ queries,
+                                                               const float* __restrict__ corpus,
+                                                               const float* __restrict__ inv_norm, int Q, int N, int D,
+                                                               float eps, float* __restrict__ scores) {
+  extern __shared__ __align__(16) float sm2[];
+  float* sq = sm2;                                  // [SC_QMAX][D]  (rows >= Q zero-filled)
+  float* qinv = sq + (size_t)SC_QMAX * D;           // [SC_QMAX]
+  float* tiles = qinv + SC_QMAX;                    // [8 warps][SC_STAGES][SC_ROWS][SC_LD]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < SC_QMAX * D / 4; i += blockDim.x)
+    reinterpret_cast<float4*>(sq)[i] = (i < Q * D / 4) ? reinterpret_cast<const float4*>(queries)[i]
+                                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+  __syncthreads();
+  for (int q = warp; q < SC_QMAX; q += 8) {
+    float s = 0.f;
+    for (int i = lane; i < D; i += 32) s += sq[q * D + i] * sq[q * D + i];
+    s = warp_sum(s);
+    if (lane == 0) qinv[q] = 1.0f / fmaxf(sqrtf(s), eps);
+  }
+  __syncthreads();
+  float* wt = tiles + (size_t)warp * SC_STAGES * SC_ROWS * SC_LD;
+  const int nk = D / SC_K;
+  const int ngroups = (N + SC_ROWS - 1) / SC_ROWS;
+  for (int g = blockIdx.x * 8 + warp; g < ngroups; g += gridDim.x * 8) {
+    const int row0 = g * SC_ROWS;
+    auto issue = [&](int kt) {  // one [64][16] tile: 8 x 16-byte cp.async per lane, 4 lanes per 64-byte row segment
+      float* dst = wt + (size_t)(kt % SC_STAGES) * SC_ROWS * SC_LD;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int r = i * 8 + (lane >> 2), c = (lane & 3) * 4;
+        const int row = min(row0 + r, N - 1);
+        const float* src = corpus + (size_t)row * D + kt * SC_K + c;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst + r * SC_LD + c)),
+                     "l"(src));
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    float accA[SC_QMAX], accB[SC_QMAX];
+#pragma unroll
+    for (int q = 0; q < SC_QMAX; ++q) { accA[q] = 0.f; accB[q] = 0.f; }
+    issue(0);
+    if (nk > 1) issue(1);
+    for (int kt = 0; kt < nk; ++kt) {
+      if (kt + 2 < nk) { issue(kt + 2); asm volatile("cp.async.wait_group 2;" ::: "memory"); }
+      else if (kt + 1 < nk) asm volatile("cp.async.wait_group 1;" ::: "memory");
+      else asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncwarp();
+      const float* t = wt + (size_t)(kt % SC_STAGES) * SC_ROWS * SC_LD;
+#pragma unroll
+      for (int c = 0; c < SC_K / 4; ++c) {
+        const float4 ra = *reinterpret_cast<const float4*>(t + lane * SC_LD + c * 4);
+        const float4 rb = *reinterpret_cast<const float4*>(t + (lane + 32) * SC_LD + c * 4);
+        const float* qp = sq + kt * SC_K + c * 4;
+#pragma unroll
+        for (int q = 0; q < SC_QMAX; ++q) {
+          const float4 x = *reinterpret_cast<const float4*>(qp + (size_t)q * D);  // same address in every lane
+          accA[q] = fmaf(ra.x, x.x, accA[q]); accA[q] = fmaf(ra.y, x.y, accA[q]);
+          accA[q] = fmaf(ra.z, x.z, accA[q]); accA[q] = fmaf(ra.w, x.w, accA[q]);
+          accB[q] = fmaf(rb.x, x.x, accB[q]); accB[q] = fmaf(rb.y, x.y, accB[q]);
+          accB[q] = fmaf(rb.z, x.z, accB[q]); accB[q] = fmaf(rb.w, x.w, accB[q]);
+        }
+      }
+      __syncwarp();  // the stage is refilled by the cp.async issued two iterations later
+    }
+    const int ra_row = row0 + lane, rb_row = row0 + lane + 32;
+    const float ca = ra_row < N ? inv_norm[ra_row] : 0.f, cb = rb_row < N ? inv_norm[rb_row] : 0.f;
+#pragma unroll
+    for (int q = 0; q < SC_QMAX; ++q) {
+      if (q < Q) {
+        if (ra_row < N) scores[(size_t)q * N + ra_row] = accA[q] * qinv[q] * ca;
+        if (rb_row < N) scores[(size_t)q * N + rb_row] = accB[q] * qinv[q] * cb;
+      }
+    }
+  }
+}
+
 template <typename T>
 __global__ void row_inv_norm_kernel(const T* __restrict__ x, float* __restrict__ out, int N, int d, float eps) {
   int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -205,23 +287,33 @@ int k_cosine_topk(const float* queries, const void* corpus, int corpus_dtype, co
   float* cand_v = reinterpret_cast<float*>(p);
   p += round_up((size_t)Q * nchunks * k * sizeof(float), 256);
   int32_t* cand_i = reinterpret_cast<int32_t*>(p);
-  const size_t smem = (size_t)Q * d * 4 + (size_t)Q * 4;
   const float eps = 1e-8f;
   const int grid = 148;
-  if (d == 768) {
-    static bool a6 = false;
-    if (!a6) {
-      CUDA_TRY(cudaFuncSetAttribute(cosine_scan_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      a6 = true;
+  const size_t smem2 = ((size_t)SC_QMAX * d + SC_QMAX + (size_t)8 * SC_STAGES * SC_ROWS * SC_LD) * sizeof(float);
+  if (Q <= SC_QMAX && d % SC_K == 0 && smem2 <= 220 * 1024) {
+    static bool a2 = false;
+    if (!a2) {
+      CUDA_TRY(cudaFuncSetAttribute(cosine_scan2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+      a2 = true;
     }
-    cosine_scan_kernel<6><<<grid, 256, smem, st>>>(queries, (const float*)corpus, corpus_inv_norm, Q, N, eps, scores);
+    cosine_scan2_kernel<<<grid, 256, smem2, st>>>(queries, (const float*)corpus, corpus_inv_norm, Q, N, d, eps, scores);
   } else {
-    static bool a1 = false;
-    if (!a1) {
-      CUDA_TRY(cudaFuncSetAttribute(cosine_scan_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      a1 = true;
+    const size_t smem = (size_t)Q * d * 4 + (size_t)Q * 4;
+    if (d == 768) {
+      static bool a6 = false;
+      if (!a6) {
+        CUDA_TRY(cudaFuncSetAttribute(cosine_scan_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        a6 = true;
+      }
+      cosine_scan_kernel<6><<<grid, 256, smem, st>>>(queries, (const float*)corpus, corpus_inv_norm, Q, N, eps, scores);
+    } else {
+      static bool a1 = false;
+      if (!a1) {
+        CUDA_TRY(cudaFuncSetAttribute(cosine_scan_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        a1 = true;
+      }
+      cosine_scan_kernel<1><<<grid, 256, smem, st>>>(queries, (const float*)corpus, corpus_inv_norm, Q, N, eps, scores);
     }
-    cosine_scan_kernel<1><<<grid, 256, smem, st>>>(queries, (const float*)corpus, corpus_inv_norm, Q, N, eps, scores);
   }
   KERNEL_LAUNCHED();
   topk_chunk_kernel<<<dim3(nchunks, Q), 256, 0, st>>>(scores, N, k, cand_v, cand_i, idx_base);

@@ -243,3 +243,24 @@ def test_left_padded_batch_matches_hf(pkg, tiny_hf, golden):
     assert agree > 0.8
     with pytest.raises(NotImplementedError):
         eng.generate(ids, attention_mask=torch.flip(mask, dims=[1]), max_new_tokens=4)  # right padding
+
+
+def test_launch_modes_are_bit_identical(pkg, small_hf, monkeypatch):
+    """CUDA graph replay, eager launches, programmatic dependent launch on/off: the same kernels in the same order,
+    so the ids must be identical - a guard against ordering hazards of the PDL chain (the length counter, the
+    split-K partial buffers and the KV rows are all produced and consumed by neighbouring kernels)."""
+    ids = rp.gpt2_prompt_ids(16, 200, seed=31)
+    outs = {}
+    for name, env in (("default", {}), ("no_pdl", {"TUTOR_NO_PDL": "1"}), ("no_graph", {"TUTOR_NO_GRAPH": "1"}),
+                      ("no_pdl_no_graph", {"TUTOR_NO_PDL": "1", "TUTOR_NO_GRAPH": "1"})):
+        for k in ("TUTOR_NO_PDL", "TUTOR_NO_GRAPH"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        eng = pkg.B200GPT2LMHeadModel.from_hf(small_hf, dtype="bf16")
+        runs = [eng.generate(ids, max_new_tokens=48, repetition_penalty=1.2) for _ in range(3)]
+        assert all(torch.equal(r, runs[0]) for r in runs), name
+        outs[name] = runs[0]
+        del eng
+    for name, o in outs.items():
+        assert torch.equal(o, outs["no_pdl_no_graph"]), name

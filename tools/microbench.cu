@@ -124,12 +124,12 @@ int main() {
 #define ATT(NAME, ...)                                                                                              \
       t = time_graph(st, 48, false, [&](int i) { __VA_ARGS__; });                                                    \
       printf("attn %-42s %6.2f us  %7.2f TB/s\n", NAME, t, mb / t * 1e-3);
-      ATT("register kernel (128 thr)", (attn_decode_kernel<bf16, bf16, bf16, true, false><<<dim3(12, 64), 128, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, nullptr)));
-      ATT("ring chunk 64 x 2 stages", (attn_decode_tma_kernel<false, 64, 2, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64)));
-      ATT("ring chunk 64 x 2 stages, no math", (attn_decode_tma_kernel<false, 64, 2, false><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64)));
-      ATT("ring chunk 32 x 4 stages", (attn_decode_tma_kernel<false, 32, 4, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64)));
-      ATT("ring chunk 32 x 4 stages, no math", (attn_decode_tma_kernel<false, 32, 4, false><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64)));
-      ATT("ring chunk 16 x 8 stages", (attn_decode_tma_kernel<false, 16, 8, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64)));
+      ATT("register kernel (128 thr)", (attn_decode_kernel<bf16, bf16, bf16, true, false><<<dim3(12, 64), 128, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, nullptr, nullptr)));
+      ATT("ring chunk 64 x 2 stages", (attn_decode_tma_kernel<false, 64, 2, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
+      ATT("ring chunk 64 x 2 stages, no math", (attn_decode_tma_kernel<false, 64, 2, false><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
+      ATT("ring chunk 32 x 4 stages", (attn_decode_tma_kernel<false, 32, 4, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
+      ATT("ring chunk 32 x 4 stages, no math", (attn_decode_tma_kernel<false, 32, 4, false><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
+      ATT("ring chunk 16 x 8 stages", (attn_decode_tma_kernel<false, 16, 8, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
     }
 #endif
     cudaFree(big); cudaFree(sink);
