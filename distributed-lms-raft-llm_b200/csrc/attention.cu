@@ -529,40 +529,54 @@ __device__ __forceinline__ void mma_bf16_16816(float* c, const uint32_t* a, uint
       : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
+__device__ __forceinline__ float fast_exp2(float x) {  // one MUFU.EX2; exp2(-inf) = 0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 p = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&p);
 }
 
-template <bool CAUSAL>
+template <bool CAUSAL, bool PADDED>
 __global__ void __launch_bounds__(128) attn_prefill_mma_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc,
                                                                 const bf16* __restrict__ vc, bf16* __restrict__ out,
                                                                 int H, int T, int Smax, const int* __restrict__ npad) {
+  // 128 queries per CTA, 32 per warp (two m16 row blocks): every K/V fragment fetched from shared memory with
+  // ldmatrix feeds two MMAs, which halves the shared-memory traffic per FLOP of the 16-rows-per-warp layout
+  constexpr int RB = 2;
   __shared__ __align__(128) uint8_t tiles[2][2][64 * 128];  // [stage][K|V][64 keys x 128 B], 16-byte chunks XOR-swizzled
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int d = H * 64;
-  const int q0 = qt * 64 + warp * 16;
-  uint32_t qf[4][4];
-  {
-    const bf16* p0 = q + ((size_t)b * T + min(q0 + g, T - 1)) * d + h * 64 + 2 * t;
-    const bf16* p1 = q + ((size_t)b * T + min(q0 + g + 8, T - 1)) * d + h * 64 + 2 * t;
+  const int q0 = qt * 128 + warp * 32;
+  uint32_t qf[RB][4][4];
+#pragma unroll
+  for (int rb = 0; rb < RB; ++rb) {
+    const bf16* p0 = q + ((size_t)b * T + min(q0 + rb * 16 + g, T - 1)) * d + h * 64 + 2 * t;
+    const bf16* p1 = q + ((size_t)b * T + min(q0 + rb * 16 + g + 8, T - 1)) * d + h * 64 + 2 * t;
 #pragma unroll
     for (int kk = 0; kk < 4; ++kk) {
-      qf[kk][0] = *reinterpret_cast<const uint32_t*>(p0 + kk * 16);
-      qf[kk][1] = *reinterpret_cast<const uint32_t*>(p1 + kk * 16);
-      qf[kk][2] = *reinterpret_cast<const uint32_t*>(p0 + kk * 16 + 8);
-      qf[kk][3] = *reinterpret_cast<const uint32_t*>(p1 + kk * 16 + 8);
+      qf[rb][kk][0] = *reinterpret_cast<const uint32_t*>(p0 + kk * 16);
+      qf[rb][kk][1] = *reinterpret_cast<const uint32_t*>(p1 + kk * 16);
+      qf[rb][kk][2] = *reinterpret_cast<const uint32_t*>(p0 + kk * 16 + 8);
+      qf[rb][kk][3] = *reinterpret_cast<const uint32_t*>(p1 + kk * 16 + 8);
     }
   }
-  float o[8][4];
+  float o[RB][8][4];
+  float mrow[RB][2], lrow[RB][2];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
-  float m0 = -CUDART_INF_F, m1 = -CUDART_INF_F, l0 = 0.f, l1 = 0.f;
+  for (int rb = 0; rb < RB; ++rb) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { o[rb][j][0] = o[rb][j][1] = o[rb][j][2] = o[rb][j][3] = 0.f; }
+    mrow[rb][0] = mrow[rb][1] = -CUDART_INF_F;
+    lrow[rb][0] = lrow[rb][1] = 0.f;
+  }
   const size_t base = ((size_t)b * H + h) * Smax * 64;
   const int nkt_all = (T + 63) / 64;
-  const int nkt = CAUSAL ? min(qt + 1, nkt_all) : nkt_all;
-  const int kp = npad ? npad[b] : 0;  // left padding, see attn_prefill_kernel
+  const int nkt = CAUSAL ? min(2 * (qt + 1), nkt_all) : nkt_all;
+  const int kp = PADDED ? npad[b] : 0;  // left padding, see attn_prefill_kernel (compiled out when unpadded)
 
   auto load_tile = [&](int kt, int stage) {
 #pragma unroll
@@ -578,6 +592,10 @@ __global__ void __launch_bounds__(128) attn_prefill_mma_kernel(const bf16* __res
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
 
+  // Raw scores stay unscaled; the 1/8 scale and log2(e) are folded into one FFMA in front of ex2.  Masking
+  // (sequence end, causal diagonal, left padding) is only evaluated on tiles that can contain a masked key -
+  // the per-element scalar work of the softmax, not the MMAs, bounds this kernel.
+  constexpr float C = 0.125f * 1.4426950408889634f;
   load_tile(0, 0);
   for (int kt = 0; kt < nkt; ++kt) {
     const int stage = kt & 1;
@@ -590,79 +608,102 @@ __global__ void __launch_bounds__(128) attn_prefill_mma_kernel(const bf16* __res
     __syncthreads();
     const uint8_t* sK = tiles[stage][0];
     const uint8_t* sV = tiles[stage][1];
-    float s[8][4];
+    // causal: this warp's rows are q0..q0+31; tiles entirely above its diagonal contribute nothing
+    const bool tile_dead = CAUSAL && kt * 64 > q0 + 31;
+    if (!tile_dead) {
+      float s[RB][8][4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
-      uint32_t kb[8];
-      const int row = j * 8 + (lane & 7);
+      for (int j = 0; j < 8; ++j) {
+        uint32_t kb[8];
+        const int row = j * 8 + (lane & 7);
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        const int ch = half * 4 + (lane >> 3);
-        ldmatrix_x4(&kb[half * 4], sK + row * 128 + ((ch ^ (row & 7)) << 4));
+        for (int half = 0; half < 2; ++half) {
+          const int ch = half * 4 + (lane >> 3);
+          ldmatrix_x4(&kb[half * 4], sK + row * 128 + ((ch ^ (row & 7)) << 4));
+        }
+#pragma unroll
+        for (int rb = 0; rb < RB; ++rb) {
+          s[rb][j][0] = s[rb][j][1] = s[rb][j][2] = s[rb][j][3] = 0.f;
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) mma_bf16_16816(s[rb][j], qf[rb][kk], kb[2 * kk], kb[2 * kk + 1]);
+        }
+      }
+      const bool tile_masked = (kt * 64 + 63 >= T) || (CAUSAL && kt * 64 + 63 > q0) || (PADDED && kt * 64 < kp);
+      uint32_t pa[RB][4][4];
+#pragma unroll
+      for (int rb = 0; rb < RB; ++rb) {
+        if (tile_masked) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+              const int key = kt * 64 + j * 8 + 2 * t + (r & 1);
+              const int qrow = q0 + rb * 16 + g + (r >> 1) * 8;
+              if (key >= T || (CAUSAL && key > qrow) || (PADDED && key < kp && qrow >= kp)) s[rb][j][r] = -CUDART_INF_F;
+            }
+          }
+        }
+        float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          mx0 = fmaxf(mx0, fmaxf(s[rb][j][0], s[rb][j][1]));
+          mx1 = fmaxf(mx1, fmaxf(s[rb][j][2], s[rb][j][3]));
+        }
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        // key 0 is visible to every row in tile 0, so the running maxima are finite from the first tile on
+        const float mn0 = fmaxf(mrow[rb][0], mx0), mn1 = fmaxf(mrow[rb][1], mx1);
+        const float c0 = fast_exp2((mrow[rb][0] - mn0) * C), c1 = fast_exp2((mrow[rb][1] - mn1) * C);
+        const float b0 = mn0 * C, b1 = mn1 * C;
+        float l0 = lrow[rb][0] * c0, l1 = lrow[rb][1] * c1;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { o[rb][j][0] *= c0; o[rb][j][1] *= c0; o[rb][j][2] *= c1; o[rb][j][3] *= c1; }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float p0 = fast_exp2(fmaf(s[rb][j][0], C, -b0)), p1 = fast_exp2(fmaf(s[rb][j][1], C, -b0));
+          const float p2 = fast_exp2(fmaf(s[rb][j][2], C, -b1)), p3 = fast_exp2(fmaf(s[rb][j][3], C, -b1));
+          l0 += p0 + p1; l1 += p2 + p3;
+          pa[rb][j >> 1][(j & 1) * 2] = pack_bf16x2(p0, p1);
+          pa[rb][j >> 1][(j & 1) * 2 + 1] = pack_bf16x2(p2, p3);
+        }
+        lrow[rb][0] = l0; lrow[rb][1] = l1;
+        mrow[rb][0] = mn0; mrow[rb][1] = mn1;
       }
 #pragma unroll
-      for (int kk = 0; kk < 4; ++kk) mma_bf16_16816(s[j], qf[kk], kb[2 * kk], kb[2 * kk + 1]);
-    }
-    float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F;
+      for (int kk = 0; kk < 4; ++kk) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+        for (int jp = 0; jp < 4; ++jp) {
+          const int mi = lane >> 3;
+          const int krow = kk * 16 + (mi & 1) * 8 + (lane & 7);
+          const int ch = 2 * jp + (mi >> 1);
+          uint32_t vb[4];
+          ldmatrix_x4_trans(vb, sV + krow * 128 + ((ch ^ (krow & 7)) << 4));
 #pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int key = kt * 64 + j * 8 + 2 * t + (r & 1);
-        const int qrow = q0 + g + (r >> 1) * 8;
-        float v = s[j][r] * 0.125f;
-        if (key >= T || (CAUSAL && key > qrow) || (key < kp && qrow >= kp)) v = -CUDART_INF_F;
-        s[j][r] = v;
-      }
-      mx0 = fmaxf(mx0, fmaxf(s[j][0], s[j][1]));
-      mx1 = fmaxf(mx1, fmaxf(s[j][2], s[j][3]));
-    }
-    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-    // key 0 is visible to every row in tile 0, so the running maxima are finite from the first tile on
-    const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
-    const float c0 = __expf(m0 - mn0), c1 = __expf(m1 - mn1);
-    l0 *= c0; l1 *= c1;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { o[j][0] *= c0; o[j][1] *= c0; o[j][2] *= c1; o[j][3] *= c1; }
-    uint32_t pa[4][4];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float p0 = __expf(s[j][0] - mn0), p1 = __expf(s[j][1] - mn0);
-      const float p2 = __expf(s[j][2] - mn1), p3 = __expf(s[j][3] - mn1);
-      l0 += p0 + p1; l1 += p2 + p3;
-      pa[j >> 1][(j & 1) * 2] = pack_bf16x2(p0, p1);
-      pa[j >> 1][(j & 1) * 2 + 1] = pack_bf16x2(p2, p3);
-    }
-#pragma unroll
-    for (int kk = 0; kk < 4; ++kk) {
-#pragma unroll
-      for (int jp = 0; jp < 4; ++jp) {
-        const int mi = lane >> 3;
-        const int krow = kk * 16 + (mi & 1) * 8 + (lane & 7);
-        const int ch = 2 * jp + (mi >> 1);
-        uint32_t vb[4];
-        ldmatrix_x4_trans(vb, sV + krow * 128 + ((ch ^ (krow & 7)) << 4));
-        mma_bf16_16816(o[2 * jp], pa[kk], vb[0], vb[1]);
-        mma_bf16_16816(o[2 * jp + 1], pa[kk], vb[2], vb[3]);
+          for (int rb = 0; rb < RB; ++rb) {
+            mma_bf16_16816(o[rb][2 * jp], pa[rb][kk], vb[0], vb[1]);
+            mma_bf16_16816(o[rb][2 * jp + 1], pa[rb][kk], vb[2], vb[3]);
+          }
+        }
       }
     }
-    m0 = mn0; m1 = mn1;
     __syncthreads();  // everyone is done with this stage before the next iteration's cp.async refills it
   }
-  l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-  l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-  const float i0 = 1.0f / l0, i1 = 1.0f / l1;
-  const int r0 = q0 + g, r1 = q0 + g + 8;
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    if (r0 < T)
-      *reinterpret_cast<uint32_t*>(out + ((size_t)b * T + r0) * d + h * 64 + j * 8 + 2 * t) =
-          pack_bf16x2(o[j][0] * i0, o[j][1] * i0);
-    if (r1 < T)
-      *reinterpret_cast<uint32_t*>(out + ((size_t)b * T + r1) * d + h * 64 + j * 8 + 2 * t) =
-          pack_bf16x2(o[j][2] * i1, o[j][3] * i1);
+  for (int rb = 0; rb < RB; ++rb) {
+    float l0 = lrow[rb][0], l1 = lrow[rb][1];
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float i0 = 1.0f / l0, i1 = 1.0f / l1;
+    const int r0 = q0 + rb * 16 + g, r1 = r0 + 8;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (r0 < T)
+        *reinterpret_cast<uint32_t*>(out + ((size_t)b * T + r0) * d + h * 64 + j * 8 + 2 * t) =
+            pack_bf16x2(o[rb][j][0] * i0, o[rb][j][1] * i0);
+      if (r1 < T)
+        *reinterpret_cast<uint32_t*>(out + ((size_t)b * T + r1) * d + h * 64 + j * 8 + 2 * t) =
+            pack_bf16x2(o[rb][j][2] * i1, o[rb][j][3] * i1);
+    }
   }
 }
 
@@ -731,13 +772,15 @@ int k_attn_prefill(const void* q, int q_dtype, const void* k, const void* v, int
     attn_prefill_kernel<float, float, float, false><<<grid, block, 0, st>>>(
         (const float*)q, (const float*)k, (const float*)v, (float*)out, H, T, Smax, causal, npad);
   else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16) {
-    dim3 g2(ceil_div(T, 64), H, B);
-    if (causal)
-      attn_prefill_mma_kernel<true><<<g2, 128, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)out, H, T,
-                                                        Smax, npad);
-    else
-      attn_prefill_mma_kernel<false><<<g2, 128, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)out, H,
-                                                         T, Smax, npad);
+    dim3 g2(ceil_div(T, 128), H, B);
+#define PF_LAUNCH(C, P)                                                                                          \
+  attn_prefill_mma_kernel<C, P><<<g2, 128, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)out, H, T, \
+                                                    Smax, npad)
+    if (causal && npad) PF_LAUNCH(true, true);
+    else if (causal) PF_LAUNCH(true, false);
+    else if (npad) PF_LAUNCH(false, true);
+    else PF_LAUNCH(false, false);
+#undef PF_LAUNCH
   }
   else {
     tutor_set_error("attn_prefill: unsupported dtype combination q=%d kv=%d out=%d", q_dtype, kv_dtype, out_dtype);

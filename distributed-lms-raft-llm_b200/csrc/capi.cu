@@ -35,6 +35,21 @@ int tutor_cuda_fail(cudaError_t e, const char* what, const char* file, int line)
   return TUTOR_ERR_CUDA;
 }
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute: remember (function, device) pairs so that a
+// process driving several GPUs sets it on each of them, and only once
+int tutor_set_max_smem(const void* func, int bytes) {
+  static std::mutex mu;
+  static std::vector<std::pair<const void*, int>> done;
+  int dev = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(mu);
+  for (auto& p : done)
+    if (p.first == func && p.second == dev) return TUTOR_OK;
+  CUDA_TRY(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  done.emplace_back(func, dev);
+  return TUTOR_OK;
+}
+
 void tutor_count_launches(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 int tutor_require_device(int device) {

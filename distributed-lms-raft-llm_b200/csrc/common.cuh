@@ -23,6 +23,7 @@ int tutor_cuda_fail(cudaError_t e, const char* what, const char* file, int line)
     if (_e != cudaSuccess) return tutor_cuda_fail(_e, #expr, __FILE__, __LINE__); \
   } while (0)
 void tutor_count_launches(uint64_t n);
+int tutor_set_max_smem(const void* func, int bytes);  // once per (kernel, device)
 // after every <<<>>>: count the launch (tutor_launch_count) and surface launch-configuration errors
 #define KERNEL_LAUNCHED()        \
   do {                           \

@@ -54,6 +54,7 @@ struct tutor_gpt2 {
   size_t partial_lane_elems = 0, lm_scratch_lane_bytes = 0;
   int num_sms = 148;
   bool use_fused = true, use_pdl = true;
+  bool use_ln_gemv = false;  // TUTOR_LN_GEMV=1: LayerNorm folded into the fp32 decode GEMVs - measured slower (2213 vs 2560 tok/s)
   // Decode lanes: the batch is cut into micro-batches whose kernel chains run concurrently (own stream, own
   // length counter), so one lane's latency-bound GEMM/reduce chain overlaps the other's bandwidth-bound attention.
   static constexpr int MAX_LANES = 4;
@@ -107,9 +108,11 @@ int forward(tutor_gpt2* e, int B, int T, bool decode) {
   bf16* xn_b = dt == DT_BF16 ? (bf16*)e->xn : nullptr;
   const int* npad = e->padded ? e->npad : nullptr;
   TRY(k_gpt2_embed(e->ids, e->ids_ld, len_dev, T, e->wte, dt, e->wpe, d, e->x, M, npad, st));
+  // parity-mode decode of a few rows: LayerNorms are folded into the GEMVs that consume them (gemv_f32_ln_kernel)
+  const bool ln_in_gemv = e->use_ln_gemv && decode && dt == DT_F32 && M <= 8 && (size_t)M * d * 4 <= 48 * 1024;
   for (int l = 0; l < e->L; ++l) {
     const Gpt2Layer& w = e->layers[l];
-    TRY(k_layernorm(e->x, 1, 0, w.ln1_g, w.ln1_b, e->cfg.layer_norm_epsilon, xn_f, xn_b, M, d, st));
+    if (!ln_in_gemv) TRY(k_layernorm(e->x, 1, 0, w.ln1_g, w.ln1_b, e->cfg.layer_norm_epsilon, xn_f, xn_b, M, d, st));
     GemmEpilogue qe{};  // c_attn + split + cache append (modeling_gpt2.py:185-196)
     qe.bias = w.qkv.b;
     qe.out_f32 = dt == DT_F32 ? (float*)e->q : nullptr;
@@ -117,7 +120,11 @@ int forward(tutor_gpt2* e, int B, int T, bool decode) {
     qe.ldo = d; qe.qkv_mode = 1; qe.kv_dtype = dt;
     qe.kcache = e->kcache(l); qe.vcache = e->vcache(l);
     qe.d = d; qe.H = e->H; qe.Smax = e->Smax; qe.T = T; qe.pos0 = 0; qe.pos_dev = len_dev;
-    TRY(gemm(e, e->xn, w.qkv, M, qe));
+    if (ln_in_gemv)
+      TRY(k_gemv_f32_ln(e->x, w.ln1_g, w.ln1_b, e->cfg.layer_norm_epsilon, (const float*)w.qkv.w, M, w.qkv.N, w.qkv.K, qe,
+                        nullptr, st));
+    else
+      TRY(gemm(e, e->xn, w.qkv, M, qe));
     if (decode)
       TRY(k_attn_decode(e->q, dt, e->kcache(l), e->vcache(l), dt, e->att, dt, B, e->H, e->Smax, e->counters, 0, npad, st));
     else
@@ -125,17 +132,24 @@ int forward(tutor_gpt2* e, int B, int T, bool decode) {
     GemmEpilogue pe{};  // attn c_proj + residual (modeling_gpt2.py:223, 282)
     pe.bias = w.proj.b; pe.residual = e->x; pe.out_f32 = e->x; pe.ldo = d;
     TRY(gemm(e, e->att, w.proj, M, pe));
-    TRY(k_layernorm(e->x, 1, 0, w.ln2_g, w.ln2_b, e->cfg.layer_norm_epsilon, xn_f, xn_b, M, d, st));
+    if (!ln_in_gemv) TRY(k_layernorm(e->x, 1, 0, w.ln2_g, w.ln2_b, e->cfg.layer_norm_epsilon, xn_f, xn_b, M, d, st));
     GemmEpilogue fe{};  // c_fc + gelu_new (modeling_gpt2.py:239-240)
     fe.bias = w.fc.b; fe.act = ACT_GELU_TANH; fe.ldo = 4 * d;
     fe.out_f32 = dt == DT_F32 ? (float*)e->hbuf : nullptr;
     fe.out_bf16 = dt == DT_BF16 ? (bf16*)e->hbuf : nullptr;
-    TRY(gemm(e, e->xn, w.fc, M, fe));
+    if (ln_in_gemv)
+      TRY(k_gemv_f32_ln(e->x, w.ln2_g, w.ln2_b, e->cfg.layer_norm_epsilon, (const float*)w.fc.w, M, w.fc.N, w.fc.K, fe,
+                        nullptr, st));
+    else
+      TRY(gemm(e, e->xn, w.fc, M, fe));
     GemmEpilogue oe{};  // mlp c_proj + residual (modeling_gpt2.py:241, 307)
     oe.bias = w.proj2.b; oe.residual = e->x; oe.out_f32 = e->x; oe.ldo = d;
     TRY(gemm(e, e->hbuf, w.proj2, M, oe));
   }
   // ln_f on the last position of every row only (logits_to_keep = 1, HF/generation/utils.py:2490-2491)
+  if (ln_in_gemv)  // folded into the LM-head kernel; CTA 0 also leaves ln_f(x) in xn_last for tutor_gpt2_logits
+    return k_lmhead_argmax_ln(e->x, dt, e->wte, dt, B, e->V, d, e->dstate(), e->lm_scratch, e->lnf_g, e->lnf_b,
+                              e->cfg.layer_norm_epsilon, (float*)e->xn_last, st);
   TRY(k_layernorm(e->x, T, T - 1, e->lnf_g, e->lnf_b, e->cfg.layer_norm_epsilon,
                   dt == DT_F32 ? (float*)e->xn_last : nullptr, dt == DT_BF16 ? (bf16*)e->xn_last : nullptr, B, d, st));
   TRY(k_lmhead_argmax(e->xn_last, dt, e->wte, dt, B, e->V, d, e->dstate(), e->lm_scratch, st));
@@ -415,6 +429,7 @@ int tutor_gpt2_create(const tutor_gpt2_config* cfg, int device, tutor_gpt2_t** o
   e->use_graph = getenv("TUTOR_NO_GRAPH") == nullptr;
   e->use_fused = getenv("TUTOR_NO_FUSED") == nullptr;  // debugging aids: unfused decode kernels / no PDL
   e->use_pdl = getenv("TUTOR_NO_PDL") == nullptr;
+  e->use_ln_gemv = getenv("TUTOR_LN_GEMV") != nullptr;
   {
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) e->num_sms = prop.multiProcessorCount;

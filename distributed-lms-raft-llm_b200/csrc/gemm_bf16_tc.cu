@@ -23,7 +23,9 @@ namespace {
 
 constexpr int BM = 128, BK = 64, UMMA_K = 16;
 constexpr int NTHREADS = 192;        // decode flavours: TMA warp, MMA warp, 4 epilogue warps
-constexpr int NTHREADS_WIDE = 320;   // row-major (prefill) flavour: 8 epilogue warps, two per TMEM lane quadrant
+constexpr int NTHREADS_WIDE = 320;   // one-tile row-major flavour: 8 epilogue warps, two per TMEM lane quadrant
+constexpr int PERSIST_EPI_WARPS = 16;  // persistent flavour: four warps per TMEM lane quadrant (epilogue issue-bound)
+constexpr int NTHREADS_PERSIST = 64 + 32 * PERSIST_EPI_WARPS;
 enum { EPI_ROWMAJOR = 0, EPI_SWAPPED = 1, EPI_ARGMAX = 2, EPI_PARTIAL = 3 };
 
 // Phase timestamps of CTA (0,0,0) for tools/microbench.cu (compiled in only with -DTUTOR_TRACE)
@@ -402,6 +404,138 @@ __global__ void __launch_bounds__(EPI == EPI_ROWMAJOR ? NTHREADS_WIDE : NTHREADS
   }
 }
 
+// ------------------------------------------------------------------------- persistent row-major GEMM
+// Prefill / BERT flavour (M = tokens).  One CTA per SM walks a static list of 128 x BN output tiles; the TMA
+// producer and the MMA issuer run ahead into the next tile while the 8 epilogue warps are still draining the
+// previous one: the accumulator is double-buffered in TMEM (2 x BN columns) and handed over through
+// tmem_full / tmem_empty mbarriers.  The one-tile-per-CTA kernel above spends most of a tile's life in its epilogue
+// (~25 instructions per output element on 4-8 warps) with the tensor pipe idle; here the two overlap.
+// Tiles are ordered m-fastest, so the CTAs running at any moment share one weight tile in L2.
+template <int BN> struct PersistLayout {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (192 * 1024) / STAGE_BYTES;  // 4 stages at BN=256, 6 at BN=128
+  static constexpr int TILE_BYTES = STAGES * STAGE_BYTES;
+  static constexpr int TOTAL = TILE_BYTES + 256 + 1024;
+};
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <int BN>
+__global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                            const __grid_constant__ CUtensorMap tmB,
+                                                                            int M, int N, int K, GemmEpilogue epi) {
+  using L = PersistLayout<BN>;
+  constexpr int TMEM_COLS = 2 * BN;  // two accumulators; 256 or 512 columns (power of two)
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + L::TILE_BYTES);
+  uint64_t* empty_bar = full_bar + L::STAGES;
+  uint64_t* tmem_full_bar = empty_bar + L::STAGES;  // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;     // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nk = K / BK;
+  const int m_tiles = (M + BM - 1) / BM, n_tiles = (N + BN - 1) / BN;
+  const int ntiles = m_tiles * n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+    for (int s = 0; s < L::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], PERSIST_EPI_WARPS); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer: runs through all of this CTA's tiles back to back =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const int a_row0 = (t % m_tiles) * BM, b_row0 = (t / m_tiles) * BN;
+        for (int kb = 0; kb < nk; ++kb, ++it) {
+          const int s = it % L::STAGES;
+          mbar_wait(&empty_bar[s], ((it / L::STAGES) & 1) ^ 1, 0);
+          mbar_expect_tx(&full_bar[s], L::STAGE_BYTES);
+          uint8_t* sa = tiles + s * L::STAGE_BYTES;
+          tma_load_2d(sa, &tmA, &full_bar[s], kb * BK, a_row0);
+          tma_load_2d(sa + L::A_BYTES, &tmB, &full_bar[s], kb * BK, b_row0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: accumulator (ti & 1) once the epilogue has drained its previous contents =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+      uint32_t it = 0, ti = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++ti) {
+        const uint32_t acc = ti & 1;
+        mbar_wait(&tmem_empty_bar[acc], ((ti >> 1) & 1) ^ 1, 3);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < nk; ++kb, ++it) {
+          const int s = it % L::STAGES;
+          mbar_wait(&full_bar[s], (it / L::STAGES) & 1, 1);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(tiles + s * L::STAGE_BYTES);
+          const uint32_t sb = sa + L::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            tc_mma_bf16(d_tmem, umma_desc_sw128(sa + k * UMMA_K * 2), umma_desc_sw128(sb + k * UMMA_K * 2), idesc,
+                        (kb | k) != 0);
+          tc_commit(&empty_bar[s]);
+        }
+        tc_commit(&tmem_full_bar[acc]);
+      }
+    }
+  } else {
+    // ===== epilogue: warp w reads TMEM lanes of quadrant w % 4 and column slice (w - 2) / 4 of the tile =====
+    constexpr int SLICE = BN / (PERSIST_EPI_WARPS / 4);
+    const int quad = warp & 3, half = (warp - 2) >> 2;
+    uint32_t ti = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++ti) {
+      const int a_row0 = (t % m_tiles) * BM, b_row0 = (t / m_tiles) * BN;
+      const uint32_t acc = ti & 1;
+      mbar_wait(&tmem_full_bar[acc], (ti >> 1) & 1, 2);
+      tc_fence_after();
+      const int row = a_row0 + quad * 32 + lane;
+      const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quad * 32) << 16);
+      const int c_begin = half * SLICE, c_end = c_begin + SLICE;
+      for (int c0 = c_begin; c0 < c_end; c0 += 32) {
+        float v[32];
+        tc_ld32(taddr + c0, v);
+        if (c0 + 32 >= c_end) {  // last read of this accumulator by this warp: hand it back before the stores
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        }
+        if (row < M && b_row0 + c0 < N) store_run32(epi, row, b_row0 + c0, N, v);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+  }
+}
+
 // ------------------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -464,12 +598,7 @@ template <int BN, int EPI>
 int launch(const bf16* A, int rowsA, const bf16* B, int rowsB, int K, const GemmEpilogue& epi, const ArgmaxArgs& am,
            cudaStream_t st, int ks = 1) {
   using L = SmemLayout<BN>;
-  static bool attr_done = false;  // per instantiation; racing first calls set the same value
-  if (!attr_done) {
-    CUDA_TRY(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  L::TOTAL));
-    attr_done = true;
-  }
+  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(gemm_bf16_tcgen05_kernel<BN, EPI>), L::TOTAL));
   CUtensorMap ta, tb, tc;
   TRY(make_map(&ta, A, rowsA, K, BM));
   TRY(make_map(&tb, B, rowsB, K, BN));
@@ -479,6 +608,23 @@ int launch(const bf16* A, int rowsA, const bf16* B, int rowsB, int K, const Gemm
   CUDA_TRY(tutor_launch(gemm_bf16_tcgen05_kernel<BN, EPI>, grid, dim3(EPI == EPI_ROWMAJOR ? NTHREADS_WIDE : NTHREADS),
                         (size_t)L::TOTAL, st, ta, tb, tc, rowsA,
                         rowsB, K, epi, am));
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+
+template <int BN>
+int launch_persistent(const bf16* A, int M, const bf16* W, int N, int K, const GemmEpilogue& epi, cudaStream_t st) {
+  using L = PersistLayout<BN>;
+  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(gemm_bf16_persistent_kernel<BN>), L::TOTAL));
+  CUtensorMap ta, tb;
+  TRY(make_map(&ta, A, M, K, BM));
+  TRY(make_map(&tb, W, N, K, BN));
+  int dev = 0, sms = 148;
+  CUDA_TRY(cudaGetDevice(&dev));
+  CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int ntiles = ceil_div(M, BM) * ceil_div(N, BN);
+  CUDA_TRY(tutor_launch(gemm_bf16_persistent_kernel<BN>, dim3(ntiles < sms ? ntiles : sms), dim3(NTHREADS_PERSIST),
+                        (size_t)L::TOTAL, st, ta, tb, M, N, K, epi));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }
@@ -503,6 +649,11 @@ int k_gemm_bf16(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpi
   // 128x256 tiles halve the operand bytes per FLOP of 128x128 ones (the 128x128 kernel measured L2-bandwidth
   // bound: 32 KB of operands per 4 MMAs = 6.2 TB/s at 410 TFLOP/s); two 97 KB CTAs still share an SM
   static const bool wide = getenv("TUTOR_GEMM_BN128") == nullptr;
+  static const bool persistent = getenv("TUTOR_GEMM_NONPERSISTENT") == nullptr;  // debugging aid / A-B measurements
+  if (persistent) {
+    if (wide && N >= 256) return launch_persistent<256>(A, M, W, N, K, epi, st);
+    return launch_persistent<128>(A, M, W, N, K, epi, st);
+  }
   if (wide && N >= 256) return launch<256, EPI_ROWMAJOR>(A, M, W, N, K, epi, am, st);
   return launch<128, EPI_ROWMAJOR>(A, M, W, N, K, epi, am, st);
 }

@@ -51,6 +51,68 @@ __global__ void __launch_bounds__(256) gemv_f32_kernel(const float* __restrict__
   }
 }
 
+// Same GEMV with the preceding LayerNorm folded in (decode, M <= 8): every CTA normalises the M input rows into
+// shared memory itself - M*K floats, a few microseconds of redundant work per CTA - which removes one whole kernel
+// (and one dependent-launch boundary) per LayerNorm from the 88-kernel decode chain of the parity path.
+// xn_out (optional) receives the normalised rows from CTA 0 (the debug-logits entry point reads them).
+template <int MB>
+__global__ void __launch_bounds__(256) gemv_f32_ln_kernel(const float* __restrict__ X, const float* __restrict__ gamma,
+                                                           const float* __restrict__ beta, float eps,
+                                                           const float* __restrict__ W, int N, int K, GemmEpilogue epi,
+                                                           float* __restrict__ xn_out) {
+  extern __shared__ __align__(16) float xs[];  // [MB][K]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = blockIdx.x * 8 + warp;
+  pdl_launch_dependents();
+  const float* w = W + (size_t)min(n, N - 1) * K;
+  for (int off = lane * 32; off < K; off += 1024) asm volatile("prefetch.global.L2 [%0];" ::"l"(w + off));
+  pdl_wait();
+  for (int m = warp; m < MB; m += 8) {  // one warp per row, two-pass like layernorm_kernel
+    const float* xr = X + (size_t)m * K;
+    float s = 0.f;
+    for (int k = lane * 4; k < K; k += 128) {
+      const float4 v = load4(xr + k);
+      *reinterpret_cast<float4*>(xs + m * K + k) = v;
+      s += (v.x + v.y) + (v.z + v.w);
+    }
+    const float mean = warp_sum(s) / K;
+    float q = 0.f;
+    for (int k = lane * 4; k < K; k += 128) {
+      const float4 v = *reinterpret_cast<const float4*>(xs + m * K + k);
+      const float a = v.x - mean, b = v.y - mean, c = v.z - mean, d = v.w - mean;
+      q += (a * a + b * b) + (c * c + d * d);
+    }
+    const float rstd = 1.0f / sqrtf(warp_sum(q) / K + eps);
+    for (int k = lane * 4; k < K; k += 128) {
+      const float4 v = *reinterpret_cast<const float4*>(xs + m * K + k);
+      const float4 g = load4(gamma + k), b = load4(beta + k);
+      float4 o;
+      o.x = (v.x - mean) * rstd * g.x + b.x; o.y = (v.y - mean) * rstd * g.y + b.y;
+      o.z = (v.z - mean) * rstd * g.z + b.z; o.w = (v.w - mean) * rstd * g.w + b.w;
+      *reinterpret_cast<float4*>(xs + m * K + k) = o;
+      if (xn_out && blockIdx.x == 0) *reinterpret_cast<float4*>(xn_out + (size_t)m * K + k) = o;
+    }
+  }
+  __syncthreads();
+  if (n >= N) return;
+  float acc[MB];
+#pragma unroll
+  for (int m = 0; m < MB; ++m) acc[m] = 0.f;
+  for (int k = lane * 4; k < K; k += 128) {
+    const float4 w0 = load4(w + k);
+#pragma unroll
+    for (int m = 0; m < MB; ++m) {
+      const float4 a0 = *reinterpret_cast<const float4*>(xs + m * K + k);
+      acc[m] += w0.x * a0.x + w0.y * a0.y + w0.z * a0.z + w0.w * a0.w;
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < MB; ++m) {
+    const float s = warp_sum(acc[m]);
+    if (lane == 0) epilogue_store(epi, m, n, s);
+  }
+}
+
 constexpr int BM = 64, BN = 64, BK = 16, PAD = 4;
 
 __global__ void __launch_bounds__(256) sgemm_f32_kernel(const float* __restrict__ A, const float* __restrict__ W,
@@ -107,6 +169,22 @@ __global__ void __launch_bounds__(256) sgemm_f32_kernel(const float* __restrict_
 }
 
 }  // namespace
+
+int k_gemv_f32_ln(const float* X, const float* gamma, const float* beta, float eps, const float* W, int M, int N, int K,
+                  const GemmEpilogue& epi, float* xn_out, cudaStream_t st) {
+  ARG_CHECK(M >= 1 && M <= 8 && K % 128 == 0, "gemv_f32_ln: unsupported M=%d K=%d", M, K);
+  const dim3 grid(ceil_div(N, 8)), block(256);
+  const size_t smem = (size_t)M * K * sizeof(float);
+  ARG_CHECK(smem <= 48 * 1024, "gemv_f32_ln: %d rows of %d do not fit in shared memory", M, K);
+#define GEMVLN_CASE(n) case n: CUDA_TRY(tutor_launch(gemv_f32_ln_kernel<n>, grid, block, smem, st, X, gamma, beta, eps, W, N, K, epi, xn_out)); break;
+  switch (M) {
+    GEMVLN_CASE(1) GEMVLN_CASE(2) GEMVLN_CASE(3) GEMVLN_CASE(4) GEMVLN_CASE(5) GEMVLN_CASE(6) GEMVLN_CASE(7)
+    GEMVLN_CASE(8)
+  }
+#undef GEMVLN_CASE
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
 
 int k_gemm_f32(const float* A, const float* W, int M, int N, int K, const GemmEpilogue& epi, cudaStream_t st) {
   ARG_CHECK(K % 128 == 0 || (M > 8 && K % BK == 0), "gemm_f32: K=%d unsupported (M=%d)", K, M);

@@ -18,6 +18,10 @@ int k_seen_bitmap(const int32_t* ids, int ids_ld, int T, uint32_t* seen, int wor
 // ---- gemm_f32.cu : C[m,n] = sum_k A[m,k] * W[n,k]   (A [M,K] fp32, W [N,K] fp32, both K-contiguous)
 int k_gemm_f32(const float* A, const float* W, int M, int N, int K, const GemmEpilogue& epi, cudaStream_t st);
 
+// decode GEMV (M <= 8) with the preceding LayerNorm of X folded in; xn_out (nullable) also receives LN(X)
+int k_gemv_f32_ln(const float* X, const float* gamma, const float* beta, float eps, const float* W, int M, int N, int K,
+                  const GemmEpilogue& epi, float* xn_out, cudaStream_t st);
+
 // ---- gemm_bf16_tc.cu : same contraction on bf16 operands, fp32 accumulation in TMEM (tcgen05 + TMA)
 int k_gemm_bf16(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpilogue& epi, cudaStream_t st);
 int k_gemm_bf16_splitk(const bf16* X, const bf16* W, int M, int N, int K, int ks, float* partial, cudaStream_t st);
@@ -69,6 +73,9 @@ struct DecodeState {
 size_t k_lmhead_scratch_bytes(int B, int V);
 int k_lmhead_argmax(const void* xn, int x_dtype, const void* wte, int w_dtype, int B, int V, int d,
                     const DecodeState& ds, void* scratch, cudaStream_t st);
+int k_lmhead_argmax_ln(const void* x, int x_dtype, const void* wte, int w_dtype, int B, int V, int d,
+                       const DecodeState& ds, void* scratch, const float* ln_g, const float* ln_b, float ln_eps,
+                       float* xn_out, cudaStream_t st);
 // debug / parity: materialise logits [B,V] fp32
 int k_lmhead_logits(const void* xn, int x_dtype, const void* wte, int w_dtype, int B, int V, int Vpad, int d,
                     float* logits, cudaStream_t st);

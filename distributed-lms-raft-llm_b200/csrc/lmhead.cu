@@ -25,10 +25,43 @@ __global__ void __launch_bounds__(256) lmhead_argmax_simt_kernel(const float* __
                                                                   int d, const uint32_t* __restrict__ seen,
                                                                   int seen_words, float penalty,
                                                                   float* __restrict__ part_val,
-                                                                  int* __restrict__ part_idx) {
+                                                                  int* __restrict__ part_idx,
+                                                                  const float* __restrict__ ln_gamma,
+                                                                  const float* __restrict__ ln_beta, float ln_eps,
+                                                                  float* __restrict__ xn_out) {
+  extern __shared__ __align__(16) float xs[];  // [MB][d] input rows, normalised here when ln_gamma is given (ln_f)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   pdl_launch_dependents();
   pdl_wait();
+  for (int m = warp; m < MB; m += 8) {
+    const float* xr = x + (size_t)(b0 + m) * d;
+    float s = 0.f;
+    for (int k = lane * 4; k < d; k += 128) {
+      const float4 v = load4(xr + k);
+      *reinterpret_cast<float4*>(xs + m * d + k) = v;
+      s += (v.x + v.y) + (v.z + v.w);
+    }
+    if (ln_gamma) {
+      const float mean = warp_sum(s) / d;
+      float q = 0.f;
+      for (int k = lane * 4; k < d; k += 128) {
+        const float4 v = *reinterpret_cast<const float4*>(xs + m * d + k);
+        const float a = v.x - mean, b = v.y - mean, c = v.z - mean, e = v.w - mean;
+        q += (a * a + b * b) + (c * c + e * e);
+      }
+      const float rstd = 1.0f / sqrtf(warp_sum(q) / d + ln_eps);
+      for (int k = lane * 4; k < d; k += 128) {
+        const float4 v = *reinterpret_cast<const float4*>(xs + m * d + k);
+        const float4 g = load4(ln_gamma + k), bb = load4(ln_beta + k);
+        float4 o;
+        o.x = (v.x - mean) * rstd * g.x + bb.x; o.y = (v.y - mean) * rstd * g.y + bb.y;
+        o.z = (v.z - mean) * rstd * g.z + bb.z; o.w = (v.w - mean) * rstd * g.w + bb.w;
+        *reinterpret_cast<float4*>(xs + m * d + k) = o;
+        if (xn_out && blockIdx.x == 0) *reinterpret_cast<float4*>(xn_out + (size_t)(b0 + m) * d + k) = o;
+      }
+    }
+  }
+  __syncthreads();
   float best[MB];
   int besti[MB];
 #pragma unroll
@@ -42,7 +75,7 @@ __global__ void __launch_bounds__(256) lmhead_argmax_simt_kernel(const float* __
       float4 wv = load4(w + k);
 #pragma unroll
       for (int m = 0; m < MB; ++m) {
-        float4 a = __ldg(reinterpret_cast<const float4*>(x + (size_t)(b0 + m) * d + k));
+        const float4 a = *reinterpret_cast<const float4*>(xs + m * d + k);
         acc[m] += wv.x * a.x + wv.y * a.y + wv.z * a.z + wv.w * a.w;
       }
     }
@@ -123,13 +156,15 @@ __global__ void __launch_bounds__(1024) argmax_finalize_kernel(const float* __re
 
 template <typename WT>
 int launch_simt(const float* x, const WT* wte, int B, int V, int d, const DecodeState& ds, float* pv, int* pi,
-                int nblocks, cudaStream_t st) {
+                int nblocks, const float* ln_g, const float* ln_b, float ln_eps, float* xn_out, cudaStream_t st) {
+  ARG_CHECK((size_t)8 * d * sizeof(float) <= 48 * 1024, "lmhead: d=%d too wide for the shared-memory row cache", d);
   for (int b0 = 0; b0 < B; b0 += 8) {
     const int mb = (B - b0 < 8) ? (B - b0) : 8;
 #define LM_CASE(n)                                                                                              \
   case n:                                                                                                       \
-    CUDA_TRY(tutor_launch(lmhead_argmax_simt_kernel<WT, n>, dim3(nblocks), dim3(256), 0, st, x, wte, b0, B, V, d,   \
-                          (const uint32_t*)ds.seen, ds.seen_words, ds.penalty, pv, pi));                       \
+    CUDA_TRY(tutor_launch(lmhead_argmax_simt_kernel<WT, n>, dim3(nblocks), dim3(256), (size_t)n * d * sizeof(float), \
+                          st, x, wte, b0, B, V, d, (const uint32_t*)ds.seen, ds.seen_words, ds.penalty, pv, pi, ln_g,  \
+                          ln_b, ln_eps, xn_out));                                                                    \
     break;
     switch (mb) {
       LM_CASE(1) LM_CASE(2) LM_CASE(3) LM_CASE(4) LM_CASE(5) LM_CASE(6) LM_CASE(7) LM_CASE(8)
@@ -149,14 +184,22 @@ size_t k_lmhead_scratch_bytes(int B, int V) {
 
 int k_lmhead_argmax(const void* xn, int x_dtype, const void* wte, int w_dtype, int B, int V, int d,
                     const DecodeState& ds, void* scratch, cudaStream_t st) {
+  return k_lmhead_argmax_ln(xn, x_dtype, wte, w_dtype, B, V, d, ds, scratch, nullptr, nullptr, 0.f, nullptr, st);
+}
+
+// ln_g != null (fp32 activations only): xn is the un-normalised residual stream and ln_f is applied inside the kernel
+int k_lmhead_argmax_ln(const void* xn, int x_dtype, const void* wte, int w_dtype, int B, int V, int d,
+                       const DecodeState& ds, void* scratch, const float* ln_g, const float* ln_b, float ln_eps,
+                       float* xn_out, cudaStream_t st) {
+  ARG_CHECK(!ln_g || x_dtype == DT_F32, "lmhead: fused ln_f needs fp32 activations");
   ARG_CHECK(B >= 1 && d % 128 == 0, "lmhead: unsupported B=%d d=%d", B, d);
   float* pv = reinterpret_cast<float*>(scratch);
   int* pi = reinterpret_cast<int*>(pv + (size_t)LM_MAX_PARTS * B);
   int nparts;
   if (x_dtype == DT_F32) {
     nparts = ceil_div(V, 8) < LM_BLOCKS ? ceil_div(V, 8) : LM_BLOCKS;
-    if (w_dtype == DT_F32) TRY(launch_simt<float>((const float*)xn, (const float*)wte, B, V, d, ds, pv, pi, nparts, st));
-    else TRY(launch_simt<bf16>((const float*)xn, (const bf16*)wte, B, V, d, ds, pv, pi, nparts, st));
+    if (w_dtype == DT_F32) TRY(launch_simt<float>((const float*)xn, (const float*)wte, B, V, d, ds, pv, pi, nparts, ln_g, ln_b, ln_eps, xn_out, st));
+    else TRY(launch_simt<bf16>((const float*)xn, (const bf16*)wte, B, V, d, ds, pv, pi, nparts, ln_g, ln_b, ln_eps, xn_out, st));
   } else {
     ARG_CHECK(w_dtype == DT_BF16, "lmhead: bf16 activations need bf16 weights");
     nparts = ceil_div(V, 128);

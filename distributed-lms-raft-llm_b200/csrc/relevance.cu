@@ -263,11 +263,7 @@ int k_topk_merge(const float* cand_scores, const int32_t* cand_idx, int Q, int n
   ARG_CHECK(k >= 1 && ncand >= 1, "topk_merge: bad k=%d ncand=%d", k, ncand);
   size_t smem = (size_t)ncand * 8;
   ARG_CHECK(smem <= 200 * 1024, "topk_merge: %d candidates do not fit in shared memory", ncand);
-  static bool attr_done = false;
-  if (!attr_done) {
-    CUDA_TRY(cudaFuncSetAttribute(topk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_done = true;
-  }
+  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(topk_merge_kernel), 200 * 1024));
   topk_merge_kernel<<<Q, 256, smem, st>>>(cand_scores, cand_idx, ncand, k, out_scores, out_idx);
   KERNEL_LAUNCHED();
   return TUTOR_OK;
@@ -291,27 +287,15 @@ int k_cosine_topk(const float* queries, const void* corpus, int corpus_dtype, co
   const int grid = 148;
   const size_t smem2 = ((size_t)SC_QMAX * d + SC_QMAX + (size_t)8 * SC_STAGES * SC_ROWS * SC_LD) * sizeof(float);
   if (Q <= SC_QMAX && d % SC_K == 0 && smem2 <= 220 * 1024) {
-    static bool a2 = false;
-    if (!a2) {
-      CUDA_TRY(cudaFuncSetAttribute(cosine_scan2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-      a2 = true;
-    }
+    TRY(tutor_set_max_smem(reinterpret_cast<const void*>(cosine_scan2_kernel), 220 * 1024));
     cosine_scan2_kernel<<<grid, 256, smem2, st>>>(queries, (const float*)corpus, corpus_inv_norm, Q, N, d, eps, scores);
   } else {
     const size_t smem = (size_t)Q * d * 4 + (size_t)Q * 4;
     if (d == 768) {
-      static bool a6 = false;
-      if (!a6) {
-        CUDA_TRY(cudaFuncSetAttribute(cosine_scan_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        a6 = true;
-      }
+      TRY(tutor_set_max_smem(reinterpret_cast<const void*>(cosine_scan_kernel<6>), 200 * 1024));
       cosine_scan_kernel<6><<<grid, 256, smem, st>>>(queries, (const float*)corpus, corpus_inv_norm, Q, N, eps, scores);
     } else {
-      static bool a1 = false;
-      if (!a1) {
-        CUDA_TRY(cudaFuncSetAttribute(cosine_scan_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        a1 = true;
-      }
+      TRY(tutor_set_max_smem(reinterpret_cast<const void*>(cosine_scan_kernel<1>), 200 * 1024));
       cosine_scan_kernel<1><<<grid, 256, smem, st>>>(queries, (const float*)corpus, corpus_inv_norm, Q, N, eps, scores);
     }
   }

@@ -1,7 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 1500 python tools/determinism_check.py large 2>&1 | grep -v Warning | tee gpurun_out/determinism.txt | tail -8
-run() { name=$1; shift; echo "=== $name"; timeout 1200 "$@" > gpurun_out/$name.log 2>&1; echo "exit $?" | tee -a gpurun_out/$name.log; tail -${TAILN:-6} gpurun_out/$name.log; }
+run() { name=$1; shift; echo "=== $name"; timeout 1200 "$@" > gpurun_out/$name.log 2>&1; echo "exit $?" | tee -a gpurun_out/$name.log; tail -${TAILN:-3} gpurun_out/$name.log; }
 run all python -m pytest tests -m gpu -q -x
-timeout 600 python bench.py --steps 3 --warmup 3 --no-extras > gpurun_out/bench.log 2>&1
-grep "^{" gpurun_out/bench.log | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('value', round(d['value']), 'e2e', round(d['e2e']['value']), 'decode ms', round(d['decode']['ms_per_forward'],4))"
+timeout 600 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.log 2>&1
+grep "^{" gpurun_out/bench.log | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('value', round(d['value']), 'e2e', round(d['e2e']['value']), 'decode ms', round(d['decode']['ms_per_forward'],4), 'prefill', round(d['decode']['prefill_ms'],2)); print(d['extras'])"
