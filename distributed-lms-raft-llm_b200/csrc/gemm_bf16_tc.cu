@@ -156,9 +156,34 @@ template <int BN> struct SmemLayout {
   static constexpr int TOTAL = TILE_BYTES + BAR_BYTES + 1024;  // +1024: manual 1 KB alignment of the tiles
 };
 
+// 256-bit global accesses (LDG/STG.E.256, new on sm_100): in the row-major epilogue every lane owns a different
+// output row, so each warp-level access touches 32 separate lines; moving a whole 32-byte sector per lane halves
+// both the instruction count and the sector operations of the 128-bit form (which used half of every sector).
+__device__ __forceinline__ void ldg256(const float* p, float* v) {
+  asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+               : "l"(p));
+}
+__device__ __forceinline__ void stg256(float* p, const float* v) {
+  asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]),
+               "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
+               : "memory");
+}
+__device__ __forceinline__ void stg256_bf16(bf16* p, const float* v) {  // 16 floats -> 16 bf16 = 32 bytes
+  uint32_t w[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    w[i] = *reinterpret_cast<uint32_t*>(&h);
+  }
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]),
+               "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+               : "memory");
+}
+
 // vectorised row run: 32 consecutive columns n0.. of row m (EPI_ROWMAJOR)
 __device__ __forceinline__ void store_run32(const GemmEpilogue& e, int m, int n0, int N, float* v) {
-  if (n0 + 32 > N || (e.ldo & 7)) {  // ragged edge: scalar path
+  if (n0 + 32 > N || (e.ldo & 15)) {  // ragged edge / unaligned rows: scalar path
     for (int i = 0; i < 32 && n0 + i < N; ++i) epilogue_store(e, m, n0 + i, v[i]);
     return;
   }
@@ -179,9 +204,11 @@ __device__ __forceinline__ void store_run32(const GemmEpilogue& e, int m, int n0
     size_t o = (size_t)m * e.ldo + n0;
     if (!e.qkv_mode && e.residual) {
 #pragma unroll
-      for (int i = 0; i < 32; i += 4) {
-        float4 r = *reinterpret_cast<const float4*>(e.residual + o + i);
-        v[i] += r.x; v[i + 1] += r.y; v[i + 2] += r.z; v[i + 3] += r.w;
+      for (int i = 0; i < 32; i += 8) {
+        float r[8];
+        ldg256(e.residual + o + i, r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[i + j] += r[j];
       }
     }
     if (e.out_f32) of = e.out_f32 + o;
@@ -199,18 +226,11 @@ __device__ __forceinline__ void store_run32(const GemmEpilogue& e, int m, int n0
   }
   if (of) {
 #pragma unroll
-    for (int i = 0; i < 32; i += 4)
-      *reinterpret_cast<float4*>(of + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+    for (int i = 0; i < 32; i += 8) stg256(of + i, v + i);
   }
   if (ob) {
 #pragma unroll
-    for (int i = 0; i < 32; i += 8) {
-      __nv_bfloat162 p0 = __floats2bfloat162_rn(v[i], v[i + 1]), p1 = __floats2bfloat162_rn(v[i + 2], v[i + 3]);
-      __nv_bfloat162 p2 = __floats2bfloat162_rn(v[i + 4], v[i + 5]), p3 = __floats2bfloat162_rn(v[i + 6], v[i + 7]);
-      uint4 pk = make_uint4(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1),
-                            *reinterpret_cast<uint32_t*>(&p2), *reinterpret_cast<uint32_t*>(&p3));
-      *reinterpret_cast<uint4*>(ob + i) = pk;
-    }
+    for (int i = 0; i < 32; i += 16) stg256_bf16(ob + i, v + i);
   }
 }
 
