@@ -83,3 +83,16 @@ def test_ragged_lengths_and_errors(pkg, base_hf):
     with pytest.raises(NotImplementedError):
         ids = rp.bert_ids(2, 8)
         eng(input_ids=ids, attention_mask=torch.tensor([[1] * 8, [1] * 4 + [0] * 4]))
+
+
+@pytest.mark.parametrize("B,T", [(1, 1), (1, 7), (2, 77), (5, 128), (3, 300), (1, 512)])
+def test_bf16_ragged_shapes(pkg, base_hf, B, T):
+    """bf16 mode with sequence lengths that leave partial attention tiles and batch*length that leaves partial GEMM
+    tiles (persistent tcgen05 kernel when B*T > 128, swap-AB kernel otherwise): embeddings within 3e-2 of the oracle."""
+    eng = pkg.B200BertModel.from_hf(base_hf, dtype="bf16")
+    ids = rp.bert_ids(B, max(T, 2), seed=B * 7 + T)[:, :T]
+    ref = rp.embeddings_from_ids(base_hf, ids)
+    got = eng.embed(ids)
+    err = (got - ref).abs().max().item()
+    assert err < 3e-2, err
+    assert (torch.nn.functional.cosine_similarity(got, ref) > 0.9995).all()

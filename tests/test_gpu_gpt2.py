@@ -264,3 +264,22 @@ def test_launch_modes_are_bit_identical(pkg, small_hf, monkeypatch):
         del eng
     for name, o in outs.items():
         assert torch.equal(o, outs["no_pdl_no_graph"]), name
+
+
+@pytest.mark.parametrize("B,T", [(1, 1), (1, 37), (3, 5), (17, 65), (33, 9), (100, 20), (128, 3)])
+def test_bf16_ragged_shapes_against_oracle_logits(pkg, tiny_hf, B, T):
+    """bf16 throughput mode over batch sizes that select every tile width of the swap-AB GEMM (16/32/64/128) and
+    prompt lengths that leave ragged attention / GEMM tiles: prefill logits within the stated bf16 tolerance
+    (3e-2 relative) of the fp32 oracle, decode runs, output deterministic."""
+    eng = pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="bf16")
+    ids = rp.gpt2_prompt_ids(B, T, seed=B * 1000 + T, vocab=1000)
+    with torch.no_grad():
+        ref = tiny_hf(ids).logits[:, -1].float()
+    eng.prefill(ids, max_new_tokens=12, eos_token_id=999, pad_token_id=999)
+    got = eng.last_logits().float().cpu()
+    err = ((got - ref).abs().max() / ref.abs().max()).item()
+    assert err < 3e-2, err
+    a = eng.generate(ids, max_new_tokens=12, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
+    b = eng.generate(ids, max_new_tokens=12, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
+    assert tuple(a.shape) == (B, T + 12) and torch.equal(a, b) and torch.equal(a[:, :T], ids)
+    assert int(a.min()) >= 0 and int(a.max()) < 1000
