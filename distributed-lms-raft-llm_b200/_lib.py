@@ -73,6 +73,13 @@ SIGNATURES = {
     "tutor_lmhead_argmax": (c_int, [c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_float, c_void_p,
                                     c_void_p, c_void_p]),
     "tutor_meanpool": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "tutor_row_tile_stats": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "tutor_decode_ln_linear_partial": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_int, c_int,
+                                               c_int, c_int, c_void_p, c_void_p]),
+    "tutor_decode_ln_linear_act": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_int,
+                                           c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "tutor_decode_linear_residual": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p,
+                                             c_void_p, c_void_p]),
     "tutor_lmhead_argmax_static": (c_int, [c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_float, c_void_p,
                                            c_void_p]),
 }

@@ -157,6 +157,46 @@ int tutor_lmhead_argmax(int dtype, const void* x, const void* wte, int B, int V,
   return k_lmhead_argmax(x, dtype, wte, dtype, B, V, d, ds, scratch, (cudaStream_t)stream);
 }
 
+// ---- decode-step linears with fused LayerNorm operand / cluster split-K reduction (gemm_decode_fused.cu)
+namespace {
+int sm_count() {
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  return sms;
+}
+}  // namespace
+
+int tutor_row_tile_stats(const float* x, float* stats, int M, int d, void* stream) {
+  ARG_CHECK(x && stats, "row_tile_stats: null argument");
+  return k_row_tile_stats(x, stats, M, d, (cudaStream_t)stream);
+}
+
+int tutor_decode_ln_linear_partial(const float* x, const float* stats, const float* gamma, const float* beta, float eps,
+                                   const void* W, int M, int N, int K, int ks, float* partial, void* stream) {
+  ARG_CHECK(x && stats && gamma && beta && W && partial && K % 128 == 0, "decode_ln_linear_partial: bad argument");
+  if (ks <= 0) ks = k_pick_splitk(N, K, sm_count());
+  return k_gemm_ln_splitk(x, stats, K / 128, gamma, beta, eps, (const bf16*)W, M, N, K, ks, partial,
+                          (cudaStream_t)stream);
+}
+
+int tutor_decode_ln_linear_act(const float* x, const float* stats, const float* gamma, const float* beta, float eps,
+                               const void* W, const float* bias, int act, int M, int N, int K, int ks, int bn,
+                               void* out_bf16, void* stream) {
+  ARG_CHECK(x && stats && gamma && beta && W && bias && out_bf16 && K % 128 == 0, "decode_ln_linear_act: bad argument");
+  if (bn <= 0) bn = k_decode_batch_tile(M);
+  if (ks <= 0) ks = k_pick_cluster_splitk(N, K, ceil_div(M, bn), sm_count());
+  return k_gemm_ln_act(x, stats, K / 128, gamma, beta, eps, (const bf16*)W, bias, act, M, N, K, ks, bn, (bf16*)out_bf16,
+                       (cudaStream_t)stream);
+}
+
+int tutor_decode_linear_residual(const void* A, const void* W, const float* bias, int M, int N, int K, int ks, int bn,
+                                 float* x, float* stats, void* stream) {
+  ARG_CHECK(A && W && bias && x && stats, "decode_linear_residual: null argument");
+  if (bn <= 0) bn = k_decode_batch_tile(M);
+  if (ks <= 0) ks = k_pick_cluster_splitk(N, K, ceil_div(M, bn), sm_count());
+  return k_gemm_resid_stats((const bf16*)A, (const bf16*)W, bias, M, N, K, ks, bn, x, stats, (cudaStream_t)stream);
+}
+
 int tutor_meanpool(const float* x, float* out, int B, int T, int d, void* stream) {
   ARG_CHECK(x && out && T >= 1, "meanpool: bad argument");
   return k_meanpool(x, out, B, T, d, (cudaStream_t)stream);

@@ -54,6 +54,9 @@ struct tutor_gpt2 {
   size_t partial_lane_elems = 0, lm_scratch_lane_bytes = 0;
   int num_sms = 148;
   bool use_fused = true, use_pdl = true;
+  bool use_cluster = true;   // TUTOR_NO_CLUSTER=1: the 8-launch-per-layer chain (separate reduce kernels) for A/B runs
+  float* ln_stats = nullptr;  // [d/128][B][2] per-row (mean, M2) of x over each 128-column tile, one slice per lane
+  size_t ln_stats_lane_elems = 0;
   bool use_ln_gemv = false;  // TUTOR_LN_GEMV=1: LayerNorm folded into the fp32 decode GEMVs - measured slower (2213 vs 2560 tok/s)
   // Decode lanes: the batch is cut into micro-batches whose kernel chains run concurrently (own stream, own
   // length counter), so one lane's latency-bound GEMM/reduce chain overlaps the other's bandwidth-bound attention.
@@ -200,6 +203,52 @@ int forward_decode_fused(tutor_gpt2* e, int lane, int b0, int B) {
                          (uint8_t*)e->lm_scratch + (size_t)lane * e->lm_scratch_lane_bytes, st);
 }
 
+// The same forward in 5 launches per layer (gemm_decode_fused.cu): LayerNorm is applied while the consuming GEMM
+// stages its operand (from x and per-tile row statistics), and the split-K sums of c_proj / c_fc / mlp c_proj are
+// closed inside the GEMM by a thread-block cluster reading its peers' shared memory.
+int forward_decode_cluster(tutor_gpt2* e, int lane, int b0, int B) {
+  const int d = e->d, nst = d / 128;
+  cudaStream_t st = e->lane_stream[lane];
+  const float eps = e->cfg.layer_norm_epsilon;
+  const int* len = e->counters + 2 * lane;
+  float* x = e->x + (size_t)b0 * d;
+  bf16* att = (bf16*)e->att + (size_t)b0 * d;
+  bf16* hb = (bf16*)e->hbuf + (size_t)b0 * 4 * d;
+  bf16* xl = (bf16*)e->xn_last + (size_t)b0 * d;
+  float* partial = e->partial + (size_t)lane * e->partial_lane_elems;
+  float* stats = e->ln_stats + (size_t)lane * e->ln_stats_lane_elems;
+  const size_t kv_off = (size_t)b0 * e->H * e->Smax * 64 * e->esz();
+  const int* npad = e->padded ? e->npad + b0 : nullptr;
+  // batch tile of the residual GEMMs (N = d is only d/128 weight tiles): smaller tiles = more CTAs, less DSMEM per CTA
+  const int bn_full = k_decode_batch_tile(B);
+  int bn_res = bn_full;
+  while (bn_res > 16 && ceil_div(d, 128) * ceil_div(B, bn_res / 2) * 8 <= e->num_sms) bn_res /= 2;
+  if (const char* v = getenv("TUTOR_BN_RES")) bn_res = atoi(v);
+  const int bt_res = ceil_div(B, bn_res);
+  const int ks_qkv = k_pick_splitk(3 * d, d, e->num_sms);
+  const int ks_proj = k_pick_cluster_splitk(d, d, bt_res, e->num_sms);
+  const int ks_fc = k_pick_cluster_splitk(4 * d, d, 1, e->num_sms);
+  const int ks_proj2 = k_pick_cluster_splitk(d, 4 * d, bt_res, e->num_sms);
+  TRY(k_gpt2_embed(e->ids + (size_t)b0 * e->ids_ld, e->ids_ld, len, 1, e->wte, e->dt, e->wpe, d, x, B, npad, st));
+  TRY(k_row_tile_stats(x, stats, B, d, st));
+  for (int l = 0; l < e->L; ++l) {
+    const Gpt2Layer& w = e->layers[l];
+    void* kc = (uint8_t*)e->kcache(l) + kv_off;
+    void* vc = (uint8_t*)e->vcache(l) + kv_off;
+    TRY(k_gemm_ln_splitk(x, stats, nst, w.ln1_g, w.ln1_b, eps, (const bf16*)w.qkv.w, B, 3 * d, d, ks_qkv, partial, st));
+    TRY(k_attn_decode_fused(partial, ks_qkv, w.qkv.b, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
+                            e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, npad,
+                            e->cur_T, st));
+    TRY(k_gemm_resid_stats(att, (const bf16*)w.proj.w, w.proj.b, B, d, d, ks_proj, bn_res, x, stats, st));
+    TRY(k_gemm_ln_act(x, stats, nst, w.ln2_g, w.ln2_b, eps, (const bf16*)w.fc.w, w.fc.b, ACT_GELU_TANH, B, 4 * d, d, ks_fc,
+                      bn_full, hb, st));
+    TRY(k_gemm_resid_stats(hb, (const bf16*)w.proj2.w, w.proj2.b, B, d, 4 * d, ks_proj2, bn_res, x, stats, st));
+  }
+  TRY(k_layernorm(x, 1, 0, e->lnf_g, e->lnf_b, eps, nullptr, xl, B, d, st));
+  return k_lmhead_argmax(xl, e->dt, e->wte, e->dt, B, e->V, d, e->dstate(lane, b0),
+                         (uint8_t*)e->lm_scratch + (size_t)lane * e->lm_scratch_lane_bytes, st);
+}
+
 int decode_forward(tutor_gpt2* e, int B) {
   if (!(e->dt == DT_BF16 && e->use_fused && B <= 128)) {
     // parity (fp32) path: same kernel chain as prefill, with PDL when every GEMM is the weight-streaming GEMV
@@ -218,7 +267,7 @@ int decode_forward(tutor_gpt2* e, int B) {
   int rc = TUTOR_OK;
   for (int i = 0; i < e->nlanes && rc == TUTOR_OK; ++i) {
     const int b0 = e->lane_b0(i), b1 = e->lane_b0(i + 1);
-    rc = forward_decode_fused(e, i, b0, b1 - b0);
+    rc = e->use_cluster ? forward_decode_cluster(e, i, b0, b1 - b0) : forward_decode_fused(e, i, b0, b1 - b0);
   }
   tutor_pdl_enabled = false;
   if (rc != TUTOR_OK) return rc;
@@ -258,6 +307,9 @@ int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
       }
       e->partial_lane_elems = elems;  // every lane slice can hold the whole batch (lanes only ever hold a part of it)
       TRY(dev_alloc(&e->partial, tutor_gpt2::MAX_LANES * elems * sizeof(float)));
+      dev_free(e->ln_stats);
+      e->ln_stats_lane_elems = (size_t)(d / 128) * nb * 2;
+      TRY(dev_alloc(&e->ln_stats, tutor_gpt2::MAX_LANES * e->ln_stats_lane_elems * sizeof(float)));
     }
     e->ids_ld = ns;
     e->seen_words = ceil_div(e->V, 32);
@@ -429,6 +481,7 @@ int tutor_gpt2_create(const tutor_gpt2_config* cfg, int device, tutor_gpt2_t** o
   e->use_graph = getenv("TUTOR_NO_GRAPH") == nullptr;
   e->use_fused = getenv("TUTOR_NO_FUSED") == nullptr;  // debugging aids: unfused decode kernels / no PDL
   e->use_pdl = getenv("TUTOR_NO_PDL") == nullptr;
+  e->use_cluster = getenv("TUTOR_NO_CLUSTER") == nullptr;
   e->use_ln_gemv = getenv("TUTOR_LN_GEMV") != nullptr;
   {
     cudaDeviceProp prop;
@@ -466,7 +519,7 @@ void tutor_gpt2_destroy(tutor_gpt2_t* e) {
   }
   dev_free(e->kv); dev_free(e->x); dev_free(e->xn); dev_free(e->q); dev_free(e->att); dev_free(e->hbuf);
   dev_free(e->xn_last); dev_free(e->ids); dev_free(e->counters); dev_free(e->seen); dev_free(e->finished);
-  dev_free(e->lm_scratch); dev_free(e->partial); dev_free(e->attn_scratch); dev_free(e->npad);
+  dev_free(e->lm_scratch); dev_free(e->partial); dev_free(e->attn_scratch); dev_free(e->npad); dev_free(e->ln_stats);
   if (e->h_counters) cudaFreeHost(e->h_counters);
   for (int i = 1; i < tutor_gpt2::MAX_LANES; ++i) {
     if (e->lane_stream[i]) cudaStreamDestroy(e->lane_stream[i]);

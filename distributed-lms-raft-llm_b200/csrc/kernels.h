@@ -26,6 +26,22 @@ int k_gemv_f32_ln(const float* X, const float* gamma, const float* beta, float e
 int k_gemm_bf16(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpilogue& epi, cudaStream_t st);
 int k_gemm_bf16_splitk(const bf16* X, const bf16* W, int M, int N, int K, int ks, float* partial, cudaStream_t st);
 int k_pick_splitk(int N, int K, int num_sms);
+int k_make_map_bf16(void* tensor_map, const bf16* ptr, int rows, int K, int box_rows);
+int k_make_map_partial(void* tensor_map, float* ptr, int N, int M, int ks, int box_m);
+
+// ---- gemm_decode_fused.cu : decode-step linears with LayerNorm folded into the operand load and the split-K
+// reduction done across a thread-block cluster (DSMEM) with bias + gelu / bias + residual fused behind it.
+// stats: [d/128][M][2] = per-row (mean, M2) of x over each 128-column tile.
+int k_decode_batch_tile(int M);
+int k_pick_cluster_splitk(int N, int K, int batch_tiles, int num_sms);
+int k_row_tile_stats(const float* x, float* stats, int M, int d, cudaStream_t st);
+int k_gemm_ln_splitk(const float* x, const float* stats, int nst, const float* gamma, const float* beta, float eps,
+                     const bf16* W, int M, int N, int K, int ks, float* partial, cudaStream_t st);
+int k_gemm_ln_act(const float* x, const float* stats, int nst, const float* gamma, const float* beta, float eps,
+                  const bf16* W, const float* bias, int act, int M, int N, int K, int ks, int bn, bf16* out,
+                  cudaStream_t st);
+int k_gemm_resid_stats(const bf16* A, const bf16* W, const float* bias, int M, int N, int K, int ks, int bn, float* x,
+                       float* stats, cudaStream_t st);
 // legacy mma.sync kernel kept only as an on-GPU cross-check of the tcgen05 kernel (tests)
 int k_gemm_bf16_legacy(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpilogue& epi, cudaStream_t st);
 

@@ -166,6 +166,24 @@ int tutor_lmhead_argmax(int dtype, const void* x_dev, const void* wte_dev, int B
                         const uint32_t* seen_dev, float penalty, int32_t* out_idx_dev, void* scratch_dev,
                         void* stream);
 int tutor_meanpool(const float* x_dev, float* out_dev, int B, int T, int d, void* stream);
+/* The decode-step (one token per sequence, M <= 128 rows) linears of GPT2Block.forward (modeling_gpt2.py:262-309) as
+ * the engine launches them in bf16 mode: LayerNorm folded into the operand load, split-K over a thread-block cluster
+ * with the reduction done through distributed shared memory, bias + gelu_new or bias + residual fused behind it.
+ * stats_dev [d/128][M][2] holds per-row (mean, M2) of the fp32 residual stream x over each 128-column tile:
+ * tutor_row_tile_stats builds it from x, tutor_decode_linear_residual rewrites it for the x it produces.
+ * ks = K splits (0 = pick; <= 8 for the cluster forms), bn = batch tile 16/32/64/128 (0 = pick).
+ *   ln_linear_partial : partial_dev[ks][M][N] fp32 = per-split sums of LN(x) . W^T  (c_attn; modeling_gpt2.py:185)
+ *   ln_linear_act     : out_bf16_dev[M,N] = act(LN(x) . W^T + bias)                (ln_2 + c_fc + gelu_new; :239-240,:304)
+ *   linear_residual   : x_dev[M,N] += A[M,K] . W^T + bias, in place              (c_proj + residual; :223,:282,:241,:307) */
+int tutor_row_tile_stats(const float* x_dev, float* stats_dev, int M, int d, void* stream);
+int tutor_decode_ln_linear_partial(const float* x_dev, const float* stats_dev, const float* gamma_dev,
+                                   const float* beta_dev, float eps, const void* W_dev, int M, int N, int K, int ks,
+                                   float* partial_dev, void* stream);
+int tutor_decode_ln_linear_act(const float* x_dev, const float* stats_dev, const float* gamma_dev, const float* beta_dev,
+                               float eps, const void* W_dev, const float* bias_dev, int act, int M, int N, int K, int ks,
+                               int bn, void* out_bf16_dev, void* stream);
+int tutor_decode_linear_residual(const void* A_dev, const void* W_dev, const float* bias_dev, int M, int N, int K,
+                                 int ks, int bn, float* x_dev, float* stats_dev, void* stream);
 
 /* No counterpart in the reference: tutor_lmhead_argmax for callers that may not allocate device memory (a host
  * whose own pool owns the whole GPU heap, a latency-critical loop that must stay off the driver's allocation lock,

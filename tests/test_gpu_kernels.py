@@ -196,3 +196,110 @@ def test_meanpool_and_cosine(pkg, lib):
     ref = torch.nn.functional.cosine_similarity(a, b)
     assert (cs - ref).abs().max().item() < 1e-6
     assert abs(pkg.cosine_similarity(a[:1].cpu(), b[:1].cpu()) - ref[0].item()) < 1e-6
+
+
+# ---- decode-step linears with fused LayerNorm operand / cluster split-K reduction (gemm_decode_fused.cu)
+def _tile_stats(lib, pkg, x):
+    M, d = x.shape
+    stats = torch.empty(d // 128, M, 2, device=DEV)
+    pkg._lib.check(lib.tutor_row_tile_stats(ptr(x), ptr(stats), M, d, None))
+    return stats
+
+
+def _ln_bf16(x, g, b, eps):
+    # what the kernel feeds the tensor core: LayerNorm in fp32, rounded to bf16
+    return torch.nn.functional.layer_norm(x, (x.shape[1],), g, b, eps).bfloat16()
+
+
+def test_row_tile_stats(pkg, lib):
+    g = torch.Generator().manual_seed(11)
+    x = (torch.randn(37, 768, generator=g) * 2 + 0.3).to(DEV)
+    stats = _tile_stats(lib, pkg, x)
+    sync()
+    xt = x.view(37, 6, 128).permute(1, 0, 2).double()
+    assert (stats[..., 0] - xt.mean(-1)).abs().max().item() < 1e-6
+    assert rel_err(stats[..., 1], ((xt - xt.mean(-1, keepdim=True)) ** 2).sum(-1)) < 1e-5
+
+
+# (M, N, K, ks, bn): engine shapes for GPT-2 small / large, ragged batches, every batch tile, ring wrap (nk/ks > stages)
+LN_ACT_SHAPES = [(64, 3072, 768, 6, 64), (64, 3072, 768, 0, 0), (16, 5120, 1280, 2, 16), (50, 3072, 768, 3, 32),
+                 (1, 256, 128, 2, 16), (100, 384, 768, 1, 128), (33, 128, 1280, 4, 64), (128, 1024, 512, 8, 128)]
+
+
+@pytest.mark.parametrize("M,N,K,ks,bn", LN_ACT_SHAPES)
+def test_decode_ln_linear_act(pkg, lib, M, N, K, ks, bn):
+    g = torch.Generator().manual_seed(M + N + K)
+    x = (torch.randn(M, K, generator=g) * 1.7 + 0.2).to(DEV)
+    gam, bet = (1 + 0.1 * torch.randn(K, generator=g)).to(DEV), (0.1 * torch.randn(K, generator=g)).to(DEV)
+    W = (torch.randn(N, K, generator=g) * 0.05).to(DEV).bfloat16()
+    bias = torch.randn(N, generator=g).to(DEV)
+    stats = _tile_stats(lib, pkg, x)
+    out = torch.full((M, N), float("nan"), dtype=torch.bfloat16, device=DEV)
+    pkg._lib.check(lib.tutor_decode_ln_linear_act(ptr(x), ptr(stats), ptr(gam), ptr(bet), 1e-5, ptr(W), ptr(bias), 1, M, N,
+                                                  K, ks, bn, ptr(out), None))
+    sync()
+    ref = _linear_ref(_ln_bf16(x, gam, bet, 1e-5).double(), W.double(), bias.double(), None, 1).float()
+    # bf16 rounding of LN(x) can differ by one ulp from torch's for values on a rounding boundary; output is bf16
+    assert rel_err(out, ref) < 1e-2
+
+
+@pytest.mark.parametrize("M,N,K,ks", [(64, 2304, 768, 6), (64, 2304, 768, 0), (16, 3840, 1280, 4), (7, 384, 256, 2),
+                                      (128, 256, 768, 12)])
+def test_decode_ln_linear_partial(pkg, lib, M, N, K, ks):
+    g = torch.Generator().manual_seed(M + N + K + 1)
+    x = (torch.randn(M, K, generator=g) * 1.3 - 0.1).to(DEV)
+    gam, bet = (1 + 0.1 * torch.randn(K, generator=g)).to(DEV), (0.1 * torch.randn(K, generator=g)).to(DEV)
+    W = (torch.randn(N, K, generator=g) * 0.05).to(DEV).bfloat16()
+    stats = _tile_stats(lib, pkg, x)
+    nsplit = ks if ks else 12
+    partial = torch.zeros(nsplit, M, N, device=DEV)
+    pkg._lib.check(lib.tutor_decode_ln_linear_partial(ptr(x), ptr(stats), ptr(gam), ptr(bet), 1e-5, ptr(W), M, N, K, ks,
+                                                      ptr(partial), None))
+    sync()
+    ref = _ln_bf16(x, gam, bet, 1e-5).double() @ W.double().T
+    assert rel_err(partial.double().sum(0), ref) < 2e-3  # a one-ulp bf16 difference in LN(x) shows at ~1e-3
+
+
+@pytest.mark.parametrize("M,N,K,ks,bn", [(64, 768, 768, 6, 32), (64, 768, 3072, 8, 32), (64, 768, 3072, 0, 0),
+                                         (64, 768, 768, 6, 16), (16, 1280, 5120, 8, 16), (50, 256, 512, 4, 64),
+                                         (1, 128, 128, 2, 16), (128, 384, 1024, 8, 128), (100, 768, 768, 3, 32)])
+def test_decode_linear_residual(pkg, lib, M, N, K, ks, bn):
+    g = torch.Generator().manual_seed(M + N + K + 2)
+    A = torch.randn(M, K, generator=g).to(DEV).bfloat16()
+    W = (torch.randn(N, K, generator=g) * 0.05).to(DEV).bfloat16()
+    bias = torch.randn(N, generator=g).to(DEV)
+    x0 = torch.randn(M, N, generator=g).to(DEV)
+    x = x0.clone()
+    stats = torch.full((N // 128, M, 2), float("nan"), device=DEV)
+    pkg._lib.check(lib.tutor_decode_linear_residual(ptr(A), ptr(W), ptr(bias), M, N, K, ks, bn, ptr(x), ptr(stats), None))
+    sync()
+    ref = _linear_ref(A.double(), W.double(), bias.double(), x0.double(), 0)
+    assert rel_err(x, ref.float()) < 1e-5
+    rt = ref.view(M, N // 128, 128).permute(1, 0, 2)
+    assert (stats[..., 0] - rt.mean(-1)).abs().max().item() < 1e-5
+    assert rel_err(stats[..., 1], ((rt - rt.mean(-1, keepdim=True)) ** 2).sum(-1)) < 1e-4
+    # deterministic: a second run from the same input gives the same bits
+    x2 = x0.clone()
+    pkg._lib.check(lib.tutor_decode_linear_residual(ptr(A), ptr(W), ptr(bias), M, N, K, ks, bn, ptr(x2), ptr(stats), None))
+    sync()
+    assert torch.equal(x, x2)
+
+
+def test_decode_fused_chain_matches_layernorm(pkg, lib):
+    """residual GEMM -> statistics -> LN-operand GEMM equals the unfused LayerNorm + linear on the same x."""
+    g = torch.Generator().manual_seed(99)
+    M, d = 64, 768
+    A = torch.randn(M, d, generator=g).to(DEV).bfloat16()
+    Wp = (torch.randn(d, d, generator=g) * 0.05).to(DEV).bfloat16()
+    Wf = (torch.randn(4 * d, d, generator=g) * 0.05).to(DEV).bfloat16()
+    bp, bf = torch.randn(d, generator=g).to(DEV), torch.randn(4 * d, generator=g).to(DEV)
+    gam, bet = (1 + 0.1 * torch.randn(d, generator=g)).to(DEV), (0.1 * torch.randn(d, generator=g)).to(DEV)
+    x = torch.randn(M, d, generator=g).to(DEV)
+    stats = torch.empty(d // 128, M, 2, device=DEV)
+    h = torch.empty(M, 4 * d, dtype=torch.bfloat16, device=DEV)
+    pkg._lib.check(lib.tutor_decode_linear_residual(ptr(A), ptr(Wp), ptr(bp), M, d, d, 0, 0, ptr(x), ptr(stats), None))
+    pkg._lib.check(lib.tutor_decode_ln_linear_act(ptr(x), ptr(stats), ptr(gam), ptr(bet), 1e-5, ptr(Wf), ptr(bf), 1, M,
+                                                  4 * d, d, 0, 0, ptr(h), None))
+    sync()
+    ref = _linear_ref(_ln_bf16(x, gam, bet, 1e-5).double(), Wf.double(), bf.double(), None, 1).float()
+    assert rel_err(h, ref) < 1e-2
