@@ -707,6 +707,195 @@ __global__ void __launch_bounds__(128) attn_prefill_mma_kernel(const bf16* __res
   }
 }
 
+
+// ------------------------------------------------------------------- decode on tensor cores (bf16)
+// Same producer / ring structure as attn_decode_tma_kernel, with the arithmetic moved to mma.sync m16n8k16: the
+// SIMT consumers needed ~50 instructions per key per lane (unpack, FMA, shuffles) and held the kernel at 80 % of
+// the measured HBM peak while the same ring drained without arithmetic reached 94 %.  Here the query is row 0 of
+// a 16-row A operand (rows 1..15 are zero - the tensor pipe is idle anyway), each 64-key chunk costs a warp
+// 16 ldmatrix + 32 MMAs, and the softmax touches 4 scores per lane.  K/V chunks arrive through
+// cp.async.bulk.tensor with the 128-byte swizzle, so ldmatrix (K) and ldmatrix.trans (V) are conflict-free.
+// 96 threads: warps 0-1 consume (32 keys of every chunk each), warp 2 produces.  grid (H, B), 6 CTAs per SM.
+constexpr int DM_THREADS = 96, DM_CHUNK = 64, DM_STAGES = 2;
+
+template <bool FUSED>
+__global__ void __launch_bounds__(DM_THREADS, 6) attn_decode_mma_kernel(
+    const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const bf16* __restrict__ q, bf16* kc,
+    bf16* vc, bf16* __restrict__ out, int H, int Smax, const int* __restrict__ len_dev, int len_host,
+    const float* __restrict__ qkv_partial, int ks, const float* __restrict__ qkv_bias, int B,
+    const int* __restrict__ npad, int safe_rows) {
+  __shared__ __align__(1024) uint8_t sK[DM_STAGES][DM_CHUNK * 128];
+  __shared__ __align__(1024) uint8_t sV[DM_STAGES][DM_CHUNK * 128];
+  __shared__ __align__(8) uint64_t full_bar[DM_STAGES], empty_bar[DM_STAGES];
+  __shared__ float s_new[3][64];
+  __shared__ float sm_m[2], sm_l[2], sm_o[2][64], s_self;
+  const int h = blockIdx.x, b = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row_base = (b * H + h) * Smax;  // first cache row of this (b,h) in the [B*H*Smax, 64] view
+  const size_t base = (size_t)row_base * 64;
+  const int kp = npad ? npad[b] : 0;
+  const int early = min(DM_STAGES, max(0, safe_rows - kp) / DM_CHUNK);  // see attn_decode_tma_kernel
+  if (threadIdx.x == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmK) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmV) : "memory");
+    for (int s = 0; s < DM_STAGES; ++s) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dk_smem(&full_bar[s])), "r"(1));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dk_smem(&empty_bar[s])), "r"(2));
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+  pdl_launch_dependents();
+
+  if (warp == 2) {
+    // ===== producer: one lane streams the cache rows of this (b,h), 64 keys (8 KB of K + 8 KB of V) per stage =====
+    if (lane == 0) {
+      auto copy_chunk = [&](int c) {
+        const int s = c % DM_STAGES;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dk_smem(&full_bar[s])),
+                     "r"(2 * DM_CHUNK * 128) : "memory");
+        const int row = row_base + kp + c * DM_CHUNK;  // rows past the end of the tensor are zero-filled
+        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+                         dk_smem(&sK[s][0])), "l"(&tmK), "r"(dk_smem(&full_bar[s])), "r"(0), "r"(row) : "memory");
+        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+                         dk_smem(&sV[s][0])), "l"(&tmV), "r"(dk_smem(&full_bar[s])), "r"(0), "r"(row) : "memory");
+      };
+      for (int c = 0; c < early; ++c) copy_chunk(c);  // the ring is empty: no wait needed
+      pdl_wait();
+      const int len = len_dev ? *len_dev : len_host;
+      const int nkeys = (FUSED ? len - 1 : len) - kp;
+      const int nchunks = (nkeys + DM_CHUNK - 1) / DM_CHUNK;
+      for (int c = early; c < nchunks; ++c) {
+        dk_wait(&empty_bar[c % DM_STAGES], ((c / DM_STAGES) & 1) ^ 1);
+        copy_chunk(c);
+      }
+    }
+    return;
+  }
+
+  // ===== consumers (64 threads) =====
+  pdl_wait();  // q (or the c_attn partials) come from the preceding kernel; the length counter is final now
+  const int len = len_dev ? *len_dev : len_host;
+  const int nkeys = (FUSED ? len - 1 : len) - kp;
+  const int nchunks = (nkeys + DM_CHUNK - 1) / DM_CHUNK;
+  const int g = lane >> 2, t = lane & 3;
+  if (FUSED) {
+    const int d = H * 64;
+    for (int e = threadIdx.x; e < 192; e += 64) {
+      const int which = e >> 6, i = e & 63;
+      const int n = which * d + h * 64 + i;
+      float acc = qkv_bias[n];
+#pragma unroll 8
+      for (int zz = 0; zz < ks; ++zz) acc += qkv_partial[((size_t)zz * B + b) * (3 * d) + n];
+      const bf16 st = __float2bfloat16_rn(which == 0 ? acc * 0.125f : acc);  // q carries the 1/sqrt(64) scale (exact)
+      if (which != 0) (which == 1 ? kc : vc)[base + (size_t)(len - 1) * 64 + i] = st;  // cache append (no torch.cat)
+      s_new[which][i] = __bfloat162float(st);
+    }
+  } else {
+    const int i = threadIdx.x;
+    s_new[0][i] = __bfloat162float(__float2bfloat16_rn(__bfloat162float(q[((size_t)b * H + h) * 64 + i]) * 0.125f));
+  }
+  asm volatile("bar.sync 1, 64;" ::: "memory");  // consumer warps only
+  // A fragments of the query: row 0 of the 16 x 16 tile is q, rows 1..15 are zero
+  uint32_t qa[4][4];
+#pragma unroll
+  for (int kk = 0; kk < 4; ++kk) {
+    qa[kk][1] = qa[kk][3] = 0u;
+    qa[kk][0] = g == 0 ? pack_bf16x2(s_new[0][kk * 16 + 2 * t], s_new[0][kk * 16 + 2 * t + 1]) : 0u;
+    qa[kk][2] = g == 0 ? pack_bf16x2(s_new[0][kk * 16 + 8 + 2 * t], s_new[0][kk * 16 + 8 + 2 * t + 1]) : 0u;
+  }
+  constexpr float LOG2E = 1.4426950408889634f;
+  float m = -CUDART_INF_F, l = 0.f, o[8][4];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
+  const int mi = lane >> 3, lr = lane & 7;
+
+  for (int c = 0; c < nchunks; ++c) {
+    const int s = c % DM_STAGES;
+    dk_wait(&full_bar[s], (c / DM_STAGES) & 1);
+    const int valid_rows = min(DM_CHUNK, nkeys - c * DM_CHUNK);
+#pragma unroll
+    for (int sub = 0; sub < 2; ++sub) {
+      const int key0 = warp * 32 + sub * 16;
+      uint32_t kb[16], vb[16];
+      {
+        const int krow = key0 + (mi >> 1) * 8 + lr;
+        const uint8_t* kp8 = sK[s] + krow * 128;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) ldmatrix_x4(&kb[kk * 4], kp8 + (((2 * kk + (mi & 1)) ^ (krow & 7)) << 4));
+        const int vrow = key0 + (mi & 1) * 8 + lr;
+        const uint8_t* vp8 = sV[s] + vrow * 128;
+#pragma unroll
+        for (int p = 0; p < 4; ++p) ldmatrix_x4_trans(&vb[p * 4], vp8 + (((2 * p + (mi >> 1)) ^ (vrow & 7)) << 4));
+      }
+      if (sub == 1) {  // both sub-blocks of this warp are in registers: hand the stage back to the producer
+        __syncwarp();
+        if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(dk_smem(&empty_bar[s])) : "memory");
+      }
+      if (key0 >= valid_rows) continue;  // warp-uniform: nothing but masked keys in this sub-block
+      float sc[2][4];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        sc[j][0] = sc[j][1] = sc[j][2] = sc[j][3] = 0.f;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) mma_bf16_16816(sc[j], qa[kk], kb[kk * 4 + 2 * j], kb[kk * 4 + 2 * j + 1]);
+      }
+      if (key0 + 16 > valid_rows) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          if (key0 + j * 8 + 2 * t >= valid_rows) sc[j][0] = -CUDART_INF_F;
+          if (key0 + j * 8 + 2 * t + 1 >= valid_rows) sc[j][1] = -CUDART_INF_F;
+        }
+      }
+      float mx = fmaxf(fmaxf(sc[0][0], sc[0][1]), fmaxf(sc[1][0], sc[1][1]));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+      const float mn = fmaxf(m, mx);  // finite: key0 < valid_rows, so at least one key of the row is unmasked
+      const float corr = fast_exp2((m - mn) * LOG2E), nb = mn * LOG2E;
+      const float p00 = fast_exp2(fmaf(sc[0][0], LOG2E, -nb)), p01 = fast_exp2(fmaf(sc[0][1], LOG2E, -nb));
+      const float p10 = fast_exp2(fmaf(sc[1][0], LOG2E, -nb)), p11 = fast_exp2(fmaf(sc[1][1], LOG2E, -nb));
+      l = l * corr + (p00 + p01) + (p10 + p11);
+      m = mn;
+      uint32_t pa[4] = {pack_bf16x2(p00, p01), 0u, pack_bf16x2(p10, p11), 0u};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { o[j][0] *= corr; o[j][1] *= corr; }
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        mma_bf16_16816(o[2 * p], pa, vb[p * 4], vb[p * 4 + 1]);
+        mma_bf16_16816(o[2 * p + 1], pa, vb[p * 4 + 2], vb[p * 4 + 3]);
+      }
+    }
+  }
+  // row 0 (the query) lives in lanes 0..3 of each consumer warp
+  l += __shfl_xor_sync(0xffffffffu, l, 1);
+  l += __shfl_xor_sync(0xffffffffu, l, 2);
+  if (g == 0) {
+    if (t == 0) { sm_m[warp] = m; sm_l[warp] = l; }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { sm_o[warp][j * 8 + 2 * t] = o[j][0]; sm_o[warp][j * 8 + 2 * t + 1] = o[j][1]; }
+  }
+  if (FUSED && warp == 0) {  // score of the current token's own key (its row is not part of the streamed range)
+    const float d = warp_sum(s_new[0][2 * lane] * s_new[1][2 * lane] + s_new[0][2 * lane + 1] * s_new[1][2 * lane + 1]);
+    if (lane == 0) s_self = d;
+  }
+  asm volatile("bar.sync 1, 64;" ::: "memory");
+  {
+    const int i = threadIdx.x;  // output dim
+    float M = fmaxf(sm_m[0], sm_m[1]);
+    if (FUSED) M = fmaxf(M, s_self);
+    const float w0 = sm_m[0] == -CUDART_INF_F ? 0.f : fast_exp2((sm_m[0] - M) * LOG2E);
+    const float w1 = sm_m[1] == -CUDART_INF_F ? 0.f : fast_exp2((sm_m[1] - M) * LOG2E);
+    float num = w0 * sm_o[0][i] + w1 * sm_o[1][i], den = w0 * sm_l[0] + w1 * sm_l[1];
+    if (FUSED) {
+      const float ws = fast_exp2((s_self - M) * LOG2E);
+      num = fmaf(ws, s_new[2][i], num);
+      den += ws;
+    }
+    out[((size_t)b * H + h) * 64 + i] = __float2bfloat16_rn(num / den);
+  }
+}
+
 }  // namespace
 
 // number of key-range splits: enough CTAs for ~8 per SM, at least 64 keys per split

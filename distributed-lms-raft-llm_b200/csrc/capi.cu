@@ -175,8 +175,8 @@ int tutor_decode_ln_linear_partial(const float* x, const float* stats, const flo
                                    const void* W, int M, int N, int K, int ks, float* partial, void* stream) {
   ARG_CHECK(x && stats && gamma && beta && W && partial && K % 128 == 0, "decode_ln_linear_partial: bad argument");
   if (ks <= 0) ks = k_pick_splitk(N, K, sm_count());
-  return k_gemm_ln_splitk(x, stats, K / 128, gamma, beta, eps, (const bf16*)W, M, N, K, ks, partial,
-                          (cudaStream_t)stream);
+  return k_gemm_ln_splitk(x, stats, K / 128, gamma, beta, eps, (const bf16*)W, M, N, K, ks, k_decode_batch_tile(M),
+                          partial, (cudaStream_t)stream);
 }
 
 int tutor_decode_ln_linear_act(const float* x, const float* stats, const float* gamma, const float* beta, float eps,

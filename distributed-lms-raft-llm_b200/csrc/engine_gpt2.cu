@@ -203,6 +203,26 @@ int forward_decode_fused(tutor_gpt2* e, int lane, int b0, int B) {
                          (uint8_t*)e->lm_scratch + (size_t)lane * e->lm_scratch_lane_bytes, st);
 }
 
+// Tile plan of the fused decode GEMMs.  Measured on B200 (B=64, GPT-2 small; tools/gpu_sweep.sh): cutting the batch into
+// 16-row tiles and splitting K only until tiles x batch tiles x splits reaches ~4/3 of the SM count beats wide batch
+// tiles with deep K splits (0.611 vs 0.652 ms per forward) - fewer fp32 partials cross L2 / DSMEM, and the weight tile
+// shared by the batch tiles is served by L2.
+struct DecodePlan { int bn_qkv, bn_fc, bn_res, ks_qkv, ks_proj, ks_fc, ks_proj2; };
+DecodePlan decode_plan(const tutor_gpt2* e, int B) {
+  const int d = e->d, cap = e->num_sms * 4 / 3;
+  DecodePlan p;
+  p.bn_qkv = p.bn_fc = p.bn_res = 16;
+  auto env = [](const char* name, int& v) { if (const char* s = getenv(name)) v = atoi(s); };
+  env("TUTOR_BN_QKV", p.bn_qkv); env("TUTOR_BN_FC", p.bn_fc); env("TUTOR_BN_RES", p.bn_res);  // A/B knobs
+  p.ks_qkv = k_pick_cluster_splitk(3 * d, d, ceil_div(B, p.bn_qkv), cap);
+  p.ks_proj = k_pick_cluster_splitk(d, d, ceil_div(B, p.bn_res), cap);
+  p.ks_fc = k_pick_cluster_splitk(4 * d, d, ceil_div(B, p.bn_fc), cap);
+  p.ks_proj2 = k_pick_cluster_splitk(d, 4 * d, ceil_div(B, p.bn_res), cap);
+  env("TUTOR_KS_QKV", p.ks_qkv); env("TUTOR_KS_PROJ", p.ks_proj); env("TUTOR_KS_FC", p.ks_fc);
+  env("TUTOR_KS_PROJ2", p.ks_proj2);
+  return p;
+}
+
 // The same forward in 5 launches per layer (gemm_decode_fused.cu): LayerNorm is applied while the consuming GEMM
 // stages its operand (from x and per-tile row statistics), and the split-K sums of c_proj / c_fc / mlp c_proj are
 // closed inside the GEMM by a thread-block cluster reading its peers' shared memory.
@@ -219,29 +239,23 @@ int forward_decode_cluster(tutor_gpt2* e, int lane, int b0, int B) {
   float* stats = e->ln_stats + (size_t)lane * e->ln_stats_lane_elems;
   const size_t kv_off = (size_t)b0 * e->H * e->Smax * 64 * e->esz();
   const int* npad = e->padded ? e->npad + b0 : nullptr;
-  // batch tile of the residual GEMMs (N = d is only d/128 weight tiles): smaller tiles = more CTAs, less DSMEM per CTA
-  const int bn_full = k_decode_batch_tile(B);
-  int bn_res = bn_full;
-  while (bn_res > 16 && ceil_div(d, 128) * ceil_div(B, bn_res / 2) * 8 <= e->num_sms) bn_res /= 2;
-  if (const char* v = getenv("TUTOR_BN_RES")) bn_res = atoi(v);
-  const int bt_res = ceil_div(B, bn_res);
-  const int ks_qkv = k_pick_splitk(3 * d, d, e->num_sms);
-  const int ks_proj = k_pick_cluster_splitk(d, d, bt_res, e->num_sms);
-  const int ks_fc = k_pick_cluster_splitk(4 * d, d, 1, e->num_sms);
-  const int ks_proj2 = k_pick_cluster_splitk(d, 4 * d, bt_res, e->num_sms);
+  const DecodePlan pl = decode_plan(e, B);
+  const int bn_qkv = pl.bn_qkv, bn_fc = pl.bn_fc, bn_res = pl.bn_res;
+  const int ks_qkv = pl.ks_qkv, ks_proj = pl.ks_proj, ks_fc = pl.ks_fc, ks_proj2 = pl.ks_proj2;
   TRY(k_gpt2_embed(e->ids + (size_t)b0 * e->ids_ld, e->ids_ld, len, 1, e->wte, e->dt, e->wpe, d, x, B, npad, st));
   TRY(k_row_tile_stats(x, stats, B, d, st));
   for (int l = 0; l < e->L; ++l) {
     const Gpt2Layer& w = e->layers[l];
     void* kc = (uint8_t*)e->kcache(l) + kv_off;
     void* vc = (uint8_t*)e->vcache(l) + kv_off;
-    TRY(k_gemm_ln_splitk(x, stats, nst, w.ln1_g, w.ln1_b, eps, (const bf16*)w.qkv.w, B, 3 * d, d, ks_qkv, partial, st));
+    TRY(k_gemm_ln_splitk(x, stats, nst, w.ln1_g, w.ln1_b, eps, (const bf16*)w.qkv.w, B, 3 * d, d, ks_qkv, bn_qkv, partial,
+                         st));
     TRY(k_attn_decode_fused(partial, ks_qkv, w.qkv.b, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
                             e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, npad,
                             e->cur_T, st));
     TRY(k_gemm_resid_stats(att, (const bf16*)w.proj.w, w.proj.b, B, d, d, ks_proj, bn_res, x, stats, st));
     TRY(k_gemm_ln_act(x, stats, nst, w.ln2_g, w.ln2_b, eps, (const bf16*)w.fc.w, w.fc.b, ACT_GELU_TANH, B, 4 * d, d, ks_fc,
-                      bn_full, hb, st));
+                      bn_fc, hb, st));
     TRY(k_gemm_resid_stats(hb, (const bf16*)w.proj2.w, w.proj2.b, B, d, 4 * d, ks_proj2, bn_res, x, stats, st));
   }
   TRY(k_layernorm(x, 1, 0, e->lnf_g, e->lnf_b, eps, nullptr, xl, B, d, st));
@@ -305,6 +319,8 @@ int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
         const size_t n = (size_t)k_pick_splitk(s[0], s[1], e->num_sms) * nb * s[0];
         if (n > elems) elems = n;
       }
+      const size_t qkv_elems = (size_t)decode_plan(e, nb).ks_qkv * nb * 3 * d;  // the cluster path's c_attn partials
+      if (qkv_elems > elems) elems = qkv_elems;
       e->partial_lane_elems = elems;  // every lane slice can hold the whole batch (lanes only ever hold a part of it)
       TRY(dev_alloc(&e->partial, tutor_gpt2::MAX_LANES * elems * sizeof(float)));
       dev_free(e->ln_stats);

@@ -423,12 +423,12 @@ int check_common(int M, int N, int K, int ks, int bn) {
 // smallest batch tile (UMMA N) that covers M in one tile
 int k_decode_batch_tile(int M) { return M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : 128; }
 
-// largest split count <= 8 (portable cluster size) that divides K/64 and keeps tiles * batch_tiles * ks within one wave
-int k_pick_cluster_splitk(int N, int K, int batch_tiles, int num_sms) {
+// largest split count <= 8 (portable cluster size) that divides K/64 and keeps tiles * batch_tiles * ks <= max_ctas
+int k_pick_cluster_splitk(int N, int K, int batch_tiles, int max_ctas) {
   const int tiles = ceil_div(N, BM) * batch_tiles, nk = K / BK;
   int best = 1;
   for (int ks = 1; ks <= nk && ks <= 8; ++ks)
-    if (nk % ks == 0 && tiles * ks <= num_sms) best = ks;
+    if (nk % ks == 0 && tiles * ks <= max_ctas) best = ks;
   return best;
 }
 
@@ -442,12 +442,12 @@ int k_row_tile_stats(const float* x, float* stats, int M, int d, cudaStream_t st
 
 // partial[z][m][n] = sum over K slice z of LayerNorm(x)[m,:] . W[n,:]      (c_attn; the attention kernel reduces)
 int k_gemm_ln_splitk(const float* x, const float* stats, int nst, const float* gamma, const float* beta, float eps,
-                     const bf16* W, int M, int N, int K, int ks, float* partial, cudaStream_t st) {
-  TRY(check_common(M, N, K, ks, 16));
+                     const bf16* W, int M, int N, int K, int ks, int bn, float* partial, cudaStream_t st) {
+  TRY(check_common(M, N, K, ks, bn));
   ARG_CHECK(nst >= 1 && K % nst == 0, "decode gemm: %d statistic tiles do not divide K=%d", nst, K);
   LnOperand ln{x, stats, nst, gamma, beta, eps};
   FusedEpi ep{};
-  return launch_bn<true, MODE_PARTIAL>(k_decode_batch_tile(M), W, N, nullptr, M, K, ks, ln, ep, partial, st);
+  return launch_bn<true, MODE_PARTIAL>(bn, W, N, nullptr, M, K, ks, ln, ep, partial, st);
 }
 
 // out[m,n] = act(bias[n] + LayerNorm(x)[m,:] . W[n,:]) as bf16                       (c_fc + gelu_new)

@@ -33,10 +33,10 @@ int k_make_map_partial(void* tensor_map, float* ptr, int N, int M, int ks, int b
 // reduction done across a thread-block cluster (DSMEM) with bias + gelu / bias + residual fused behind it.
 // stats: [d/128][M][2] = per-row (mean, M2) of x over each 128-column tile.
 int k_decode_batch_tile(int M);
-int k_pick_cluster_splitk(int N, int K, int batch_tiles, int num_sms);
+int k_pick_cluster_splitk(int N, int K, int batch_tiles, int max_ctas);
 int k_row_tile_stats(const float* x, float* stats, int M, int d, cudaStream_t st);
 int k_gemm_ln_splitk(const float* x, const float* stats, int nst, const float* gamma, const float* beta, float eps,
-                     const bf16* W, int M, int N, int K, int ks, float* partial, cudaStream_t st);
+                     const bf16* W, int M, int N, int K, int ks, int bn, float* partial, cudaStream_t st);
 int k_gemm_ln_act(const float* x, const float* stats, int nst, const float* gamma, const float* beta, float eps,
                   const bf16* W, const float* bias, int act, int M, int N, int K, int ks, int bn, bf16* out,
                   cudaStream_t st);

@@ -68,7 +68,7 @@ int main() {
     printf("--- PDL %s\n", pdl ? "on" : "off");
     float t;
     for (int ks : {6, 12}) {
-      t = time_graph(st, 96, pdl, [&](int i) { if (k_gemm_ln_splitk(xf, stats, 6, gam, bias, 1e-5f, W(i), B, 3 * d, d, ks, partial, st)) DIE(); });
+      t = time_graph(st, 96, pdl, [&](int i) { if (k_gemm_ln_splitk(xf, stats, 6, gam, bias, 1e-5f, W(i), B, 3 * d, d, ks, 64, partial, st)) DIE(); });
       printf("c_attn LN -> partials   ks=%2d         %6.2f us/kernel\n", ks, t); show_trace();
     }
     for (auto cfg : {std::pair<int,int>{6, 64}, {3, 32}, {2, 16}}) {
@@ -87,7 +87,7 @@ int main() {
     t = time_graph(st, 96, pdl, [&](int i) {
       int rc = 0;
       switch (i & 3) {
-        case 0: rc = k_gemm_ln_splitk(xf, stats, 6, gam, bias, 1e-5f, W(i), B, 3 * d, d, 6, partial, st); break;
+        case 0: rc = k_gemm_ln_splitk(xf, stats, 6, gam, bias, 1e-5f, W(i), B, 3 * d, d, 6, 64, partial, st); break;
         case 1: rc = k_gemm_resid_stats(a, W(i), bias, B, d, d, 6, 32, xf, stats, st); break;
         case 2: rc = k_gemm_ln_act(xf, stats, 6, gam, bias, 1e-5f, W(i), bias, ACT_GELU_TANH, B, 4 * d, d, 6, 64, h, st); break;
         default: rc = k_gemm_resid_stats(h, W(i), bias, B, d, 4 * d, 8, 32, xf, stats, st);
