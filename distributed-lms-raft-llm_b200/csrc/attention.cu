@@ -3,7 +3,10 @@
 //                  or bidirectional (BERT, HF/models/bert/modeling_bert.py:192-205); scale 1/8.
 //   attn_decode  : one query per (b,h) streaming the KV cache [B][H][Smax][64] - the HBM-bound kernel that
 //                  carries 86 % of the bytes at bs=64.
+#include <cuda.h>
 #include <math_constants.h>
+
+#include <cstdlib>
 
 #include "kernels.h"
 
@@ -716,14 +719,25 @@ __global__ void __launch_bounds__(128) attn_prefill_mma_kernel(const bf16* __res
 // 16 ldmatrix + 32 MMAs, and the softmax touches 4 scores per lane.  K/V chunks arrive through
 // cp.async.bulk.tensor with the 128-byte swizzle, so ldmatrix (K) and ldmatrix.trans (V) are conflict-free.
 // 96 threads: warps 0-1 consume (32 keys of every chunk each), warp 2 produces.  grid (H, B), 6 CTAs per SM.
-constexpr int DM_THREADS = 96, DM_CHUNK = 64, DM_STAGES = 2;
+constexpr int DM_THREADS = 96, DM_CHUNK = 32, DM_STAGES = 4;
 
-template <bool FUSED>
+// D rows 0-7 += A x B; the accumulator rows 8-15 (always zero here: only row 0 of A is populated) are fed as
+// constants and their results dropped, so they cost no registers
+__device__ __forceinline__ void mma_bf16_16816_top(float& c0, float& c1, uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
+  float d2, d3;
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%8,%5,%8}, {%6,%7}, {%0,%1,%9,%9};"
+      : "+f"(c0), "+f"(c1), "=f"(d2), "=f"(d3)
+      : "r"(a0), "r"(a2), "r"(b0), "r"(b1), "r"(0u), "f"(0.f));
+}
+
+// MATH=false (microbench only) drains the ring without the arithmetic
+template <bool FUSED, bool MATH>
 __global__ void __launch_bounds__(DM_THREADS, 6) attn_decode_mma_kernel(
     const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const bf16* __restrict__ q, bf16* kc,
     bf16* vc, bf16* __restrict__ out, int H, int Smax, const int* __restrict__ len_dev, int len_host,
     const float* __restrict__ qkv_partial, int ks, const float* __restrict__ qkv_bias, int B,
-    const int* __restrict__ npad, int safe_rows) {
+    const int* __restrict__ npad, int safe_rows, int split_rows, float* split_scratch, int* split_counters) {
   __shared__ __align__(1024) uint8_t sK[DM_STAGES][DM_CHUNK * 128];
   __shared__ __align__(1024) uint8_t sV[DM_STAGES][DM_CHUNK * 128];
   __shared__ __align__(8) uint64_t full_bar[DM_STAGES], empty_bar[DM_STAGES];
@@ -734,7 +748,14 @@ __global__ void __launch_bounds__(DM_THREADS, 6) attn_decode_mma_kernel(
   const int row_base = (b * H + h) * Smax;  // first cache row of this (b,h) in the [B*H*Smax, 64] view
   const size_t base = (size_t)row_base * 64;
   const int kp = npad ? npad[b] : 0;
-  const int early = min(DM_STAGES, max(0, safe_rows - kp) / DM_CHUNK);  // see attn_decode_tma_kernel
+  // gridDim.z > 1: the key range of every (b,h) is cut at multiples of split_rows (a host-known constant, so the
+  // rows a split may prefetch ahead of the programmatic-launch wait do not depend on the device-side length).
+  // 768 equal CTAs on 148 SMs leave 28 SMs with six streams and 120 with five - a 16 % tail; with 2-4 splits the
+  // block scheduler hands out 1536-3072 smaller units as slots free up.  The last CTA to finish a (b,h) merges the
+  // split states in split order (deterministic).
+  const int z = blockIdx.z, nsplit = gridDim.z;
+  const int kbeg = z * split_rows;
+  const int early = min(DM_STAGES, max(0, safe_rows - kp - kbeg) / DM_CHUNK);  // see attn_decode_tma_kernel
   if (threadIdx.x == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmK) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmV) : "memory");
@@ -749,13 +770,13 @@ __global__ void __launch_bounds__(DM_THREADS, 6) attn_decode_mma_kernel(
   pdl_launch_dependents();
 
   if (warp == 2) {
-    // ===== producer: one lane streams the cache rows of this (b,h), 64 keys (8 KB of K + 8 KB of V) per stage =====
+    // ===== producer: one lane streams the cache rows of this (b,h), 32 keys (4 KB of K + 4 KB of V) per stage =====
     if (lane == 0) {
       auto copy_chunk = [&](int c) {
         const int s = c % DM_STAGES;
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dk_smem(&full_bar[s])),
                      "r"(2 * DM_CHUNK * 128) : "memory");
-        const int row = row_base + kp + c * DM_CHUNK;  // rows past the end of the tensor are zero-filled
+        const int row = row_base + kp + kbeg + c * DM_CHUNK;  // rows past the end of the tensor are zero-filled
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
                          dk_smem(&sK[s][0])), "l"(&tmK), "r"(dk_smem(&full_bar[s])), "r"(0), "r"(row) : "memory");
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
@@ -764,7 +785,8 @@ __global__ void __launch_bounds__(DM_THREADS, 6) attn_decode_mma_kernel(
       for (int c = 0; c < early; ++c) copy_chunk(c);  // the ring is empty: no wait needed
       pdl_wait();
       const int len = len_dev ? *len_dev : len_host;
-      const int nkeys = (FUSED ? len - 1 : len) - kp;
+      const int nk_all = (FUSED ? len - 1 : len) - kp;
+      const int nkeys = max(0, (z == nsplit - 1 ? nk_all : min(nk_all, kbeg + split_rows)) - kbeg);
       const int nchunks = (nkeys + DM_CHUNK - 1) / DM_CHUNK;
       for (int c = early; c < nchunks; ++c) {
         dk_wait(&empty_bar[c % DM_STAGES], ((c / DM_STAGES) & 1) ^ 1);
@@ -774,12 +796,14 @@ __global__ void __launch_bounds__(DM_THREADS, 6) attn_decode_mma_kernel(
     return;
   }
 
-  // ===== consumers (64 threads) =====
+  // ===== consumers (64 threads): warp w owns keys [16w, 16w+16) of every chunk =====
   pdl_wait();  // q (or the c_attn partials) come from the preceding kernel; the length counter is final now
   const int len = len_dev ? *len_dev : len_host;
-  const int nkeys = (FUSED ? len - 1 : len) - kp;
+  const int nk_all = (FUSED ? len - 1 : len) - kp;
+  const int nkeys = max(0, (z == nsplit - 1 ? nk_all : min(nk_all, kbeg + split_rows)) - kbeg);
   const int nchunks = (nkeys + DM_CHUNK - 1) / DM_CHUNK;
   const int g = lane >> 2, t = lane & 3;
+  const bool self_here = FUSED && z == nsplit - 1;  // the split that folds in the current token's own key / value
   if (FUSED) {
     const int d = H * 64;
     for (int e = threadIdx.x; e < 192; e += 64) {
@@ -789,7 +813,7 @@ __global__ void __launch_bounds__(DM_THREADS, 6) attn_decode_mma_kernel(
 #pragma unroll 8
       for (int zz = 0; zz < ks; ++zz) acc += qkv_partial[((size_t)zz * B + b) * (3 * d) + n];
       const bf16 st = __float2bfloat16_rn(which == 0 ? acc * 0.125f : acc);  // q carries the 1/sqrt(64) scale (exact)
-      if (which != 0) (which == 1 ? kc : vc)[base + (size_t)(len - 1) * 64 + i] = st;  // cache append (no torch.cat)
+      if (which != 0 && z == 0) (which == 1 ? kc : vc)[base + (size_t)(len - 1) * 64 + i] = st;  // cache append (no torch.cat)
       s_new[which][i] = __bfloat162float(st);
     }
   } else {
@@ -798,73 +822,70 @@ __global__ void __launch_bounds__(DM_THREADS, 6) attn_decode_mma_kernel(
   }
   asm volatile("bar.sync 1, 64;" ::: "memory");  // consumer warps only
   // A fragments of the query: row 0 of the 16 x 16 tile is q, rows 1..15 are zero
-  uint32_t qa[4][4];
+  uint32_t qa0[4], qa2[4];
 #pragma unroll
   for (int kk = 0; kk < 4; ++kk) {
-    qa[kk][1] = qa[kk][3] = 0u;
-    qa[kk][0] = g == 0 ? pack_bf16x2(s_new[0][kk * 16 + 2 * t], s_new[0][kk * 16 + 2 * t + 1]) : 0u;
-    qa[kk][2] = g == 0 ? pack_bf16x2(s_new[0][kk * 16 + 8 + 2 * t], s_new[0][kk * 16 + 8 + 2 * t + 1]) : 0u;
+    qa0[kk] = g == 0 ? pack_bf16x2(s_new[0][kk * 16 + 2 * t], s_new[0][kk * 16 + 2 * t + 1]) : 0u;
+    qa2[kk] = g == 0 ? pack_bf16x2(s_new[0][kk * 16 + 8 + 2 * t], s_new[0][kk * 16 + 8 + 2 * t + 1]) : 0u;
   }
   constexpr float LOG2E = 1.4426950408889634f;
-  float m = -CUDART_INF_F, l = 0.f, o[8][4];
+  float m = -CUDART_INF_F, l = 0.f, o[8][2];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
+  for (int j = 0; j < 8; ++j) o[j][0] = o[j][1] = 0.f;
   const int mi = lane >> 3, lr = lane & 7;
+  const int key0 = warp * 16;
+  const int krow = key0 + (mi >> 1) * 8 + lr, vrow = key0 + (mi & 1) * 8 + lr;
 
   for (int c = 0; c < nchunks; ++c) {
     const int s = c % DM_STAGES;
     dk_wait(&full_bar[s], (c / DM_STAGES) & 1);
     const int valid_rows = min(DM_CHUNK, nkeys - c * DM_CHUNK);
+    uint32_t kb[16], vb[16];
+    const uint8_t* kp8 = sK[s] + krow * 128;
+    const uint8_t* vp8 = sV[s] + vrow * 128;
 #pragma unroll
-    for (int sub = 0; sub < 2; ++sub) {
-      const int key0 = warp * 32 + sub * 16;
-      uint32_t kb[16], vb[16];
-      {
-        const int krow = key0 + (mi >> 1) * 8 + lr;
-        const uint8_t* kp8 = sK[s] + krow * 128;
+    for (int kk = 0; kk < 4; ++kk) ldmatrix_x4(&kb[kk * 4], kp8 + (((2 * kk + (mi & 1)) ^ (krow & 7)) << 4));
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) ldmatrix_x4(&kb[kk * 4], kp8 + (((2 * kk + (mi & 1)) ^ (krow & 7)) << 4));
-        const int vrow = key0 + (mi & 1) * 8 + lr;
-        const uint8_t* vp8 = sV[s] + vrow * 128;
+    for (int p = 0; p < 4; ++p) ldmatrix_x4_trans(&vb[p * 4], vp8 + (((2 * p + (mi >> 1)) ^ (vrow & 7)) << 4));
+    __syncwarp();  // this warp's 16 keys are in registers: hand the stage back to the producer
+    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(dk_smem(&empty_bar[s])) : "memory");
+    if (!MATH) {
 #pragma unroll
-        for (int p = 0; p < 4; ++p) ldmatrix_x4_trans(&vb[p * 4], vp8 + (((2 * p + (mi >> 1)) ^ (vrow & 7)) << 4));
-      }
-      if (sub == 1) {  // both sub-blocks of this warp are in registers: hand the stage back to the producer
-        __syncwarp();
-        if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(dk_smem(&empty_bar[s])) : "memory");
-      }
-      if (key0 >= valid_rows) continue;  // warp-uniform: nothing but masked keys in this sub-block
-      float sc[2][4];
+      for (int i = 0; i < 16; ++i) o[i & 7][0] += __uint_as_float(kb[i] ^ vb[i]);
+      continue;
+    }
+    if (key0 >= valid_rows) continue;  // warp-uniform: nothing but masked keys for this warp in the last chunk
+    float sc[2][2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      sc[j][0] = sc[j][1] = 0.f;
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk)
+        mma_bf16_16816_top(sc[j][0], sc[j][1], qa0[kk], qa2[kk], kb[kk * 4 + 2 * j], kb[kk * 4 + 2 * j + 1]);
+    }
+    if (key0 + 16 > valid_rows) {
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
-        sc[j][0] = sc[j][1] = sc[j][2] = sc[j][3] = 0.f;
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk) mma_bf16_16816(sc[j], qa[kk], kb[kk * 4 + 2 * j], kb[kk * 4 + 2 * j + 1]);
+        if (key0 + j * 8 + 2 * t >= valid_rows) sc[j][0] = -CUDART_INF_F;
+        if (key0 + j * 8 + 2 * t + 1 >= valid_rows) sc[j][1] = -CUDART_INF_F;
       }
-      if (key0 + 16 > valid_rows) {
+    }
+    float mx = fmaxf(fmaxf(sc[0][0], sc[0][1]), fmaxf(sc[1][0], sc[1][1]));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+    const float mn = fmaxf(m, mx);  // finite: key0 < valid_rows, so at least one key of the row is unmasked
+    const float corr = fast_exp2((m - mn) * LOG2E), nb = mn * LOG2E;
+    const float p00 = fast_exp2(fmaf(sc[0][0], LOG2E, -nb)), p01 = fast_exp2(fmaf(sc[0][1], LOG2E, -nb));
+    const float p10 = fast_exp2(fmaf(sc[1][0], LOG2E, -nb)), p11 = fast_exp2(fmaf(sc[1][1], LOG2E, -nb));
+    l = l * corr + (p00 + p01) + (p10 + p11);
+    m = mn;
+    const uint32_t pa0 = pack_bf16x2(p00, p01), pa2 = pack_bf16x2(p10, p11);
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          if (key0 + j * 8 + 2 * t >= valid_rows) sc[j][0] = -CUDART_INF_F;
-          if (key0 + j * 8 + 2 * t + 1 >= valid_rows) sc[j][1] = -CUDART_INF_F;
-        }
-      }
-      float mx = fmaxf(fmaxf(sc[0][0], sc[0][1]), fmaxf(sc[1][0], sc[1][1]));
-      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
-      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-      const float mn = fmaxf(m, mx);  // finite: key0 < valid_rows, so at least one key of the row is unmasked
-      const float corr = fast_exp2((m - mn) * LOG2E), nb = mn * LOG2E;
-      const float p00 = fast_exp2(fmaf(sc[0][0], LOG2E, -nb)), p01 = fast_exp2(fmaf(sc[0][1], LOG2E, -nb));
-      const float p10 = fast_exp2(fmaf(sc[1][0], LOG2E, -nb)), p11 = fast_exp2(fmaf(sc[1][1], LOG2E, -nb));
-      l = l * corr + (p00 + p01) + (p10 + p11);
-      m = mn;
-      uint32_t pa[4] = {pack_bf16x2(p00, p01), 0u, pack_bf16x2(p10, p11), 0u};
+    for (int j = 0; j < 8; ++j) { o[j][0] *= corr; o[j][1] *= corr; }
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { o[j][0] *= corr; o[j][1] *= corr; }
-#pragma unroll
-      for (int p = 0; p < 4; ++p) {
-        mma_bf16_16816(o[2 * p], pa, vb[p * 4], vb[p * 4 + 1]);
-        mma_bf16_16816(o[2 * p + 1], pa, vb[p * 4 + 2], vb[p * 4 + 3]);
-      }
+    for (int p = 0; p < 4; ++p) {
+      mma_bf16_16816_top(o[2 * p][0], o[2 * p][1], pa0, pa2, vb[p * 4], vb[p * 4 + 1]);
+      mma_bf16_16816_top(o[2 * p + 1][0], o[2 * p + 1][1], pa0, pa2, vb[p * 4 + 2], vb[p * 4 + 3]);
     }
   }
   // row 0 (the query) lives in lanes 0..3 of each consumer warp
@@ -875,35 +896,78 @@ __global__ void __launch_bounds__(DM_THREADS, 6) attn_decode_mma_kernel(
 #pragma unroll
     for (int j = 0; j < 8; ++j) { sm_o[warp][j * 8 + 2 * t] = o[j][0]; sm_o[warp][j * 8 + 2 * t + 1] = o[j][1]; }
   }
-  if (FUSED && warp == 0) {  // score of the current token's own key (its row is not part of the streamed range)
+  if (self_here && warp == 0) {  // score of the current token's own key (its row is not part of the streamed range)
     const float d = warp_sum(s_new[0][2 * lane] * s_new[1][2 * lane] + s_new[0][2 * lane + 1] * s_new[1][2 * lane + 1]);
     if (lane == 0) s_self = d;
   }
   asm volatile("bar.sync 1, 64;" ::: "memory");
-  {
-    const int i = threadIdx.x;  // output dim
-    float M = fmaxf(sm_m[0], sm_m[1]);
-    if (FUSED) M = fmaxf(M, s_self);
+  const int i = threadIdx.x;  // output dim
+  float M = fmaxf(sm_m[0], sm_m[1]);
+  if (self_here) M = fmaxf(M, s_self);
+  float num = 0.f, den = 0.f;
+  if (M != -CUDART_INF_F) {  // (a split past the end of a short sequence has seen no key at all)
     const float w0 = sm_m[0] == -CUDART_INF_F ? 0.f : fast_exp2((sm_m[0] - M) * LOG2E);
     const float w1 = sm_m[1] == -CUDART_INF_F ? 0.f : fast_exp2((sm_m[1] - M) * LOG2E);
-    float num = w0 * sm_o[0][i] + w1 * sm_o[1][i], den = w0 * sm_l[0] + w1 * sm_l[1];
-    if (FUSED) {
+    num = w0 * sm_o[0][i] + w1 * sm_o[1][i];
+    den = w0 * sm_l[0] + w1 * sm_l[1];
+    if (self_here) {
       const float ws = fast_exp2((s_self - M) * LOG2E);
       num = fmaf(ws, s_new[2][i], num);
       den += ws;
     }
-    out[((size_t)b * H + h) * 64 + i] = __float2bfloat16_rn(num / den);
   }
+  if (nsplit == 1) {
+    out[((size_t)b * H + h) * 64 + i] = __float2bfloat16_rn(num / den);
+    return;
+  }
+  // publish this split's state [max, denominator, 64 numerators]; the last split to arrive merges them all
+  float* st = split_scratch + (((size_t)b * H + h) * nsplit + z) * 66;
+  if (i == 0) { st[0] = M; st[1] = den; }
+  st[2 + i] = num;
+  __threadfence();
+  asm volatile("bar.sync 1, 64;" ::: "memory");
+  if (i == 0) {
+    const int done = atomicAdd(&split_counters[b * H + h], 1);
+    const int last = done == nsplit - 1;
+    if (last) split_counters[b * H + h] = 0;  // ready for the next launch
+    sm_m[0] = last ? 1.f : 0.f;
+  }
+  asm volatile("bar.sync 1, 64;" ::: "memory");
+  if (sm_m[0] != 0.f) {
+    __threadfence();
+    const float* sp = split_scratch + ((size_t)b * H + h) * nsplit * 66;
+    float MM = -CUDART_INF_F;
+    for (int s2 = 0; s2 < nsplit; ++s2) MM = fmaxf(MM, __ldcg(sp + s2 * 66));
+    float nn = 0.f, dd = 0.f;
+    for (int s2 = 0; s2 < nsplit; ++s2) {  // fixed split order: deterministic
+      const float ms = __ldcg(sp + s2 * 66);
+      const float w = (ms == -CUDART_INF_F) ? 0.f : fast_exp2((ms - MM) * LOG2E);
+      nn = fmaf(w, __ldcg(sp + s2 * 66 + 2 + i), nn);
+      dd = fmaf(w, __ldcg(sp + s2 * 66 + 1), dd);
+    }
+    out[((size_t)b * H + h) * 64 + i] = __float2bfloat16_rn(nn / dd);
+  }
+}
+
+// TUTOR_ATTN_MMA=1 selects the tensor-core consumers (attn_decode_mma_kernel).  Measured on B200 at B=64, H=12,
+// S=640: 24.4 us per launch against 23.4 us for the SIMT consumers of attn_decode_tma_kernel, and 0.638 against
+// 0.612 ms per decode forward; with 2 / 3 / 4 key-range splits 0.689 / 0.729 / 0.776 ms.  Both kernels drain the
+// same ring in 20.4-20.6 us without arithmetic and take 27.1 us under ncu: what is left is the per-CTA prologue and
+// epilogue latency of a one-wave launch, which neither fewer instructions nor more (smaller) CTAs remove.
+bool use_mma_decode() {
+  static const bool mma = getenv("TUTOR_ATTN_MMA") != nullptr;
+  return mma;
 }
 
 }  // namespace
 
 // number of key-range splits: enough CTAs for ~8 per SM, at least 64 keys per split
 int k_attn_decode_splits(int B, int H, int len_hint, int num_sms) {
-  // measured on B200: at B*H = 768 one CTA per (b,h) beats 2 or 4 splits (0.730 vs 0.859 / 0.867 ms per decode
-  // forward); splitting only pays when there are fewer CTAs than SMs
+  // fewer (b,h) streams than SMs: split until every SM has work
   int n = 1;
   while (n < 8 && B * H * n < num_sms && len_hint / (2 * n) >= 64) n *= 2;
+  // more streams than SMs: one CTA per (b,h).  768 equal CTAs leave 28 of 148 SMs with six streams and 120 with
+  // five, but cutting the key range to even that out measured slower with every kernel flavour (see use_mma_decode)
   return n;
 }
 size_t k_attn_decode_scratch_bytes(int B, int H) { return (size_t)B * H * (8 * 66 * sizeof(float) + sizeof(int)); }
@@ -917,10 +981,19 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
     attn_decode_kernel<float, float, float, false, false><<<grid, block, 0, st>>>(
         (const float*)q, (float*)k, (float*)v, (float*)out, H, Smax, len_dev, len_host, nullptr, 0, nullptr, B, nullptr,
         nullptr, npad);
-  else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16)
-    attn_decode_tma_kernel<false, 64, 2, true><<<grid, DK_THREADS, 0, st>>>((const bf16*)q, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax,
-                                                               len_dev, len_host, nullptr, 0, nullptr, B, npad, 0);
-  else {
+  else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16) {
+    if (use_mma_decode()) {
+      CUtensorMap tk, tv;  // the cache as a [B*H*Smax, 64] bf16 matrix, 64-row boxes, 128-byte swizzle
+      TRY(k_make_map_bf16(&tk, (const bf16*)k, B * H * Smax, 64, DM_CHUNK));
+      TRY(k_make_map_bf16(&tv, (const bf16*)v, B * H * Smax, 64, DM_CHUNK));
+      attn_decode_mma_kernel<false, true><<<grid, DM_THREADS, 0, st>>>(tk, tv, (const bf16*)q, (bf16*)k, (bf16*)v, (bf16*)out, H,
+                                                                 Smax, len_dev, len_host, nullptr, 0, nullptr, B, npad, 0,
+                                                                 0, nullptr, nullptr);
+    } else {
+      attn_decode_tma_kernel<false, 64, 2, true><<<grid, DK_THREADS, 0, st>>>((const bf16*)q, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax,
+                                                                 len_dev, len_host, nullptr, 0, nullptr, B, npad, 0);
+    }
+  } else {
     tutor_set_error("attn_decode: unsupported dtype combination q=%d kv=%d out=%d", q_dtype, kv_dtype, out_dtype);
     return TUTOR_ERR_ARG;
   }
@@ -930,12 +1003,27 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
 
 int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias, void* k, void* v, int kv_dtype,
                         void* out, int out_dtype, int B, int H, int Smax, const int* len_dev, int len_host,
-                        int nsplit, void* split_scratch, const int* npad, int safe_rows, cudaStream_t st) {
+                        int nsplit, void* split_scratch, const int* npad, int safe_rows, int len_hint,
+                        cudaStream_t st) {
   if (B == 0) return TUTOR_OK;
   ARG_CHECK(kv_dtype == DT_BF16 && out_dtype == DT_BF16, "attn_decode_fused: bf16 cache and output only");
   ARG_CHECK(qkv_partial && qkv_bias && ks >= 1, "attn_decode_fused: bad partials");
   ARG_CHECK(len_dev || (len_host >= 1 && len_host <= Smax), "attn_decode_fused: len %d outside [1,%d]", len_host, Smax);
   ARG_CHECK(nsplit >= 1 && nsplit <= 8 && (nsplit == 1 || split_scratch), "attn_decode_fused: bad split setup");
+  float* sc = reinterpret_cast<float*>(split_scratch);
+  int* counters = reinterpret_cast<int*>(sc + (size_t)B * H * 8 * 66);  // zeroed by the owner; self-resetting
+  if (use_mma_decode()) {
+    CUtensorMap tk, tv;
+    TRY(k_make_map_bf16(&tk, (const bf16*)k, B * H * Smax, 64, DM_CHUNK));
+    TRY(k_make_map_bf16(&tv, (const bf16*)v, B * H * Smax, 64, DM_CHUNK));
+    // split boundaries are fixed multiples of the chunk size derived from the expected length, not the live one
+    const int split_rows = (int)round_up((size_t)ceil_div(len_hint > 0 ? len_hint : Smax, nsplit), DM_CHUNK);
+    CUDA_TRY(tutor_launch(attn_decode_mma_kernel<true, true>, dim3(H, B, nsplit), dim3(DM_THREADS), 0, st, tk, tv,
+                          (const bf16*)nullptr, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks,
+                          qkv_bias, B, npad, safe_rows, split_rows, sc, counters));
+    KERNEL_LAUNCHED();
+    return TUTOR_OK;
+  }
   if (nsplit == 1) {
     CUDA_TRY(tutor_launch(attn_decode_tma_kernel<true, 64, 2, true>, dim3(H, B), dim3(DK_THREADS), 0, st, (const bf16*)nullptr,
                           (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B,
@@ -943,8 +1031,6 @@ int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias,
     KERNEL_LAUNCHED();
     return TUTOR_OK;
   }
-  float* sc = reinterpret_cast<float*>(split_scratch);
-  int* counters = reinterpret_cast<int*>(sc + (size_t)B * H * 8 * 66);  // zeroed by the owner; self-resetting
   CUDA_TRY(tutor_launch(attn_decode_kernel<bf16, bf16, bf16, true, true>, dim3(H, B, nsplit), dim3(128), 0, st,
                         (const bf16*)nullptr, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks,
                         qkv_bias, B, sc, counters, npad));

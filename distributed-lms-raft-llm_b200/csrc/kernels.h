@@ -60,7 +60,8 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
 // k_attn_decode_scratch_bytes(B,H) bytes laid out for B rows, zero-initialised once by the owner
 int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias, void* k, void* v, int kv_dtype,
                         void* out, int out_dtype, int B, int H, int Smax, const int* len_dev, int len_host,
-                        int nsplit, void* split_scratch, const int* npad, int safe_rows, cudaStream_t st);
+                        int nsplit, void* split_scratch, const int* npad, int safe_rows, int len_hint,
+                        cudaStream_t st);
 int k_attn_decode_splits(int B, int H, int len_hint, int num_sms);
 size_t k_attn_decode_scratch_bytes(int B, int H);
 

@@ -3,6 +3,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -I distributed-lms-raft-llm_b200/csrc \
 //        tools/microbench.cu -o gpurun_out/microbench -L distributed-lms-raft-llm_b200 -ltutor_b200
 #include <cstdio>
+#include <cstdlib>
 #include <functional>
 #include <vector>
 
@@ -129,11 +130,20 @@ int main() {
       ATT("ring chunk 64 x 2 stages, no math", (attn_decode_tma_kernel<false, 64, 2, false><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
       ATT("ring chunk 32 x 4 stages", (attn_decode_tma_kernel<false, 32, 4, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
       ATT("ring chunk 32 x 4 stages, no math", (attn_decode_tma_kernel<false, 32, 4, false><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
+      {  // tensor-core consumers: the cache of every "layer" as a [768*768, 64] bf16 matrix behind a tensor map
+        static CUtensorMap tk[12], tv[12];
+        for (int i = 0; i < 12; ++i) {
+          if (k_make_map_bf16(&tk[i], kp(i), 768 * 768, 64, DM_CHUNK) || k_make_map_bf16(&tv[i], vp(i), 768 * 768, 64, DM_CHUNK)) exit(3);
+        }
+        ATT("mma ring chunk 32 x 4 stages", (attn_decode_mma_kernel<false, true><<<dim3(12, 64), DM_THREADS, 0, st>>>(tk[i % 12], tv[i % 12], qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
+        ATT("mma ring chunk 32 x 4 stages, no math", (attn_decode_mma_kernel<false, false><<<dim3(12, 64), DM_THREADS, 0, st>>>(tk[i % 12], tv[i % 12], qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
+      }
       ATT("ring chunk 16 x 8 stages", (attn_decode_tma_kernel<false, 16, 8, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
     }
 #endif
     cudaFree(big); cudaFree(sink);
   }
+  if (getenv("MB_ATTN_ONLY")) return 0;
   for (int pdl = 0; pdl < 2; ++pdl) {
     printf("--- PDL %s\n", pdl ? "on" : "off");
     float t = time_graph(st, 96, pdl, [&](int) { CK(tutor_launch(k_empty, dim3(64), dim3(128), 0, st, cnt)); });
