@@ -30,6 +30,7 @@ enum { EPI_ROWMAJOR = 0, EPI_SWAPPED = 1, EPI_ARGMAX = 2, EPI_PARTIAL = 3 };
 
 // Phase timestamps of CTA (0,0,0) for tools/microbench.cu (compiled in only with -DTUTOR_TRACE)
 #ifdef TUTOR_TRACE
+__device__ int g_epi_skip;  // tools/microbench_gemm.cu: 1 = persistent epilogue only hands the accumulator back
 __device__ long long g_gemm_trace[8];
 #define TRACE(i)                                                              \
   do {                                                                        \
@@ -428,17 +429,301 @@ __global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_kernel(
       const int row = a_row0 + quad * 32 + lane;
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quad * 32) << 16);
       const int c_begin = half * SLICE, c_end = c_begin + SLICE;
+#ifdef TUTOR_TRACE
+      if (g_epi_skip == 1) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        continue;
+      }
+#endif
       for (int c0 = c_begin; c0 < c_end; c0 += 32) {
         float v[32];
+#ifdef TUTOR_TRACE
+        if (g_epi_skip == 3) {  // no TMEM read: the stores see zeros
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = 0.f;
+        } else
+#endif
         tc_ld32(taddr + c0, v);
         if (c0 + 32 >= c_end) {  // last read of this accumulator by this warp: hand it back before the stores
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
         }
+#ifdef TUTOR_TRACE
+        if (g_epi_skip == 4) {  // TMEM read only: no epilogue math, no global traffic
+          float acc = 0.f;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) acc += v[i];
+          if (acc == 123.456f) epi.out_f32[0] = acc;
+          continue;
+        }
+#endif
         if (row < M && b_row0 + c0 < N) store_run32(epi, row, b_row0 + c0, N, v);
       }
     }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+  }
+}
+
+// ---------------------------------------------------- persistent row-major GEMM, TMA-staged epilogue
+// Same mainloop as gemm_bf16_persistent_kernel.  Measured on B200 (tools/microbench_gemm.cu, BERT-base layer shapes at
+// 16384 tokens): the mainloop alone runs at 1.3-1.7 PFLOP/s, while the epilogue above - every lane owning one output
+// row, bias fetched from global inside the loop, 32 scattered sectors per store instruction - held the kernels at
+// 290-760 TFLOP/s (stalls: long scoreboard + LSU queue throttle).  Here each epilogue warp owns a 32-row x 64-column
+// piece of the tile and a private 4 KB staging buffer: bias comes from shared memory, the fp32 residual arrives by a
+// TMA tile load into that buffer, results are written back in place in the 128-byte-swizzled layout (conflict-free
+// for row-per-lane 16-byte accesses) and leave through one TMA tile store per 32 x 128-byte piece - full lines,
+// asynchronous, no LSU traffic.  Warps never synchronise with each other.
+struct TmaEpilogue {
+  const float* bias;  // [N] or null
+  int act;
+  int has_res;        // residual tile (fp32) is read through tmRes
+  int out_f32;        // 1: fp32 output in 32-column pieces, 0: bf16 output in 64-column pieces
+  // QKV scatter (qkv != 0, bf16): columns [0,d) -> q [M,d] through tmOut; [d,2d) / [2d,3d) -> the K / V cache,
+  // addressed as a [(B*H*Smax), 64] matrix through tmRes / tmV: a piece is one head's 64 dims of 32 consecutive tokens
+  // of one sequence (T % 32 == 0), i.e. 32 consecutive cache rows
+  int qkv, d, H, T, Smax, pos0;
+};
+
+template <int BN> struct PersistTmaLayout {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int EPI_BYTES = PERSIST_EPI_WARPS * 4096;  // one swizzled 32 x 128 B buffer per epilogue warp
+  static constexpr int BIAS_BYTES = PERSIST_EPI_WARPS * 256;  // 64 floats per epilogue warp
+  static constexpr int STAGES = (226 * 1024 - EPI_BYTES - BIAS_BYTES - 512 - 1024) / STAGE_BYTES;  // 3 at BN=256
+  static constexpr int TILE_BYTES = STAGES * STAGE_BYTES;
+  static constexpr int TOTAL = TILE_BYTES + EPI_BYTES + BIAS_BYTES + 512 + 1024;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_tma_kernel(
+    const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+    const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes,
+    const __grid_constant__ CUtensorMap tmV, int M, int N, int K, TmaEpilogue epi) {
+  using L = PersistTmaLayout<BN>;
+  static_assert(BN == 256, "16 epilogue warps x 64 columns");
+  constexpr int TMEM_COLS = 2 * BN;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* stage_all = tiles + L::TILE_BYTES;  // 1 KB aligned: TILE_BYTES is a multiple of 1024
+  float* bias_all = reinterpret_cast<float*>(stage_all + L::EPI_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_all + L::EPI_BYTES + L::BIAS_BYTES);
+  uint64_t* empty_bar = full_bar + L::STAGES;
+  uint64_t* tmem_full_bar = empty_bar + L::STAGES;  // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;     // [2]
+  uint64_t* res_bar = tmem_empty_bar + 2;           // [PERSIST_EPI_WARPS]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + PERSIST_EPI_WARPS);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nk = K / BK;
+  const int m_tiles = (M + BM - 1) / BM, n_tiles = (N + BN - 1) / BN;
+  const int ntiles = m_tiles * n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmOut) : "memory");
+    for (int s = 0; s < L::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], PERSIST_EPI_WARPS); }
+    for (int w = 0; w < PERSIST_EPI_WARPS; ++w) mbar_init(&res_bar[w], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const int a_row0 = (t % m_tiles) * BM, b_row0 = (t / m_tiles) * BN;
+        for (int kb = 0; kb < nk; ++kb, ++it) {
+          const int s = it % L::STAGES;
+          mbar_wait(&empty_bar[s], ((it / L::STAGES) & 1) ^ 1, 0);
+          mbar_expect_tx(&full_bar[s], L::STAGE_BYTES);
+          uint8_t* sa = tiles + s * L::STAGE_BYTES;
+          tma_load_2d(sa, &tmA, &full_bar[s], kb * BK, a_row0);
+          tma_load_2d(sa + L::A_BYTES, &tmB, &full_bar[s], kb * BK, b_row0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+      uint32_t it = 0, ti = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++ti) {
+        const uint32_t acc = ti & 1;
+        mbar_wait(&tmem_empty_bar[acc], ((ti >> 1) & 1) ^ 1, 3);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < nk; ++kb, ++it) {
+          const int s = it % L::STAGES;
+          mbar_wait(&full_bar[s], (it / L::STAGES) & 1, 1);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(tiles + s * L::STAGE_BYTES);
+          const uint32_t sb = sa + L::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            tc_mma_bf16(d_tmem, umma_desc_sw128(sa + k * UMMA_K * 2), umma_desc_sw128(sb + k * UMMA_K * 2), idesc,
+                        (kb | k) != 0);
+          tc_commit(&empty_bar[s]);
+        }
+        tc_commit(&tmem_full_bar[acc]);
+      }
+    }
+  } else {
+    // ===== epilogue: warp w owns TMEM lanes of quadrant w % 4 (32 output rows) and columns [64 q, 64 q + 64) =====
+    const int ew = warp - 2, quad = warp & 3, cslice = ew >> 2;
+    const uint32_t stage = smem_u32(stage_all + ew * 4096);
+    float* sbias = bias_all + ew * 64;
+    uint64_t* rbar = &res_bar[ew];
+    uint32_t ti = 0, res_uses = 0;
+    const uint32_t swz = (uint32_t)(lane & 7);
+    const uint32_t my_row = stage + lane * 128;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++ti) {
+      const int a_row0 = (t % m_tiles) * BM, b_row0 = (t / m_tiles) * BN;
+      const uint32_t acc = ti & 1;
+      const int row0 = a_row0 + quad * 32, col0 = b_row0 + cslice * 64;
+      const bool live = row0 < M && col0 < N;  // warp-uniform; a dead piece only hands the accumulator back
+      if (live) {
+        // ahead of the accumulator: bias of these 64 columns into shared memory, first residual piece on its way
+        if (lane < 16) {
+          const int n = col0 + lane * 4;
+          float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (epi.bias && n < N) b4 = *reinterpret_cast<const float4*>(epi.bias + n);  // N % 4 == 0
+          *reinterpret_cast<float4*>(sbias + lane * 4) = b4;
+        }
+        if (epi.has_res && lane == 0) {
+          tma_store_wait_read();  // the previous tile's store has left the buffer
+          mbar_expect_tx(rbar, 4096);
+          tma_load_2d(reinterpret_cast<void*>(stage_all + ew * 4096), &tmRes, rbar, col0, row0);
+        }
+        __syncwarp();
+      }
+      mbar_wait(&tmem_full_bar[acc], (ti >> 1) & 1, 2);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quad * 32) << 16) + cslice * 64;
+#ifdef TUTOR_TRACE
+      if (g_epi_skip == 1) {  // tools/microbench_gemm.cu: mainloop only
+        if (epi.has_res) { mbar_wait(rbar, res_uses & 1, 5); ++res_uses; }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        continue;
+      }
+#endif
+      if (!live) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        continue;
+      }
+      if (epi.out_f32) {
+        // two pieces of 32 fp32 columns (128-byte rows)
+#pragma unroll 1
+        for (int sub = 0; sub < 2; ++sub) {
+          float v[32];
+          tc_ld32(taddr + sub * 32, v);
+          if (sub == 1) {  // last read of this accumulator by this warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+          }
+          const int c0 = col0 + sub * 32;
+          if (c0 >= N) continue;  // (the TMA store would clip it anyway)
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = apply_act_fast(v[i] + sbias[sub * 32 + i], epi.act);
+          if (epi.has_res) {
+            mbar_wait(rbar, res_uses & 1, 5);
+            ++res_uses;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              float4 r;
+              asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                           : "r"(my_row + (((uint32_t)c ^ swz) << 4)));
+              v[4 * c] += r.x; v[4 * c + 1] += r.y; v[4 * c + 2] += r.z; v[4 * c + 3] += r.w;
+            }
+          } else {
+            if (lane == 0) tma_store_wait_read();  // the buffer's previous contents have left
+            __syncwarp();
+          }
+#pragma unroll
+          for (int c = 0; c < 8; ++c)
+            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(my_row + (((uint32_t)c ^ swz) << 4)), "f"(v[4 * c]),
+                         "f"(v[4 * c + 1]), "f"(v[4 * c + 2]), "f"(v[4 * c + 3])
+                         : "memory");
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmOut, stage, c0, row0);
+            if (epi.has_res && sub == 0 && c0 + 32 < N) {  // second residual piece into the same buffer
+              tma_store_wait_read();
+              mbar_expect_tx(rbar, 4096);
+              tma_load_2d(reinterpret_cast<void*>(stage_all + ew * 4096), &tmRes, rbar, c0 + 32, row0);
+            }
+          }
+          __syncwarp();
+        }
+      } else {
+        // one piece of 64 bf16 columns (128-byte rows)
+        float v[64];
+        tc_ld32(taddr, v);
+        tc_ld32(taddr + 32, v + 32);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(&tmem_empty_bar[acc]);
+          tma_store_wait_read();  // the buffer's previous contents have left
+        }
+        __syncwarp();
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          uint32_t w[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int i = 8 * c + 2 * j;
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(apply_act_fast(v[i] + sbias[i], epi.act),
+                                                     apply_act_fast(v[i + 1] + sbias[i + 1], epi.act));
+            w[j] = *reinterpret_cast<uint32_t*>(&h2);
+          }
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(my_row + (((uint32_t)c ^ swz) << 4)), "r"(w[0]),
+                       "r"(w[1]), "r"(w[2]), "r"(w[3])
+                       : "memory");
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+          if (!epi.qkv || col0 < epi.d) {
+            tma_store_2d(&tmOut, stage, col0, row0);
+          } else {  // this head's rows of the K or V cache (replaces DynamicLayer.update's torch.cat)
+            const int which = col0 >= 2 * epi.d, c = col0 - (which ? 2 * epi.d : epi.d);
+            const int b = row0 / epi.T, t0 = row0 - b * epi.T;
+            const int crow = (b * epi.H + (c >> 6)) * epi.Smax + epi.pos0 + t0;
+            tma_store_2d(which ? &tmV : &tmRes, stage, 0, crow);
+          }
+        }
+        __syncwarp();
+      }
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // stores complete before the CTA exits
   }
 
   tc_fence_before();
@@ -506,6 +791,25 @@ int make_map_out(CUtensorMap* map, float* ptr, int N, int M, int ks, int box_m) 
   return TUTOR_OK;
 }
 
+// [rows, cols] row-major tensor of fp32 or bf16 cut into 32-row x 128-byte boxes (the epilogue warps' staging tiles)
+int make_map_epi(CUtensorMap* map, const void* ptr, bool f32, int rows, int cols) {
+  TRY(get_encoder());
+  const size_t es = f32 ? 4 : 2;
+  ARG_CHECK((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (cols * es) % 16 == 0, "gemm_bf16: output not 16-byte aligned");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * es};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / es), 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                        const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    tutor_set_error("cuTensorMapEncodeTiled (epilogue) failed (%d) rows=%d cols=%d", (int)r, rows, cols);
+    return TUTOR_ERR_CUDA;
+  }
+  return TUTOR_OK;
+}
+
 template <int BN, int EPI>
 int launch(const bf16* A, int rowsA, const bf16* B, int rowsB, int K, const GemmEpilogue& epi, const ArgmaxArgs& am,
            cudaStream_t st, int ks = 1) {
@@ -541,6 +845,53 @@ int launch_persistent(const bf16* A, int M, const bf16* W, int N, int K, const G
   return TUTOR_OK;
 }
 
+// the TMA-staged epilogue covers plain row-major outputs: bias -> activation -> (+ fp32 residual) -> fp32 or bf16
+bool tma_epilogue_ok(const GemmEpilogue& e, int M, int N) {
+  if (e.qkv_mode) {  // q [M,d] + scatter into the K / V cache: whole 32-token pieces of one sequence, bf16 everywhere
+    return e.out_bf16 && !e.out_f32 && !e.residual && !e.pos_dev && e.kv_dtype == DT_BF16 && e.T % 32 == 0 &&
+           e.d % 64 == 0 && N == 3 * e.d && e.ldo == e.d && M % e.T == 0 && e.Smax >= e.pos0 + e.T &&
+           !((reinterpret_cast<uintptr_t>(e.out_bf16) | reinterpret_cast<uintptr_t>(e.kcache) |
+              reinterpret_cast<uintptr_t>(e.vcache) | reinterpret_cast<uintptr_t>(e.bias)) & 15);
+  }
+  if (e.ldo != N) return false;
+  if ((e.out_f32 != nullptr) == (e.out_bf16 != nullptr)) return false;  // exactly one output
+  if (e.residual && !e.out_f32) return false;
+  const void* out = e.out_f32 ? (const void*)e.out_f32 : (const void*)e.out_bf16;
+  if ((reinterpret_cast<uintptr_t>(out) & 15) || (e.residual && (reinterpret_cast<uintptr_t>(e.residual) & 15))) return false;
+  if (e.bias && (reinterpret_cast<uintptr_t>(e.bias) & 15)) return false;
+  return N % 8 == 0;
+}
+
+int launch_persistent_tma(const bf16* A, int M, const bf16* W, int N, int K, const GemmEpilogue& e, cudaStream_t st) {
+  using L = PersistTmaLayout<256>;
+  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(gemm_bf16_persistent_tma_kernel<256>), L::TOTAL));
+  CUtensorMap ta, tb, to, tr, tv;
+  TRY(make_map(&ta, A, M, K, BM));
+  TRY(make_map(&tb, W, N, K, 256));
+  const bool f32 = e.out_f32 != nullptr;
+  TmaEpilogue te{e.bias, e.act, e.residual != nullptr, f32 ? 1 : 0, 0, 0, 0, 0, 0, 0};
+  if (e.qkv_mode) {
+    const int cache_rows = (M / e.T) * e.H * e.Smax;
+    TRY(make_map_epi(&to, e.out_bf16, false, M, e.d));
+    TRY(make_map_epi(&tr, e.kcache, false, cache_rows, 64));
+    TRY(make_map_epi(&tv, e.vcache, false, cache_rows, 64));
+    te.qkv = 1; te.d = e.d; te.H = e.H; te.T = e.T; te.Smax = e.Smax; te.pos0 = e.pos0;
+  } else {
+    TRY(make_map_epi(&to, f32 ? (const void*)e.out_f32 : (const void*)e.out_bf16, f32, M, N));
+    if (e.residual) TRY(make_map_epi(&tr, e.residual, true, M, N));
+    else tr = to;  // unused
+    tv = to;       // unused
+  }
+  int dev = 0, sms = 148;
+  CUDA_TRY(cudaGetDevice(&dev));
+  CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int ntiles = ceil_div(M, BM) * ceil_div(N, 256);
+  CUDA_TRY(tutor_launch(gemm_bf16_persistent_tma_kernel<256>, dim3(ntiles < sms ? ntiles : sms), dim3(NTHREADS_PERSIST),
+                        (size_t)L::TOTAL, st, ta, tb, to, tr, tv, M, N, K, te));
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+
 template <int EPI>
 int launch_swapped(const bf16* W, int N, const bf16* X, int M, int K, const GemmEpilogue& epi, const ArgmaxArgs& am,
                    cudaStream_t st, int ks = 1) {
@@ -570,6 +921,8 @@ int k_gemm_bf16(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpi
   // bound: 32 KB of operands per 4 MMAs = 6.2 TB/s at 410 TFLOP/s); two 97 KB CTAs still share an SM
   static const bool wide = getenv("TUTOR_GEMM_BN128") == nullptr;
   static const bool persistent = getenv("TUTOR_GEMM_NONPERSISTENT") == nullptr;  // debugging aid / A-B measurements
+  static const bool tma_epi = getenv("TUTOR_GEMM_NO_TMA_EPILOGUE") == nullptr;  // A/B measurements
+  if (persistent && tma_epi && N >= 128 && tma_epilogue_ok(epi, M, N)) return launch_persistent_tma(A, M, W, N, K, epi, st);
   if (persistent) {
     if (wide && N >= 256) return launch_persistent<256>(A, M, W, N, K, epi, st);
     return launch_persistent<128>(A, M, W, N, K, epi, st);
