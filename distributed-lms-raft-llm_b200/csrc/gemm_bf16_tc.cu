@@ -908,6 +908,28 @@ int launch_swapped(const bf16* W, int N, const bf16* X, int M, int K, const Gemm
 int k_make_map_bf16(void* map, const bf16* ptr, int rows, int K, int box_rows) {
   return make_map(reinterpret_cast<CUtensorMap*>(map), ptr, rows, K, box_rows);
 }
+// generic row-major 2-D tensor [rows, cols] of 4-byte (fp32) or 2-byte (bf16) elements, boxes of box_rows x box_cols
+// (box_cols * element size must be 128 bytes: one swizzle atom per box row)
+int k_make_map_2d(void* map, const void* ptr, int elem_bytes, int rows, int cols, int box_rows, int box_cols) {
+  TRY(get_encoder());
+  ARG_CHECK((elem_bytes == 4 || elem_bytes == 2) && box_cols * elem_bytes == 128 && box_rows >= 1 && box_rows <= 256,
+            "make_map_2d: unsupported box %d x %d of %d-byte elements", box_rows, box_cols, elem_bytes);
+  ARG_CHECK((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && ((size_t)cols * elem_bytes) % 16 == 0,
+            "make_map_2d: tensor not 16-byte aligned");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * elem_bytes};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(reinterpret_cast<CUtensorMap*>(map),
+                        elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                        const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    tutor_set_error("cuTensorMapEncodeTiled failed (%d) rows=%d cols=%d box=%dx%d", (int)r, rows, cols, box_rows, box_cols);
+    return TUTOR_ERR_CUDA;
+  }
+  return TUTOR_OK;
+}
 int k_make_map_partial(void* map, float* ptr, int N, int M, int ks, int box_m) {
   return make_map_out(reinterpret_cast<CUtensorMap*>(map), ptr, N, M, ks, box_m);
 }

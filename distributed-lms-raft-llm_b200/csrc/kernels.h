@@ -28,6 +28,7 @@ int k_gemm_bf16_splitk(const bf16* X, const bf16* W, int M, int N, int K, int ks
 int k_pick_splitk(int N, int K, int num_sms);
 int k_make_map_bf16(void* tensor_map, const bf16* ptr, int rows, int K, int box_rows);
 int k_make_map_partial(void* tensor_map, float* ptr, int N, int M, int ks, int box_m);
+int k_make_map_2d(void* tensor_map, const void* ptr, int elem_bytes, int rows, int cols, int box_rows, int box_cols);
 
 // ---- gemm_decode_fused.cu : decode-step linears with LayerNorm folded into the operand load and the split-K
 // reduction done across a thread-block cluster (DSMEM) with bias + gelu / bias + residual fused behind it.
@@ -96,6 +97,12 @@ int k_lmhead_argmax_ln(const void* x, int x_dtype, const void* wte, int w_dtype,
 // debug / parity: materialise logits [B,V] fp32
 int k_lmhead_logits(const void* xn, int x_dtype, const void* wte, int w_dtype, int B, int V, int Vpad, int d,
                     float* logits, cudaStream_t st);
+
+// ---- relevance_tc.cu : the corpus scan on the tensor cores (3xTF32, fp32-equivalent accuracy); scratch holds the
+// split queries.  scores[q][n] = cos(query q, corpus row n), the same contract as the SIMT scan in relevance.cu
+size_t k_cosine_scan_tc_scratch_bytes(int d);
+int k_cosine_scan_tc(const float* queries, const float* corpus, const float* corpus_inv_norm, int Q, int N, int d,
+                     float eps, float* scores, void* scratch, cudaStream_t st);
 
 // ---- relevance.cu : corpus scan
 size_t k_cosine_topk_scratch_bytes(int Q, int N, int k);

@@ -9,6 +9,8 @@
 // Ties always resolve to the lower corpus index, like torch.topk on the CPU oracle for distinct scores.
 #include <math_constants.h>
 
+#include <cstdlib>
+
 #include "kernels.h"
 
 namespace {
@@ -261,8 +263,8 @@ __global__ void __launch_bounds__(256) topk_merge_kernel(const float* __restrict
 
 size_t k_cosine_topk_scratch_bytes(int Q, int N, int k) {
   size_t nchunks = (size_t)ceil_div(N, CHUNK);
-  return round_up((size_t)Q * N * sizeof(float), 256) + round_up((size_t)Q * nchunks * k * sizeof(float), 256) +
-         round_up((size_t)Q * nchunks * k * sizeof(int32_t), 256);
+  return k_cosine_scan_tc_scratch_bytes(768) + round_up((size_t)Q * N * sizeof(float), 256) +
+         round_up((size_t)Q * nchunks * k * sizeof(float), 256) + round_up((size_t)Q * nchunks * k * sizeof(int32_t), 256);
 }
 
 int k_row_inv_norm(const void* corpus, int corpus_dtype, float* inv_norm, int N, int d, float eps, cudaStream_t st) {
@@ -301,7 +303,16 @@ int k_cosine_topk(const float* queries, const void* corpus, int corpus_dtype, co
   float* cand_v = reinterpret_cast<float*>(p);
   p += round_up((size_t)Q * nchunks * k * sizeof(float), 256);
   int32_t* cand_i = reinterpret_cast<int32_t*>(p);
+  p += round_up((size_t)Q * nchunks * k * sizeof(int32_t), 256);
+  void* tc_scratch = p;
   const float eps = 1e-8f;
+  static const bool use_tc = getenv("TUTOR_SCAN_SIMT") == nullptr;  // A/B: the fp32 FFMA2 scan below
+  if (use_tc && Q <= 32 && d % 32 == 0 && d <= 768) {
+    TRY(k_cosine_scan_tc(queries, (const float*)corpus, corpus_inv_norm, Q, N, d, eps, scores, tc_scratch, st));
+    topk_chunk_kernel<<<dim3(nchunks, Q), 256, 0, st>>>(scores, N, k, cand_v, cand_i, idx_base);
+    KERNEL_LAUNCHED();
+    return k_topk_merge(cand_v, cand_i, Q, nchunks * k, k, out_scores, out_idx, st);
+  }
   const int grid = 148;
   const size_t smem2 = ((size_t)SC_QMAX * d + SC_QMAX + (size_t)8 * SC_STAGES * SC_ROWS * SC_LD) * sizeof(float);
   if (Q <= SC_QMAX && d % SC_K == 0 && smem2 <= 220 * 1024) {

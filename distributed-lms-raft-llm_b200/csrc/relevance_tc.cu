@@ -1,0 +1,260 @@
+// Corpus cosine scan on the 5th-generation tensor cores (configs[4]; extends the single comparison at
+// REF/lms_server.py:1266 to a corpus of chunk embeddings).  scores[q][n] = <query q, corpus row n> / (|q| |row n|).
+//
+// The fp32 SIMT scan (relevance.cu) is bound by the FMA pipes (24.6 G FMA per 1M x 768 x 32 search), 2.4x above the
+// time the 3.07 GB corpus needs to stream from HBM.  The index sets are gated bit-for-bit against a CPU fp32 oracle, so
+// plain TF32 (10-bit mantissas) is not an option; this kernel uses the error-compensated "3xTF32" product instead:
+//     x = x_hi + x_lo,  x_hi = x with the low 13 mantissa bits cleared (exactly a TF32 number), x_lo = x - x_hi (exact)
+//     <c, q> ~= c_hi.q_hi + c_lo.q_hi + c_hi.q_lo          (the dropped c_lo.q_lo term is ~2^-22 relative)
+// The tensor core accumulates by truncation: a chain of n accumulations loses up to n * 2^-23 of the running sum, all in
+// one direction (measured: 1.5e-5 relative after the 288 MMAs of a 768-dim row in one accumulator).  So the main term
+// c_hi.q_hi and the two small cross terms go to separate TMEM accumulators, and the accumulators are drained every
+// 6 k-blocks (192 dims, 24 MMAs on the main one) into fp32 registers that the epilogue warps add with round-to-nearest:
+// the result is within ~1e-6 of the exact cosine, like an fp32 FMA chain.
+//
+// One persistent CTA per SM walks 128-row corpus tiles:
+//   warp 0      TMA producer: per 32-dim k-block the fp32 corpus tile [128 x 32] and the pre-split query blocks
+//               q_hi / q_lo [32 x 32] (L2-resident) into a 5-stage ring, 128-byte swizzle
+//   warps 2-5   splitters: write c_lo beside the corpus tile (elementwise, so the swizzled layout is preserved; the MMA
+//               itself ignores the low mantissa bits of the raw tile, i.e. reads it as c_hi), then hand the stage over
+//   warp 1      one thread issues 2 x 4 tcgen05.mma kind::tf32 per k-block (K=8 each): c x [q_hi; q_lo] (N=64) and
+//               c_lo x q_hi (N=32), into one of two TMEM accumulator sets
+//   warps 6-9   epilogue: tcgen05.ld, scale by the inverse norms, coalesced stores (32 consecutive rows per query)
+#include <cuda.h>
+
+#include "kernels.h"
+#include "tc_ptx.cuh"
+
+using namespace tcptx;
+
+namespace {
+
+constexpr int TS_BM = 128, TS_BK = 32, TS_NQ = 32, TS_STAGES = 5, TS_SEG = 6;  // k-blocks per accumulator segment
+// kind::tf32 reads fp32 words from shared memory and ignores their low 13 mantissa bits, i.e. it sees exactly c_hi when
+// given the raw corpus tile (verified by the fp64 accuracy test: a rounding conversion would show as ~1e-4 errors);
+// set to true to store c_hi explicitly (costs 16 KB of shared-memory writes per k-block)
+constexpr bool TS_WRITE_HI = false;
+constexpr int TS_A_BYTES = TS_BM * TS_BK * 4;   // 16 KB
+constexpr int TS_Q_BYTES = TS_NQ * TS_BK * 4;   // 4 KB
+constexpr int TS_STAGE_BYTES = 2 * TS_A_BYTES + 2 * TS_Q_BYTES;  // c_hi, c_lo, q_hi, q_lo
+constexpr int TS_THREADS = 320;
+constexpr int TS_SMEM = TS_STAGES * TS_STAGE_BYTES + 256 + 1024;
+
+// UMMA instruction descriptor, kind::tf32: D = f32 (bits 4-5 = 1), A = B = TF32 (format 2 in bits 7-9 and 10-12),
+// both K-major, N >> 3 in [17,23), M >> 4 in [24,29)
+constexpr uint32_t ts_idesc(int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TS_BM >> 4) << 24);
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// queries [Q, D] -> q_hi, q_lo [32, D] (rows >= Q zero) and 1 / max(|q|, eps); one block per query row
+__global__ void __launch_bounds__(256) split_queries_kernel(const float* __restrict__ queries, int Q, int D, float eps,
+                                                           float* __restrict__ q_hi, float* __restrict__ q_lo,
+                                                           float* __restrict__ qinv) {
+  __shared__ float red[8];
+  const int q = blockIdx.x;
+  float s = 0.f;
+  for (int i = threadIdx.x; i < D; i += blockDim.x) {
+    const float x = q < Q ? queries[(size_t)q * D + i] : 0.f;
+    const float hi = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+    q_hi[(size_t)q * D + i] = hi;
+    q_lo[(size_t)q * D + i] = __uint_as_float(__float_as_uint(x - hi) & 0xffffe000u);
+    s += x * x;
+  }
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < 8; ++w) t += red[w];
+    qinv[q] = 1.0f / fmaxf(sqrtf(t), eps);
+  }
+}
+
+__global__ void __launch_bounds__(TS_THREADS) cosine_scan_tf32x3_kernel(const __grid_constant__ CUtensorMap tmC,
+                                                                      const __grid_constant__ CUtensorMap tmQh,
+                                                                      const __grid_constant__ CUtensorMap tmQl,
+                                                                      const float* __restrict__ inv_norm,
+                                                                      const float* __restrict__ qinv, int Q, int N, int D,
+                                                                      float* __restrict__ scores) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + TS_STAGES * TS_STAGE_BYTES);
+  uint64_t* split_bar = full_bar + TS_STAGES;
+  uint64_t* empty_bar = split_bar + TS_STAGES;
+  uint64_t* tmem_full_bar = empty_bar + TS_STAGES;  // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;     // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nk = D / TS_BK;
+  const int ntiles = (N + TS_BM - 1) / TS_BM;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmC) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmQh) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmQl) : "memory");
+    for (int s = 0; s < TS_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&split_bar[s], 4); mbar_init(&empty_bar[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        for (int kb = 0; kb < nk; ++kb, ++it) {
+          const int s = it % TS_STAGES;
+          mbar_wait(&empty_bar[s], ((it / TS_STAGES) & 1) ^ 1, 0);
+          mbar_expect_tx(&full_bar[s], TS_A_BYTES + 2 * TS_Q_BYTES);
+          uint8_t* st = tiles + s * TS_STAGE_BYTES;
+          tma_load_2d(st, &tmC, &full_bar[s], kb * TS_BK, t * TS_BM);  // rows past N are zero-filled
+          tma_load_2d(st + 2 * TS_A_BYTES, &tmQh, &full_bar[s], kb * TS_BK, 0);
+          tma_load_2d(st + 2 * TS_A_BYTES + TS_Q_BYTES, &tmQl, &full_bar[s], kb * TS_BK, 0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc64 = ts_idesc(2 * TS_NQ), idesc32 = ts_idesc(TS_NQ);
+      uint32_t it = 0, si = 0;  // k-block and segment counters over the whole kernel
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        for (int kb0 = 0; kb0 < nk; kb0 += TS_SEG, ++si) {
+          // two accumulator sets of 96 columns: [c_hi.q_hi | c_hi.q_lo] from one N=64 MMA (the query tile is q_hi
+          // stacked on q_lo, so the corpus tile is read from shared memory once for both) and [c_lo.q_hi]
+          const uint32_t buf = si & 1;
+          mbar_wait(&tmem_empty_bar[buf], ((si >> 1) & 1) ^ 1, 3);
+          tc_fence_after();
+          const uint32_t d_main = tmem_base + buf * 128, d_cross = d_main + 2 * TS_NQ;
+          const int kb1 = kb0 + TS_SEG < nk ? kb0 + TS_SEG : nk;
+          for (int kb = kb0; kb < kb1; ++kb, ++it) {
+            const int s = it % TS_STAGES;
+            mbar_wait(&full_bar[s], (it / TS_STAGES) & 1, 1);   // the query blocks (TMA) have landed
+            mbar_wait(&split_bar[s], (it / TS_STAGES) & 1, 1);  // c_hi / c_lo have been written
+            tc_fence_after();
+            const uint32_t c_hi = smem_u32(tiles + s * TS_STAGE_BYTES);
+            const uint32_t c_lo = c_hi + TS_A_BYTES, q_hi = c_hi + 2 * TS_A_BYTES;  // q_lo follows q_hi: one 64-row tile
+#pragma unroll
+            for (int k = 0; k < TS_BK / 8; ++k) {  // 8 TF32 = 32 bytes along K per MMA, inside the 128-byte swizzle atom
+              const uint32_t first = (kb != kb0 || k != 0);
+              tc_mma_tf32(d_main, umma_desc_sw128(c_hi + k * 32), umma_desc_sw128(q_hi + k * 32), idesc64, first);
+              tc_mma_tf32(d_cross, umma_desc_sw128(c_lo + k * 32), umma_desc_sw128(q_hi + k * 32), idesc32, first);
+            }
+            tc_commit(&empty_bar[s]);
+          }
+          tc_commit(&tmem_full_bar[buf]);
+        }
+      }
+    }
+  } else if (warp < 6) {
+    // ===== splitters: c -> c_hi (in place) and c_lo; 128 threads, consecutive 16-byte vectors =====
+    const int tid = threadIdx.x - 64;
+    uint32_t it = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+      for (int kb = 0; kb < nk; ++kb, ++it) {
+        const int s = it % TS_STAGES;
+        mbar_wait(&full_bar[s], (it / TS_STAGES) & 1, 4);
+        const uint32_t hi_base = smem_u32(tiles + s * TS_STAGE_BYTES), lo_base = hi_base + TS_A_BYTES;
+#pragma unroll
+        for (int j = 0; j < TS_A_BYTES / 16 / 128; ++j) {
+          const uint32_t off = (uint32_t)(tid + j * 128) * 16u;
+          uint32_t x[4], h[4], l[4];
+          asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(x[0]), "=r"(x[1]), "=r"(x[2]), "=r"(x[3]) : "r"(hi_base + off));
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            h[i] = x[i] & 0xffffe000u;
+            l[i] = __float_as_uint(__uint_as_float(x[i]) - __uint_as_float(h[i])) & 0xffffe000u;
+          }
+          if (TS_WRITE_HI)
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(hi_base + off), "r"(h[0]), "r"(h[1]), "r"(h[2]), "r"(h[3]) : "memory");
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(lo_base + off), "r"(l[0]), "r"(l[1]), "r"(l[2]), "r"(l[3]) : "memory");
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&split_bar[s]);
+      }
+    }
+  } else {
+    // ===== epilogue: lane = corpus row of the tile, TMEM column = query =====
+    const int quad = warp & 3;
+    uint32_t si = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+      const int row = t * TS_BM + quad * 32 + lane;
+      const float ci = row < N ? inv_norm[row] : 0.f;
+      float sum[32];
+#pragma unroll
+      for (int q = 0; q < 32; ++q) sum[q] = 0.f;
+      for (int kb0 = 0; kb0 < nk; kb0 += TS_SEG, ++si) {
+        const uint32_t buf = si & 1;
+        mbar_wait(&tmem_full_bar[buf], (si >> 1) & 1, 2);
+        tc_fence_after();
+        float vm[32], vc[32], vd[32];
+        const uint32_t taddr = tmem_base + buf * 128 + ((uint32_t)(quad * 32) << 16);
+        tc_ld32(taddr, vm);               // c_hi.q_hi
+        tc_ld32(taddr + TS_NQ, vc);       // c_hi.q_lo
+        tc_ld32(taddr + 2 * TS_NQ, vd);   // c_lo.q_hi
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
+#pragma unroll
+        for (int q = 0; q < 32; ++q) sum[q] += vm[q] + (vc[q] + vd[q]);  // round-to-nearest adds of the segment sums
+      }
+      if (row < N) {
+#pragma unroll
+        for (int q = 0; q < TS_NQ; ++q)
+          if (q < Q) scores[(size_t)q * N + row] = sum[q] * qinv[q] * ci;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256) : "memory");
+  }
+}
+
+}  // namespace
+
+size_t k_cosine_scan_tc_scratch_bytes(int d) { return round_up((size_t)2 * TS_NQ * d * sizeof(float) + TS_NQ * sizeof(float), 256); }
+
+int k_cosine_scan_tc(const float* queries, const float* corpus, const float* corpus_inv_norm, int Q, int N, int d,
+                     float eps, float* scores, void* scratch, cudaStream_t st) {
+  ARG_CHECK(Q >= 1 && Q <= TS_NQ && d % TS_BK == 0 && N >= 1, "cosine_scan_tc: unsupported Q=%d d=%d N=%d", Q, d, N);
+  float* q_hi = reinterpret_cast<float*>(scratch);
+  float* q_lo = q_hi + (size_t)TS_NQ * d;
+  float* qinv = q_lo + (size_t)TS_NQ * d;
+  split_queries_kernel<<<TS_NQ, 256, 0, st>>>(queries, Q, d, eps, q_hi, q_lo, qinv);
+  KERNEL_LAUNCHED();
+  CUtensorMap tc, th, tl;
+  TRY(k_make_map_2d(&tc, corpus, 4, N, d, TS_BM, TS_BK));
+  TRY(k_make_map_2d(&th, q_hi, 4, TS_NQ, d, TS_NQ, TS_BK));
+  TRY(k_make_map_2d(&tl, q_lo, 4, TS_NQ, d, TS_NQ, TS_BK));
+  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(cosine_scan_tf32x3_kernel), TS_SMEM));
+  int dev = 0, sms = 148;
+  CUDA_TRY(cudaGetDevice(&dev));
+  CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int ntiles = ceil_div(N, TS_BM);
+  cosine_scan_tf32x3_kernel<<<ntiles < sms ? ntiles : sms, TS_THREADS, TS_SMEM, st>>>(tc, th, tl, corpus_inv_norm, qinv, Q, N, d,
+                                                                                scores);
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}

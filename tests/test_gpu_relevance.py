@@ -62,3 +62,16 @@ def test_full_size_properties(pkg):
     assert (s[:, 0] - 1).abs().max().item() < 1e-5
     assert (s[:, :-1] >= s[:, 1:]).all()
     assert (i >= 0).all() and (i < N).all()
+
+
+def test_tensor_core_scan_is_fp32_accurate(pkg):
+    """The 3xTF32 tensor-core scan must be as accurate as an fp32 FMA chain: top-k scores against float64."""
+    N, Q, k = 30_000, 32, 10
+    c = corpus(N) * torch.rand(N, 1, generator=torch.Generator().manual_seed(4)) * 7  # un-normalised rows
+    q = torch.randn(Q, 768, generator=torch.Generator().manual_seed(5))
+    s, i = pkg.CorpusShard(c.cuda()).topk(q.cuda(), k)
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.cosine_similarity(q.double()[:, None, :], c.double()[None, :, :], dim=2)
+    rs, ri = ref.topk(k, dim=1)
+    assert torch.equal(i.cpu().long(), ri)
+    assert (s.cpu().double() - rs).abs().max().item() < 2e-6
