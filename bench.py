@@ -351,6 +351,30 @@ def extras(pkg, rp, torch, hf_small, tc_peak, hbm_peak):
     res["cfg4_corpus_1M_x768_fp32_32q_top10"] = {"us_per_search": us, "queries_per_s": 32 / (us * 1e-6), "achieved_gbs": gbs,
                                                   "frac_of_hbm_peak": gbs / hbm_peak, "timing": "CUDA events"}
     del corpus, shard
+    # configs[3]: GPT-2 large bf16, B=16 - (ii) prefill-only over the full 1024-token context (one forward, first token
+    # only; 24.74 TFLOP) and (i) 896-token prompt -> +128 tokens end to end (1024 total: wpe has 1024 rows)
+    torch.cuda.empty_cache()
+    large = pkg.B200GPT2LMHeadModel.from_hf(rp.build_gpt2("large", seed=0), dtype="bf16")
+    ids_full, ids_896 = rp.gpt2_prompt_ids(16, 1024, seed=1).cuda(), rp.gpt2_prompt_ids(16, 896, seed=1)
+    for _ in range(2):
+        large.generate(ids_full, max_new_tokens=1, do_sample=False)
+    torch.cuda.synchronize()
+    n = 3
+    t0 = time.perf_counter()
+    for _ in range(n):
+        large.generate(ids_full, max_new_tokens=1, do_sample=False)
+    dt_pre = (time.perf_counter() - t0) / n
+    large.generate(ids_896, max_new_tokens=128, do_sample=False)
+    t0 = time.perf_counter()
+    for _ in range(n):
+        large.generate(ids_896, max_new_tokens=128, do_sample=False)
+    dt_gen = (time.perf_counter() - t0) / n
+    res["cfg3_gpt2_large_bf16_bs16"] = {"prefill_1024_ms": dt_pre * 1e3, "prefill_tflops": 24.74 / dt_pre,
+                                        "prefill_frac_of_bf16_peak": 24.74 / dt_pre / tc_peak,
+                                        "e2e_896_plus_128_ms": dt_gen * 1e3, "e2e_new_tokens_per_s": 16 * 128 / dt_gen,
+                                        "timing": "host wall around synchronous generate() calls (ids in HBM for the "
+                                                  "prefill figure, host ids for the end-to-end one)"}
+    del large
     return res
 
 

@@ -233,3 +233,85 @@ class RelevanceGate:
         """The tail of LMSService.GetLLMAnswer (REF/lms_server.py:1266-1274): canned reply or forward to the tutor."""
         relevant, _ = self.check(query, assignment_text)
         return ask_tutor(query) if relevant else self._bert.NOT_RELATED_MESSAGE
+
+
+# ------------------------------------------------------------------------------------------------------------
+# SURVEY.md §8f rank 4: assignment ingestion -> chunk -> embed -> corpus.  The reference extracts the text of an
+# uploaded assignment (REF/lms_server.py:21-27, 911-927) but only ever looks at the first 512 tokens of the student's
+# first assignment (:1254, :98).  AssignmentIndex embeds the whole text in 512-token chunks at upload time and answers
+# relevance queries against all of them with the corpus scan (configs[4]).
+class AssignmentIndex:
+    """Chunked assignment embeddings in HBM.
+
+    A chunk is what `compute_embeddings` feeds BERT for a text that fills its 512-token window: [CLS] + up to
+    `chunk_tokens - 2` word pieces + [SEP], mean-pooled over every position (REF/lms_server.py:97-101).  Chunk 0 of a
+    text is therefore exactly the embedding the reference computes for it.  Equal-length chunks are embedded as one
+    batch; rows live in a `CorpusShard` that is rebuilt lazily after an upload."""
+
+    def __init__(self, model, tokenizer, chunk_tokens: int = 512, embed_batch: int = 32):
+        if chunk_tokens < 3:
+            raise ValueError("chunk_tokens must leave room for [CLS], one word piece and [SEP]")
+        self.model, self.tokenizer = model, tokenizer
+        self.chunk_tokens, self.embed_batch = chunk_tokens, embed_batch
+        self.meta = []       # row -> (doc_id, chunk number)
+        self._rows = []      # list of [n, hidden] CUDA tensors, in row order
+        self._shard = None
+        self._lock = threading.Lock()
+
+    def chunk_ids(self, text):
+        """Token ids of `text` without truncation, cut into [CLS] body [SEP] windows of at most chunk_tokens ids."""
+        import torch
+        enc = self.tokenizer(text, return_tensors="pt", padding=False, truncation=False)
+        ids = enc["input_ids"][0].to(torch.int64)
+        if ids.numel() < 3:
+            raise ValueError("the tokenizer must frame the text with [CLS] ... [SEP]")
+        cls, sep, body = ids[:1], ids[-1:], ids[1:-1]
+        step = self.chunk_tokens - 2
+        return [torch.cat([cls, body[i:i + step], sep]) for i in range(0, max(1, body.numel()), step)]
+
+    def ingest(self, doc_id, text) -> int:
+        """Embed every chunk of `text`; returns the number of chunks added."""
+        import torch
+        chunks = self.chunk_ids(text)
+        embs = [None] * len(chunks)
+        by_len = {}
+        for i, c in enumerate(chunks):
+            by_len.setdefault(c.numel(), []).append(i)
+        for _, idxs in by_len.items():  # equal-length chunks share a batch (no padding: the mean is unmasked)
+            for j in range(0, len(idxs), self.embed_batch):
+                part = idxs[j:j + self.embed_batch]
+                e = self.model.embed(torch.stack([chunks[i] for i in part]).cuda())
+                for row, i in enumerate(part):
+                    embs[i] = e[row]
+        rows = torch.stack(embs).float().cuda()
+        with self._lock:
+            self.meta.extend((doc_id, n) for n in range(len(chunks)))
+            self._rows.append(rows)
+            self._shard = None
+        return len(chunks)
+
+    def __len__(self):
+        return len(self.meta)
+
+    def _corpus(self):
+        import torch
+        from .relevance import CorpusShard
+        with self._lock:
+            if self._shard is None:
+                if not self._rows:
+                    raise RuntimeError("AssignmentIndex is empty")
+                self._rows = [torch.cat(self._rows)]
+                self._shard = CorpusShard(self._rows[0])
+            return self._shard
+
+    def search(self, query, k: int = 5):
+        """[(doc_id, chunk number, cosine)] of the k chunks most similar to `query`, best first."""
+        from . import bert as _bert
+        q = _bert.compute_embeddings(query, self.model, self.tokenizer)
+        scores, idx = self._corpus().topk(q.cuda(), min(k, len(self.meta)))
+        return [(*self.meta[int(i)], float(s)) for s, i in zip(scores[0].tolist(), idx[0].tolist()) if i >= 0]
+
+    def is_relevant(self, query, threshold: float = 0.6):
+        """The gate of REF/lms_server.py:1266-1269 against the best-matching chunk instead of the first 512 tokens."""
+        best = self.search(query, 1)
+        return bool(best) and not (best[0][2] < threshold), (best[0] if best else None)

@@ -193,3 +193,41 @@ def test_batching_queue_with_engine_equals_batch1(pkg):
     assert sum(bm.batches) == 6 and len(bm.batches) <= 2
     for o, s in zip(outs, solo):
         assert torch.equal(o, s)
+
+
+@pytest.mark.gpu
+def test_assignment_index_chunks_embeds_and_finds(pkg):
+    """whole-assignment ingestion.  Chunk 0 equals the reference's (truncated) embedding; a query
+    that repeats a later chunk finds that chunk with cosine ~1."""
+    import zlib
+
+    import torch
+
+    serving = __import__("importlib").import_module("distributed-lms-raft-llm_b200.serving")
+
+    class Tok:  # deterministic "word pieces": one id per word, framed by [CLS]=101 / [SEP]=102
+        def __call__(self, text, truncation=True, max_length=512, **kw):
+            body = [1000 + zlib.crc32(w.encode()) % 900 for w in text.split()]
+            if truncation:
+                body = body[:max_length - 2]
+            ids = torch.tensor([[101] + body + [102]], dtype=torch.int64)
+            return {"input_ids": ids, "token_type_ids": torch.zeros_like(ids), "attention_mask": torch.ones_like(ids)}
+
+    hf = rp.build_bert(seed=6, hidden_size=128, num_hidden_layers=2, num_attention_heads=2, intermediate_size=512,
+                       vocab_size=2000, max_position_embeddings=64)
+    bert = pkg.B200BertModel.from_hf(hf, dtype="fp32")
+    index = serving.AssignmentIndex(bert, Tok(), chunk_tokens=64)
+    words = [f"w{i}" for i in range(62 * 3 + 20)]  # 3 full chunks and a 20-word tail
+    text = " ".join(words)
+    assert index.ingest("hw1", text) == 4 and len(index) == 4
+    assert index.ingest("hw2", " ".join(f"x{i}" for i in range(30))) == 1
+    # chunk 0 is the reference's own embedding of the (truncated) text
+    ref0 = rp.compute_embeddings(text, hf, lambda t, **kw: Tok()(t, truncation=True, max_length=64))
+    got0 = index._corpus().rows[0].cpu()
+    assert (got0 - ref0[0]).abs().max().item() < 1e-4
+    # a query made of chunk 2's words scores ~1 against ("hw1", 2)
+    hits = index.search(" ".join(words[124:186]), k=3)
+    assert hits[0][:2] == ("hw1", 2) and abs(hits[0][2] - 1.0) < 1e-4
+    assert hits[0][2] > hits[1][2]
+    ok, best = index.is_relevant(" ".join(f"x{i}" for i in range(30)), threshold=0.99)
+    assert ok and best[:2] == ("hw2", 0)

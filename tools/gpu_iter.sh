@@ -1,14 +1,11 @@
 #!/bin/bash
 mkdir -p gpurun_out
-run() { name=$1; shift; echo "=== $name"; timeout ${TMO:-600} "$@" > gpurun_out/$name.log 2>&1; echo "exit $?" | tee -a gpurun_out/$name.log; tail -${TAILN:-6} gpurun_out/$name.log; }
-run relev python -m pytest tests/test_gpu_relevance.py -q -x -s
-TUTOR_SCAN_SIMT=1 run relev_simt python -m pytest tests/test_gpu_relevance.py -q -x -s
-timeout 600 ncu --profile-from-start off --metrics gpu__time_duration.sum,dram__bytes_read.sum --clock-control none --csv --log-file gpurun_out/launches_corpus.csv python tools/profile_corpus.py > gpurun_out/ncu_corpus.log 2>&1
+run() { name=$1; shift; echo "=== $name"; timeout ${TMO:-900} "$@" > gpurun_out/$name.log 2>&1; echo "exit $?" | tee -a gpurun_out/$name.log; tail -${TAILN:-6} gpurun_out/$name.log; }
+run serving python -m pytest tests/test_serving.py -q -x -m gpu
+TAILN=1 run bench python bench.py --steps 3 --warmup 3
 python - <<'PY'
-import csv
-rows=[r for r in csv.reader(open('gpurun_out/launches_corpus.csv')) if len(r)>5]
-h=[i for i,r in enumerate(rows) if r[0]=='ID'][0]
-H=rows[h]
-for r in rows[h+1:]:
-    d=dict(zip(H,r)); print(d['Kernel Name'][:40], d['Grid Size'], d['Metric Name'], d['Metric Value'], d['Metric Unit'])
+import json
+for l in open("gpurun_out/bench.log"):
+    if l.startswith("{"):
+        j=json.loads(l); print(j["value"], j["e2e"]["value"], j["decode"]); print(json.dumps(j["extras"], indent=1)); print(j["cpu_baseline"])
 PY
