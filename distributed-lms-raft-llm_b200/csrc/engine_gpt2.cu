@@ -57,6 +57,7 @@ struct tutor_gpt2 {
   bool use_cluster = true;   // TUTOR_NO_CLUSTER=1: the 8-launch-per-layer chain (separate reduce kernels) for A/B runs
   float* ln_stats = nullptr;  // [d/128][B][2] per-row (mean, M2) of x over each 128-column tile, one slice per lane
   size_t ln_stats_lane_elems = 0;
+  bool no_ln_gemv = false;   // TUTOR_NO_LN_GEMV=1: separate LayerNorm kernels even for 1-2 rows (A/B measurements)
   bool use_ln_gemv = false;  // TUTOR_LN_GEMV=1: LayerNorm folded into the fp32 decode GEMVs - measured slower (2213 vs 2560 tok/s)
   // Decode lanes: the batch is cut into micro-batches whose kernel chains run concurrently (own stream, own
   // length counter), so one lane's latency-bound GEMM/reduce chain overlaps the other's bandwidth-bound attention.
@@ -112,7 +113,10 @@ int forward(tutor_gpt2* e, int B, int T, bool decode) {
   const int* npad = e->padded ? e->npad : nullptr;
   TRY(k_gpt2_embed(e->ids, e->ids_ld, len_dev, T, e->wte, dt, e->wpe, d, e->x, M, npad, st));
   // parity-mode decode of a few rows: LayerNorms are folded into the GEMVs that consume them (gemv_f32_ln_kernel)
-  const bool ln_in_gemv = e->use_ln_gemv && decode && dt == DT_F32 && M <= 8 && (size_t)M * d * 4 <= 48 * 1024;
+  // (M <= 2: the register GEMV, where LayerNorm costs two warp reductions; 3..8 rows: the shared-memory variant, which
+  // measured slower than separate LayerNorm kernels and stays opt-in behind TUTOR_LN_GEMV=1)
+  const bool ln_in_gemv = decode && dt == DT_F32 && d % 128 == 0 &&
+                          ((M <= 2 && d <= 1280 && !e->no_ln_gemv) || (e->use_ln_gemv && M <= 8 && (size_t)M * d * 4 <= 48 * 1024));
   for (int l = 0; l < e->L; ++l) {
     const Gpt2Layer& w = e->layers[l];
     if (!ln_in_gemv) TRY(k_layernorm(e->x, 1, 0, w.ln1_g, w.ln1_b, e->cfg.layer_norm_epsilon, xn_f, xn_b, M, d, st));
@@ -499,6 +503,7 @@ int tutor_gpt2_create(const tutor_gpt2_config* cfg, int device, tutor_gpt2_t** o
   e->use_pdl = getenv("TUTOR_NO_PDL") == nullptr;
   e->use_cluster = getenv("TUTOR_NO_CLUSTER") == nullptr;
   e->use_ln_gemv = getenv("TUTOR_LN_GEMV") != nullptr;
+  e->no_ln_gemv = getenv("TUTOR_NO_LN_GEMV") != nullptr;
   {
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) e->num_sms = prop.multiProcessorCount;

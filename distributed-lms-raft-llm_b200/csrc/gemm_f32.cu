@@ -28,8 +28,8 @@ __global__ void __launch_bounds__(256) gemv_f32_kernel(const float* __restrict__
 #pragma unroll
     for (int m = 0; m < MB; ++m) {
       const float* a = A + (size_t)(M0 + m) * K + k;
-      float4 a0 = __ldg((const float4*)a), a1 = __ldg((const float4*)(a + 128));
-      float4 a2 = __ldg((const float4*)(a + 256)), a3 = __ldg((const float4*)(a + 384));
+      float4 a0 = __ldcg((const float4*)a), a1 = __ldcg((const float4*)(a + 128));
+      float4 a2 = __ldcg((const float4*)(a + 256)), a3 = __ldcg((const float4*)(a + 384));
       acc[m] += (w0.x * a0.x + w0.y * a0.y + w0.z * a0.z + w0.w * a0.w) +
                 (w1.x * a1.x + w1.y * a1.y + w1.z * a1.z + w1.w * a1.w) +
                 (w2.x * a2.x + w2.y * a2.y + w2.z * a2.z + w2.w * a2.w) +
@@ -40,7 +40,7 @@ __global__ void __launch_bounds__(256) gemv_f32_kernel(const float* __restrict__
     float4 w0 = load4(w + k);
 #pragma unroll
     for (int m = 0; m < MB; ++m) {
-      float4 a0 = __ldg((const float4*)(A + (size_t)(M0 + m) * K + k));
+      float4 a0 = __ldcg((const float4*)(A + (size_t)(M0 + m) * K + k));
       acc[m] += w0.x * a0.x + w0.y * a0.y + w0.z * a0.z + w0.w * a0.w;
     }
   }
@@ -113,6 +113,105 @@ __global__ void __launch_bounds__(256) gemv_f32_ln_kernel(const float* __restric
   }
 }
 
+// Decode GEMV for one or two rows (the reference's own configuration is batch 1) built for the dependent-launch
+// chain: the whole weight row of this warp's output column - NV float4 per lane - and the LayerNorm parameters are
+// loaded into registers BEFORE griddepcontrol.wait (weights never change), so what remains on the critical path after
+// the predecessor finishes is one round trip for the input row, the FMAs and a warp reduction.  With LN the input row is
+// normalised in registers: a warp holds the full row (NV float4 per lane), so mean and variance are two warp
+// reductions - no shared memory, no block barrier, and no separate LayerNorm kernel (25 of the 88 launches of a
+// GPT-2-small decode forward).  xn_out (optional) receives the normalised rows from CTA 0.
+// The input row is read with ld.global.cg: under programmatic dependent launch this grid is alive while its predecessor
+// still writes that buffer, which rules out the read-only (.nc) path.
+template <int MB, int NV, bool LN>
+__global__ void __launch_bounds__(256) gemv_f32_reg_kernel(const float* __restrict__ X, const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta, float eps,
+                                                            const float* __restrict__ W, int N, GemmEpilogue epi,
+                                                            float* __restrict__ xn_out) {
+  constexpr int K = NV * 128;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = blockIdx.x * 8 + warp;
+  pdl_launch_dependents();
+  const float* w = W + (size_t)min(n, N - 1) * K + lane * 4;
+  float4 wv[NV], gv[LN ? NV : 1], bv[LN ? NV : 1];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) wv[j] = load4(w + j * 128);
+  if (LN) {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) { gv[j] = load4(gamma + lane * 4 + j * 128); bv[j] = load4(beta + lane * 4 + j * 128); }
+  }
+  pdl_wait();
+#pragma unroll
+  for (int m = 0; m < MB; ++m) {
+    const float* xr = X + (size_t)m * K + lane * 4;
+    float acc = 0.f;
+    if (LN) {
+      float4 xv[NV];
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < NV; ++j) { xv[j] = __ldcg((const float4*)(xr + j * 128)); s += (xv[j].x + xv[j].y) + (xv[j].z + xv[j].w); }
+      const float mean = warp_sum(s) / K;  // two-pass, like layernorm_kernel
+      float q = 0.f;
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        const float a = xv[j].x - mean, b = xv[j].y - mean, c = xv[j].z - mean, d = xv[j].w - mean;
+        q += (a * a + b * b) + (c * c + d * d);
+      }
+      const float rstd = 1.0f / sqrtf(warp_sum(q) / K + eps);
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        float4 o;
+        o.x = (xv[j].x - mean) * rstd * gv[j].x + bv[j].x; o.y = (xv[j].y - mean) * rstd * gv[j].y + bv[j].y;
+        o.z = (xv[j].z - mean) * rstd * gv[j].z + bv[j].z; o.w = (xv[j].w - mean) * rstd * gv[j].w + bv[j].w;
+        if (xn_out && blockIdx.x == 0 && warp == 0) *reinterpret_cast<float4*>(xn_out + (size_t)m * K + lane * 4 + j * 128) = o;
+        acc += wv[j].x * o.x + wv[j].y * o.y + wv[j].z * o.z + wv[j].w * o.w;
+      }
+    } else {
+#pragma unroll
+      for (int j0 = 0; j0 < NV; j0 += 8) {  // 8 independent 16-byte input loads in flight per lane
+        float4 xv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (j0 + j < NV) xv[j] = __ldcg((const float4*)(xr + (j0 + j) * 128));
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (j0 + j < NV)
+            acc += wv[j0 + j].x * xv[j].x + wv[j0 + j].y * xv[j].y + wv[j0 + j].z * xv[j].z + wv[j0 + j].w * xv[j].w;
+      }
+    }
+    const float s = warp_sum(acc);
+    if (lane == 0 && n < N) epilogue_store(epi, m, n, s);
+  }
+}
+
+template <int MB, bool LN>
+int launch_gemv_reg(const float* X, const float* gamma, const float* beta, float eps, const float* W, int N, int K,
+                    const GemmEpilogue& epi, float* xn_out, cudaStream_t st) {
+  const dim3 grid(ceil_div(N, 8)), block(256);
+#define GEMV_REG(nv)                                                                                                 \
+  case nv:                                                                                                           \
+    CUDA_TRY(tutor_launch(gemv_f32_reg_kernel<MB, nv, LN>, grid, block, 0, st, X, gamma, beta, eps, W, N, epi, xn_out)); \
+    break;
+  switch (K / 128) {
+    GEMV_REG(1) GEMV_REG(4) GEMV_REG(6) GEMV_REG(10)
+    case 24:  // mlp c_proj of GPT-2 small: never behind a LayerNorm (an LN instance would hold 3 x 24 float4 per lane)
+      if constexpr (!LN) {
+        CUDA_TRY(tutor_launch(gemv_f32_reg_kernel<MB, 24, false>, grid, block, 0, st, X, gamma, beta, eps, W, N, epi, xn_out));
+        break;
+      }
+      return TUTOR_ERR_ARG;
+    default:
+      tutor_set_error("gemv_f32: K=%d has no register-resident instance", K);
+      return TUTOR_ERR_ARG;
+  }
+#undef GEMV_REG
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+bool gemv_reg_ok(int M, int K, bool ln) {
+  const int nv = K / 128;
+  return M >= 1 && M <= 2 && K % 128 == 0 && (nv == 1 || nv == 4 || nv == 6 || nv == 10 || (nv == 24 && !ln));
+}
+
 constexpr int BM = 64, BN = 64, BK = 16, PAD = 4;
 
 __global__ void __launch_bounds__(256) sgemm_f32_kernel(const float* __restrict__ A, const float* __restrict__ W,
@@ -173,6 +272,9 @@ __global__ void __launch_bounds__(256) sgemm_f32_kernel(const float* __restrict_
 int k_gemv_f32_ln(const float* X, const float* gamma, const float* beta, float eps, const float* W, int M, int N, int K,
                   const GemmEpilogue& epi, float* xn_out, cudaStream_t st) {
   ARG_CHECK(M >= 1 && M <= 8 && K % 128 == 0, "gemv_f32_ln: unsupported M=%d K=%d", M, K);
+  if (gemv_reg_ok(M, K, true))
+    return M == 1 ? launch_gemv_reg<1, true>(X, gamma, beta, eps, W, N, K, epi, xn_out, st)
+                  : launch_gemv_reg<2, true>(X, gamma, beta, eps, W, N, K, epi, xn_out, st);
   const dim3 grid(ceil_div(N, 8)), block(256);
   const size_t smem = (size_t)M * K * sizeof(float);
   ARG_CHECK(smem <= 48 * 1024, "gemv_f32_ln: %d rows of %d do not fit in shared memory", M, K);
@@ -189,6 +291,9 @@ int k_gemv_f32_ln(const float* X, const float* gamma, const float* beta, float e
 int k_gemm_f32(const float* A, const float* W, int M, int N, int K, const GemmEpilogue& epi, cudaStream_t st) {
   ARG_CHECK(K % 128 == 0 || (M > 8 && K % BK == 0), "gemm_f32: K=%d unsupported (M=%d)", K, M);
   if (M == 0 || N == 0) return TUTOR_OK;
+  if (gemv_reg_ok(M, K, false))
+    return M == 1 ? launch_gemv_reg<1, false>(A, nullptr, nullptr, 0.f, W, N, K, epi, nullptr, st)
+                  : launch_gemv_reg<2, false>(A, nullptr, nullptr, 0.f, W, N, K, epi, nullptr, st);
   if (M <= 8 && K % 128 == 0) {
     dim3 grid(ceil_div(N, 8)), block(256);
 #define GEMV_CASE(n) case n: CUDA_TRY(tutor_launch(gemv_f32_kernel<n>, grid, block, 0, st, A, W, 0, N, K, epi)); break;
