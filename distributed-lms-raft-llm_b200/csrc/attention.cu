@@ -977,10 +977,18 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
   if (B == 0) return TUTOR_OK;
   ARG_CHECK(len_dev || (len_host >= 1 && len_host <= Smax), "attn_decode: len %d outside [1,%d]", len_host, Smax);
   dim3 grid(H, B), block(128);
-  if (q_dtype == DT_F32 && kv_dtype == DT_F32 && out_dtype == DT_F32)
+  // the fp32 kernel is launched without the programmatic-launch attribute unless TUTOR_ATTN_PDL=1: with it the batch-1
+  // decode forward measured 392 us against 381 us (its dependents' early weight loads compete with this kernel)
+  static const bool f32_plain = getenv("TUTOR_ATTN_PDL") == nullptr;
+  if (q_dtype == DT_F32 && kv_dtype == DT_F32 && out_dtype == DT_F32 && f32_plain)
     attn_decode_kernel<float, float, float, false, false><<<grid, block, 0, st>>>(
         (const float*)q, (float*)k, (float*)v, (float*)out, H, Smax, len_dev, len_host, nullptr, 0, nullptr, B, nullptr,
         nullptr, npad);
+  else if (q_dtype == DT_F32 && kv_dtype == DT_F32 && out_dtype == DT_F32)
+    // (through tutor_launch: part of the fp32 decode chain's programmatic dependent launches; the kernel waits first)
+    CUDA_TRY(tutor_launch(attn_decode_kernel<float, float, float, false, false>, grid, block, 0, st, (const float*)q,
+                          (float*)k, (float*)v, (float*)out, H, Smax, len_dev, len_host, (const float*)nullptr, 0,
+                          (const float*)nullptr, B, (float*)nullptr, (int*)nullptr, npad));
   else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16) {
     if (use_mma_decode()) {
       CUtensorMap tk, tv;  // the cache as a [B*H*Smax, 64] bf16 matrix, 64-row boxes, 128-byte swizzle
