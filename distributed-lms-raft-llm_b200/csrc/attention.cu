@@ -309,19 +309,34 @@ __global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf
     const int e0 = (lane % LPR) * EPL;
     float qv[EPL];
     if (FUSED) {
+      // 192 values (q, k, v of this head) over 128 threads: both rounds' loads are issued before the first store, so
+      // the prologue costs one L2 round trip, not two (it sits on the critical path right after the wait)
       const int d = H * 64;
-      for (int e = threadIdx.x; e < 192; e += 128) {
-        const int which = e >> 6, i = e & 63;
-        const int n = which * d + h * 64 + i;
-        float acc = qkv_bias[n];
+      float accv[2];
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int e = threadIdx.x + r * 128;
+        accv[r] = 0.f;
+        if (e < 192) {
+          const int n = (e >> 6) * d + h * 64 + (e & 63);
+          float acc = qkv_bias[n];
 #pragma unroll 8
-        for (int zz = 0; zz < ks; ++zz) acc += qkv_partial[((size_t)zz * B + b) * (3 * d) + n];
-        if (which == 0) {
-          s_new[0][i] = acc;
-        } else {
-          const bf16 st = __float2bfloat16_rn(acc);
-          (which == 1 ? kc : vc)[base + (size_t)(len - 1) * 64 + i] = st;  // cache append (no torch.cat)
-          s_new[which][i] = __bfloat162float(st);
+          for (int zz = 0; zz < ks; ++zz) acc += qkv_partial[((size_t)zz * B + b) * (3 * d) + n];
+          accv[r] = acc;
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int e = threadIdx.x + r * 128;
+        if (e < 192) {
+          const int which = e >> 6, i = e & 63;
+          if (which == 0) {
+            s_new[0][i] = accv[r];
+          } else {
+            const bf16 st = __float2bfloat16_rn(accv[r]);
+            (which == 1 ? kc : vc)[base + (size_t)(len - 1) * 64 + i] = st;  // cache append (no torch.cat)
+            s_new[which][i] = __bfloat162float(st);
+          }
         }
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");  // consumer warps only
