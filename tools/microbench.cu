@@ -135,8 +135,8 @@ int main() {
         for (int i = 0; i < 12; ++i) {
           if (k_make_map_bf16(&tk[i], kp(i), 768 * 768, 64, DM_CHUNK) || k_make_map_bf16(&tv[i], vp(i), 768 * 768, 64, DM_CHUNK)) exit(3);
         }
-        ATT("mma ring chunk 32 x 4 stages", (attn_decode_mma_kernel<false, true><<<dim3(12, 64), DM_THREADS, 0, st>>>(tk[i % 12], tv[i % 12], qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
-        ATT("mma ring chunk 32 x 4 stages, no math", (attn_decode_mma_kernel<false, false><<<dim3(12, 64), DM_THREADS, 0, st>>>(tk[i % 12], tv[i % 12], qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
+        ATT("mma ring chunk 32 x 4 stages", (attn_decode_mma_kernel<false, true><<<dim3(12, 64), DM_THREADS, 0, st>>>(tk[i % 12], tv[i % 12], qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0, 0, nullptr, nullptr)));
+        ATT("mma ring chunk 32 x 4 stages, no math", (attn_decode_mma_kernel<false, false><<<dim3(12, 64), DM_THREADS, 0, st>>>(tk[i % 12], tv[i % 12], qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0, 0, nullptr, nullptr)));
       }
       ATT("ring chunk 16 x 8 stages", (attn_decode_tma_kernel<false, 16, 8, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
     }
