@@ -244,6 +244,7 @@ int forward_decode_cluster(tutor_gpt2* e, int lane, int b0, int B) {
   const size_t kv_off = (size_t)b0 * e->H * e->Smax * 64 * e->esz();
   const int* npad = e->padded ? e->npad + b0 : nullptr;
   const DecodePlan pl = decode_plan(e, B);
+  const char* skip = getenv("TUTOR_SKIP") ? getenv("TUTOR_SKIP") : "";
   const int bn_qkv = pl.bn_qkv, bn_fc = pl.bn_fc, bn_res = pl.bn_res;
   const int ks_qkv = pl.ks_qkv, ks_proj = pl.ks_proj, ks_fc = pl.ks_fc, ks_proj2 = pl.ks_proj2;
   TRY(k_gpt2_embed(e->ids + (size_t)b0 * e->ids_ld, e->ids_ld, len, 1, e->wte, e->dt, e->wpe, d, x, B, npad, st));
@@ -252,17 +253,25 @@ int forward_decode_cluster(tutor_gpt2* e, int lane, int b0, int B) {
     const Gpt2Layer& w = e->layers[l];
     void* kc = (uint8_t*)e->kcache(l) + kv_off;
     void* vc = (uint8_t*)e->vcache(l) + kv_off;
-    TRY(k_gemm_ln_splitk(x, stats, nst, w.ln1_g, w.ln1_b, eps, (const bf16*)w.qkv.w, B, 3 * d, d, ks_qkv, bn_qkv, partial,
-                         st));
-    TRY(k_attn_decode_fused(partial, ks_qkv, w.qkv.b, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
-                            e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, npad,
-                            e->cur_T, (e->cur_T + e->cur_total) / 2, st));
-    TRY(k_gemm_resid_stats(att, (const bf16*)w.proj.w, w.proj.b, B, d, d, ks_proj, bn_res, x, stats, st));
-    TRY(k_gemm_ln_act(x, stats, nst, w.ln2_g, w.ln2_b, eps, (const bf16*)w.fc.w, w.fc.b, ACT_GELU_TANH, B, 4 * d, d, ks_fc,
-                      bn_fc, hb, st));
-    TRY(k_gemm_resid_stats(hb, (const bf16*)w.proj2.w, w.proj2.b, B, d, 4 * d, ks_proj2, bn_res, x, stats, st));
+    // TUTOR_SKIP=<letters> leaves kernels out of the step (q: c_attn, a: attention, p: c_proj, f: c_fc, m: mlp c_proj,
+    // h: LM head) - timing ablation only (tools/gpu_ablate.sh): the tokens are meaningless then
+    if (!strchr(skip, 'q'))
+      TRY(k_gemm_ln_splitk(x, stats, nst, w.ln1_g, w.ln1_b, eps, (const bf16*)w.qkv.w, B, 3 * d, d, ks_qkv, bn_qkv, partial,
+                           st));
+    if (!strchr(skip, 'a'))
+      TRY(k_attn_decode_fused(partial, ks_qkv, w.qkv.b, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
+                              e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, npad,
+                              e->cur_T, (e->cur_T + e->cur_total) / 2, st));
+    if (!strchr(skip, 'p'))
+      TRY(k_gemm_resid_stats(att, (const bf16*)w.proj.w, w.proj.b, B, d, d, ks_proj, bn_res, x, stats, st));
+    if (!strchr(skip, 'f'))
+      TRY(k_gemm_ln_act(x, stats, nst, w.ln2_g, w.ln2_b, eps, (const bf16*)w.fc.w, w.fc.b, ACT_GELU_TANH, B, 4 * d, d, ks_fc,
+                        bn_fc, hb, st));
+    if (!strchr(skip, 'm'))
+      TRY(k_gemm_resid_stats(hb, (const bf16*)w.proj2.w, w.proj2.b, B, d, 4 * d, ks_proj2, bn_res, x, stats, st));
   }
   TRY(k_layernorm(x, 1, 0, e->lnf_g, e->lnf_b, eps, nullptr, xl, B, d, st));
+  if (strchr(skip, 'h')) return TUTOR_OK;
   return k_lmhead_argmax(xl, e->dt, e->wte, e->dt, B, e->V, d, e->dstate(lane, b0),
                          (uint8_t*)e->lm_scratch + (size_t)lane * e->lm_scratch_lane_bytes, st);
 }

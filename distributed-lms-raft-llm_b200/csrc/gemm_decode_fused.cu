@@ -166,7 +166,9 @@ __global__ void __launch_bounds__(NTHREADS) gemm_decode_fused_kernel(const __gri
       // 16 consecutive threads read one 256-byte row segment (4 full lines per warp load); a thread keeps the same
       // float4 column group c4 in every k-block and walks the rows (t / 16) + 8 * it.
       constexpr int V4 = BN / 8;              // float4 loads per thread per k-block
-      constexpr int KG = BN >= 64 ? 128 / BN : 4;  // k-blocks loaded together: 16 float4 in flight per thread
+      // k-blocks loaded together: 16 float4 in flight per thread (8 at BN <= 32; 8 k-blocks at once at BN = 16
+      // measured slower: 0.621 vs 0.612 ms per decode forward)
+      constexpr int KG = BN >= 64 ? 128 / BN : 4;
       const int c4 = t & 15, rsub = t >> 4;
       // gamma / beta of the K slice are weights: staged in shared memory ahead of the programmatic-launch wait
       float* sgam = ln_smem;

@@ -16,6 +16,8 @@ template <int BN> struct SmemLayout {
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   // sized so that two CTAs fit one SM (<= ~100 KB each): one CTA's epilogue overlaps the other's mainloop
+  // (six stages at BN = 16 would cover all 6 k-blocks of a typical decode CTA before the programmatic-launch wait,
+  // but two such CTAs no longer fit one SM: measured 0.627 vs 0.612 ms per decode forward)
   static constexpr int STAGES = (BN >= 256) ? 2 : (BN >= 128) ? 3 : (BN >= 64 ? 4 : 5);
   static constexpr int TILE_BYTES = STAGES * STAGE_BYTES;
   static constexpr int BAR_BYTES = 256;
