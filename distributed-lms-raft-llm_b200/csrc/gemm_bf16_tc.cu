@@ -492,24 +492,29 @@ struct TmaEpilogue {
   int qkv, d, H, T, Smax, pos0;
 };
 
-template <int BN> struct PersistTmaLayout {
+// EW epilogue warps.  16: every warp owns one 64-column slice of a tile, bias in shared memory, 3 mainloop stages.
+// 8: two slices per warp and the bias in registers (fetched by shuffle), which frees the room for a 4th stage - for
+// long-K GEMMs (K >= 2048) whose mainloop hides the longer epilogue and pays for a short ring instead.
+template <int BN, int EW> struct PersistTmaLayout {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int EPI_BYTES = PERSIST_EPI_WARPS * 4096;  // one swizzled 32 x 128 B buffer per epilogue warp
-  static constexpr int BIAS_BYTES = PERSIST_EPI_WARPS * 256;  // 64 floats per epilogue warp
-  static constexpr int STAGES = (226 * 1024 - EPI_BYTES - BIAS_BYTES - 512 - 1024) / STAGE_BYTES;  // 3 at BN=256
+  static constexpr int EPI_BYTES = EW * 4096;                      // one swizzled 32 x 128 B buffer per epilogue warp
+  static constexpr int BIAS_BYTES = EW == 16 ? EW * 256 : 0;       // 64 floats per epilogue warp
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int STAGES = (227 * 1024 - EPI_BYTES - BIAS_BYTES - BAR_BYTES - 1024) / STAGE_BYTES;  // 3 / 4 at BN=256
   static constexpr int TILE_BYTES = STAGES * STAGE_BYTES;
-  static constexpr int TOTAL = TILE_BYTES + EPI_BYTES + BIAS_BYTES + 512 + 1024;
+  static constexpr int TOTAL = TILE_BYTES + EPI_BYTES + BIAS_BYTES + BAR_BYTES + 1024;
 };
 
-template <int BN>
-__global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_tma_kernel(
+template <int BN, int EW>
+__global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
     const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
     const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes,
     const __grid_constant__ CUtensorMap tmV, int M, int N, int K, TmaEpilogue epi) {
-  using L = PersistTmaLayout<BN>;
-  static_assert(BN == 256, "16 epilogue warps x 64 columns");
+  using L = PersistTmaLayout<BN, EW>;
+  static_assert(BN == 256 && (EW == 16 || EW == 8), "four 64-column slices per tile row block, 1 or 2 per warp");
+  constexpr int SPW = 16 / EW;  // 64-column slices per epilogue warp
   constexpr int TMEM_COLS = 2 * BN;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -519,8 +524,8 @@ __global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_tma_ker
   uint64_t* empty_bar = full_bar + L::STAGES;
   uint64_t* tmem_full_bar = empty_bar + L::STAGES;  // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;     // [2]
-  uint64_t* res_bar = tmem_empty_bar + 2;           // [PERSIST_EPI_WARPS]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + PERSIST_EPI_WARPS);
+  uint64_t* res_bar = tmem_empty_bar + 2;           // [EW]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + EW);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nk = K / BK;
@@ -532,8 +537,8 @@ __global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_tma_ker
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmOut) : "memory");
     for (int s = 0; s < L::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], PERSIST_EPI_WARPS); }
-    for (int w = 0; w < PERSIST_EPI_WARPS; ++w) mbar_init(&res_bar[w], 1);
+    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], EW); }
+    for (int w = 0; w < EW; ++w) mbar_init(&res_bar[w], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -591,9 +596,10 @@ __global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_tma_ker
     }
   } else {
     // ===== epilogue: warp w owns TMEM lanes of quadrant w % 4 (32 output rows) and columns [64 q, 64 q + 64) =====
-    const int ew = warp - 2, quad = warp & 3, cslice = ew >> 2;
+    const int ew = warp - 2, quad = warp & 3;
     const uint32_t stage = smem_u32(stage_all + ew * 4096);
-    float* sbias = bias_all + ew * 64;
+    float* sbias = bias_all + ew * 64;  // (EW == 16 only)
+    float2 breg = make_float2(0.f, 0.f);  // EW == 8: this lane's two bias values of the current slice
     uint64_t* rbar = &res_bar[ew];
     uint32_t ti = 0, res_uses = 0;
     const uint32_t swz = (uint32_t)(lane & 7);
@@ -601,15 +607,24 @@ __global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_tma_ker
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++ti) {
       const int a_row0 = (t % m_tiles) * BM, b_row0 = (t / m_tiles) * BN;
       const uint32_t acc = ti & 1;
-      const int row0 = a_row0 + quad * 32, col0 = b_row0 + cslice * 64;
+      const int row0 = a_row0 + quad * 32;
+#pragma unroll 1
+      for (int rep = 0; rep < SPW; ++rep) {
+      const int cslice = (ew >> 2) * SPW + rep, col0 = b_row0 + cslice * 64;
+      const bool last_slice = rep == SPW - 1;
       const bool live = row0 < M && col0 < N;  // warp-uniform; a dead piece only hands the accumulator back
       if (live) {
-        // ahead of the accumulator: bias of these 64 columns into shared memory, first residual piece on its way
-        if (lane < 16) {
-          const int n = col0 + lane * 4;
-          float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (epi.bias && n < N) b4 = *reinterpret_cast<const float4*>(epi.bias + n);  // N % 4 == 0
-          *reinterpret_cast<float4*>(sbias + lane * 4) = b4;
+        // ahead of the accumulator: bias of these 64 columns (shared memory or registers), first residual piece on its way
+        if (EW == 16) {
+          if (lane < 16) {
+            const int n = col0 + lane * 4;
+            float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (epi.bias && n < N) b4 = *reinterpret_cast<const float4*>(epi.bias + n);  // N % 4 == 0
+            *reinterpret_cast<float4*>(sbias + lane * 4) = b4;
+          }
+        } else {
+          const int n = col0 + lane * 2;
+          breg = (epi.bias && n < N) ? *reinterpret_cast<const float2*>(epi.bias + n) : make_float2(0.f, 0.f);
         }
         if (epi.has_res && lane == 0) {
           tma_store_wait_read();  // the previous tile's store has left the buffer
@@ -618,39 +633,51 @@ __global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_tma_ker
         }
         __syncwarp();
       }
-      mbar_wait(&tmem_full_bar[acc], (ti >> 1) & 1, 2);
-      tc_fence_after();
+      if (rep == 0) {
+        mbar_wait(&tmem_full_bar[acc], (ti >> 1) & 1, 2);
+        tc_fence_after();
+      }
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quad * 32) << 16) + cslice * 64;
 #ifdef TUTOR_TRACE
       if (g_epi_skip == 1) {  // tools/microbench_gemm.cu: mainloop only
-        if (epi.has_res) { mbar_wait(rbar, res_uses & 1, 5); ++res_uses; }
+        if (epi.has_res && live) { mbar_wait(rbar, res_uses & 1, 5); ++res_uses; }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        if (lane == 0 && last_slice) mbar_arrive(&tmem_empty_bar[acc]);
         continue;
       }
 #endif
       if (!live) {
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        if (lane == 0 && last_slice) mbar_arrive(&tmem_empty_bar[acc]);
         continue;
       }
+      // bias of element i (0..63) of this slice
+      auto bias_at = [&](int i) -> float {
+        if (EW == 16) return sbias[i];
+        return __shfl_sync(0xffffffffu, (i & 1) ? breg.y : breg.x, i >> 1);
+      };
       if (epi.out_f32) {
         // two pieces of 32 fp32 columns (128-byte rows)
 #pragma unroll 1
         for (int sub = 0; sub < 2; ++sub) {
           float v[32];
           tc_ld32(taddr + sub * 32, v);
-          if (sub == 1) {  // last read of this accumulator by this warp
+          if (sub == 1 && last_slice) {  // last read of this accumulator by this warp
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
           }
           const int c0 = col0 + sub * 32;
           if (c0 >= N) continue;  // (the TMA store would clip it anyway)
+          if (sub == 0) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = apply_act_fast(v[i] + sbias[sub * 32 + i], epi.act);
+            for (int i = 0; i < 32; ++i) v[i] = apply_act_fast(v[i] + bias_at(i), epi.act);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = apply_act_fast(v[i] + bias_at(32 + i), epi.act);
+          }
           if (epi.has_res) {
             mbar_wait(rbar, res_uses & 1, 5);
             ++res_uses;
@@ -690,7 +717,7 @@ __global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_tma_ker
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
-          mbar_arrive(&tmem_empty_bar[acc]);
+          if (last_slice) mbar_arrive(&tmem_empty_bar[acc]);
           tma_store_wait_read();  // the buffer's previous contents have left
         }
         __syncwarp();
@@ -700,8 +727,8 @@ __global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_tma_ker
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const int i = 8 * c + 2 * j;
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(apply_act_fast(v[i] + sbias[i], epi.act),
-                                                     apply_act_fast(v[i + 1] + sbias[i + 1], epi.act));
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(apply_act_fast(v[i] + bias_at(i), epi.act),
+                                                     apply_act_fast(v[i + 1] + bias_at(i + 1), epi.act));
             w[j] = *reinterpret_cast<uint32_t*>(&h2);
           }
           asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(my_row + (((uint32_t)c ^ swz) << 4)), "r"(w[0]),
@@ -722,6 +749,7 @@ __global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_tma_ker
         }
         __syncwarp();
       }
+      }  // slices of this warp
     }
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // stores complete before the CTA exits
   }
@@ -862,9 +890,11 @@ bool tma_epilogue_ok(const GemmEpilogue& e, int M, int N) {
   return N % 8 == 0;
 }
 
+template <int EW>
 int launch_persistent_tma(const bf16* A, int M, const bf16* W, int N, int K, const GemmEpilogue& e, cudaStream_t st) {
-  using L = PersistTmaLayout<256>;
-  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(gemm_bf16_persistent_tma_kernel<256>), L::TOTAL));
+  using L = PersistTmaLayout<256, EW>;
+  static_assert(L::TOTAL <= 227 * 1024, "shared-memory budget");
+  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(gemm_bf16_persistent_tma_kernel<256, EW>), L::TOTAL));
   CUtensorMap ta, tb, to, tr, tv;
   TRY(make_map(&ta, A, M, K, BM));
   TRY(make_map(&tb, W, N, K, 256));
@@ -886,7 +916,7 @@ int launch_persistent_tma(const bf16* A, int M, const bf16* W, int N, int K, con
   CUDA_TRY(cudaGetDevice(&dev));
   CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const int ntiles = ceil_div(M, BM) * ceil_div(N, 256);
-  CUDA_TRY(tutor_launch(gemm_bf16_persistent_tma_kernel<256>, dim3(ntiles < sms ? ntiles : sms), dim3(NTHREADS_PERSIST),
+  CUDA_TRY(tutor_launch(gemm_bf16_persistent_tma_kernel<256, EW>, dim3(ntiles < sms ? ntiles : sms), dim3(64 + 32 * EW),
                         (size_t)L::TOTAL, st, ta, tb, to, tr, tv, M, N, K, te));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
@@ -944,7 +974,12 @@ int k_gemm_bf16(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpi
   static const bool wide = getenv("TUTOR_GEMM_BN128") == nullptr;
   static const bool persistent = getenv("TUTOR_GEMM_NONPERSISTENT") == nullptr;  // debugging aid / A-B measurements
   static const bool tma_epi = getenv("TUTOR_GEMM_NO_TMA_EPILOGUE") == nullptr;  // A/B measurements
-  if (persistent && tma_epi && N >= 128 && tma_epilogue_ok(epi, M, N)) return launch_persistent_tma(A, M, W, N, K, epi, st);
+  if (persistent && tma_epi && N >= 128 && tma_epilogue_ok(epi, M, N)) {
+    // long K: the mainloop hides an 8-warp epilogue and gains a 4th pipeline stage (TUTOR_GEMM_EW16=1 forces 16 warps)
+    static const bool ew16 = getenv("TUTOR_GEMM_EW16") != nullptr;
+    if (K >= 2048 && !ew16) return launch_persistent_tma<8>(A, M, W, N, K, epi, st);
+    return launch_persistent_tma<16>(A, M, W, N, K, epi, st);
+  }
   if (persistent) {
     if (wide && N >= 256) return launch_persistent<256>(A, M, W, N, K, epi, st);
     return launch_persistent<128>(A, M, W, N, K, epi, st);

@@ -242,6 +242,89 @@ __global__ void __launch_bounds__(256) topk_chunk_kernel(const float* __restrict
               idx_base + p0);
 }
 
+// k <= 32: the same exact selection without block-wide rounds.  Each warp first selects the top k of its own 512
+// scores - a lane keeps the best of its 16 (strided) elements cached, a round is one warp arg-max (5 shuffles) and only
+// the winning lane rescans - then warp 0 selects the top k of the 8 x k survivors.  Ties go to the lower index.
+// (The block-wide version spent k rounds x (16 smem reads per thread + 2 barriers): 155 us of a 0.84 ms search.)
+__device__ __forceinline__ void warp_argmax(float& v, int& p) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, v, o);
+    const int op = __shfl_xor_sync(0xffffffffu, p, o);
+    if (ov > v || (ov == v && op < p)) { v = ov; p = op; }
+  }
+}
+
+__global__ void __launch_bounds__(256) topk_chunk_fast_kernel(const float* __restrict__ scores, int N, int k,
+                                                               float* __restrict__ cand_v, int32_t* __restrict__ cand_i,
+                                                               int idx_base) {
+  __shared__ float sv[CHUNK];
+  __shared__ float wv[8][32];
+  __shared__ int wp[8][32];
+  const int chunk = blockIdx.x, q = blockIdx.y, nchunks = gridDim.x;
+  const int p0 = chunk * CHUNK;
+  const int n = min(CHUNK, N - p0);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int wbase = warp * 512;  // this warp's 512 positions; lane owns wbase + lane + 32 j
+  auto rescan = [&](float& bv, int& bp) {
+    bv = -CUDART_INF_F; bp = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const int p = wbase + lane + 32 * j;
+      const float v = sv[p];
+      if (v > bv) { bv = v; bp = p; }  // ascending p: strict > keeps the lowest position
+    }
+  };
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const int p = wbase + lane + 32 * j;
+    sv[p] = p < n ? scores[(size_t)q * N + p0 + p] : -CUDART_INF_F;
+  }
+  __syncwarp();
+  float bv; int bp;
+  rescan(bv, bp);
+  for (int round = 0; round < k; ++round) {
+    float v = bv; int p = bp;
+    warp_argmax(v, p);
+    if (lane == 0) { wv[warp][round] = v; wp[warp][round] = p; }
+    if (p != 0x7fffffff && ((p - wbase) & 31) == lane) {  // the owner drops the winner and refreshes its cache
+      sv[p] = -CUDART_INF_F;
+      rescan(bv, bp);
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  if (warp == 0) {
+    // 8 x k survivors, lane l holds those of warp l % 8 at rounds l / 8, l / 8 + 4, ...
+    const int sw = lane & 7;
+    float cv[8]; int cp[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int r = (lane >> 3) + 4 * j;
+      const bool ok = r < k;
+      cv[j] = ok ? wv[sw][r] : -CUDART_INF_F;
+      cp[j] = ok ? wp[sw][r] : 0x7fffffff;
+      if (cv[j] == -CUDART_INF_F) cp[j] = 0x7fffffff;  // exhausted warp: not a candidate
+    }
+    float* out_v = cand_v + ((size_t)q * nchunks + chunk) * k;
+    int32_t* out_i = cand_i + ((size_t)q * nchunks + chunk) * k;
+    for (int round = 0; round < k; ++round) {
+      float v = -CUDART_INF_F; int p = 0x7fffffff;
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (cv[j] > v || (cv[j] == v && cp[j] < p)) { v = cv[j]; p = cp[j]; }
+      warp_argmax(v, p);
+      if (lane == 0) {
+        out_v[round] = p != 0x7fffffff ? v : -CUDART_INF_F;
+        out_i[round] = p != 0x7fffffff ? idx_base + p0 + p : -1;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (cp[j] == p) { cv[j] = -CUDART_INF_F; cp[j] = 0x7fffffff; }  // positions are unique
+    }
+  }
+}
+
 // grid (Q): candidates [Q][ncand] (value, index); candidates must be ordered by ascending index among equal values
 __global__ void __launch_bounds__(256) topk_merge_kernel(const float* __restrict__ cand_v,
                                                           const int32_t* __restrict__ cand_i, int ncand, int k,
@@ -309,7 +392,8 @@ int k_cosine_topk(const float* queries, const void* corpus, int corpus_dtype, co
   static const bool use_tc = getenv("TUTOR_SCAN_SIMT") == nullptr;  // A/B: the fp32 FFMA2 scan below
   if (use_tc && Q <= 32 && d % 32 == 0 && d <= 768) {
     TRY(k_cosine_scan_tc(queries, (const float*)corpus, corpus_inv_norm, Q, N, d, eps, scores, tc_scratch, st));
-    topk_chunk_kernel<<<dim3(nchunks, Q), 256, 0, st>>>(scores, N, k, cand_v, cand_i, idx_base);
+    if (k <= 32) topk_chunk_fast_kernel<<<dim3(nchunks, Q), 256, 0, st>>>(scores, N, k, cand_v, cand_i, idx_base);
+    else topk_chunk_kernel<<<dim3(nchunks, Q), 256, 0, st>>>(scores, N, k, cand_v, cand_i, idx_base);
     KERNEL_LAUNCHED();
     return k_topk_merge(cand_v, cand_i, Q, nchunks * k, k, out_scores, out_idx, st);
   }
@@ -329,7 +413,8 @@ int k_cosine_topk(const float* queries, const void* corpus, int corpus_dtype, co
     }
   }
   KERNEL_LAUNCHED();
-  topk_chunk_kernel<<<dim3(nchunks, Q), 256, 0, st>>>(scores, N, k, cand_v, cand_i, idx_base);
+  if (k <= 32) topk_chunk_fast_kernel<<<dim3(nchunks, Q), 256, 0, st>>>(scores, N, k, cand_v, cand_i, idx_base);
+    else topk_chunk_kernel<<<dim3(nchunks, Q), 256, 0, st>>>(scores, N, k, cand_v, cand_i, idx_base);
   KERNEL_LAUNCHED();
   // chunk candidates are in ascending chunk order, i.e. ascending index among equal values
   return k_topk_merge(cand_v, cand_i, Q, nchunks * k, k, out_scores, out_idx, st);

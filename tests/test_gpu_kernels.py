@@ -65,7 +65,7 @@ def test_linear_f32(pkg, lib, M, N, K, act, use_res):
 
 # (M, N, K): decode-shaped (swap-AB, M <= 128) and prefill-shaped (row-major, M > 128), ragged edges included
 BF16_SHAPES = [(1, 768, 768), (16, 2304, 768), (64, 768, 3072), (64, 3072, 768), (50, 200, 128), (128, 256, 64),
-               (129, 256, 64), (300, 2304, 768), (1024, 3072, 768), (257, 100, 192)]
+               (129, 256, 64), (300, 2304, 768), (1024, 3072, 768), (257, 100, 192), (300, 768, 3072), (512, 264, 2048)]
 
 
 @pytest.mark.parametrize("impl", [1, 0], ids=["mma_sync_check", "tcgen05"])
