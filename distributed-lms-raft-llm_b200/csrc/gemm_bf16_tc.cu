@@ -712,8 +712,7 @@ __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
       } else {
         // one piece of 64 bf16 columns (128-byte rows)
         float v[64];
-        tc_ld32(taddr, v);
-        tc_ld32(taddr + 32, v + 32);
+        tc_ld32x2(taddr, taddr + 32, v, v + 32);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {

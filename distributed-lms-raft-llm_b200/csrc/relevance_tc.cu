@@ -208,9 +208,8 @@ __global__ void __launch_bounds__(TS_THREADS) cosine_scan_tf32x3_kernel(const __
         tc_fence_after();
         float vm[32], vc[32], vd[32];
         const uint32_t taddr = tmem_base + buf * 128 + ((uint32_t)(quad * 32) << 16);
-        tc_ld32(taddr, vm);               // c_hi.q_hi
-        tc_ld32(taddr + TS_NQ, vc);       // c_hi.q_lo
-        tc_ld32(taddr + 2 * TS_NQ, vd);   // c_lo.q_hi
+        tc_ld32x2(taddr, taddr + TS_NQ, vm, vc);  // c_hi.q_hi, c_hi.q_lo
+        tc_ld32(taddr + 2 * TS_NQ, vd);           // c_lo.q_hi
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
