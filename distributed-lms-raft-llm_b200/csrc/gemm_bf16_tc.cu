@@ -137,7 +137,9 @@ __global__ void __launch_bounds__(EPI == EPI_ROWMAJOR ? NTHREADS_WIDE : NTHREADS
                                                                       const __grid_constant__ CUtensorMap tmC,
                                                                       int rowsA, int rowsB, int K, GemmEpilogue epi,
                                                                       ArgmaxArgs am) {
-  using L = SmemLayout<BN>;
+  // LM head at batch 64: three stages (72 KB) so that three CTAs share an SM - 444 slots hold all 393 vocabulary
+  // tiles of GPT-2 in one wave instead of 296 + a 97-CTA tail
+  using L = SmemLayout<BN, (EPI == EPI_ARGMAX && BN == 64) ? 3 : 0>;
   constexpr int TMEM_COLS = (BN < 32) ? 32 : BN;  // power of two >= 32 (BN in {16,32,64,128,256})
   extern __shared__ uint8_t smem_raw[];
   uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -840,7 +842,7 @@ int make_map_epi(CUtensorMap* map, const void* ptr, bool f32, int rows, int cols
 template <int BN, int EPI>
 int launch(const bf16* A, int rowsA, const bf16* B, int rowsB, int K, const GemmEpilogue& epi, const ArgmaxArgs& am,
            cudaStream_t st, int ks = 1) {
-  using L = SmemLayout<BN>;
+  using L = SmemLayout<BN, (EPI == EPI_ARGMAX && BN == 64) ? 3 : 0>;
   TRY(tutor_set_max_smem(reinterpret_cast<const void*>(gemm_bf16_tcgen05_kernel<BN, EPI>), L::TOTAL));
   CUtensorMap ta, tb, tc;
   TRY(make_map(&ta, A, rowsA, K, BM));

@@ -11,14 +11,14 @@ namespace tcptx {
 constexpr int BM = 128, BK = 64, UMMA_K = 16;  // UMMA tile: 128 rows of operand A, 64-wide (128-byte) k-blocks
 
 // pipeline stages of the one-tile-per-CTA kernels (operand A 128 x 64 bf16, operand B BN x 64 bf16 per stage)
-template <int BN> struct SmemLayout {
+template <int BN, int ST = 0> struct SmemLayout {  // ST: pipeline stages (0 = the default for this tile width)
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   // sized so that two CTAs fit one SM (<= ~100 KB each): one CTA's epilogue overlaps the other's mainloop
   // (six stages at BN = 16 would cover all 6 k-blocks of a typical decode CTA before the programmatic-launch wait,
   // but two such CTAs no longer fit one SM: measured 0.627 vs 0.612 ms per decode forward)
-  static constexpr int STAGES = (BN >= 256) ? 2 : (BN >= 128) ? 3 : (BN >= 64 ? 4 : 5);
+  static constexpr int STAGES = ST ? ST : (BN >= 256) ? 2 : (BN >= 128) ? 3 : (BN >= 64 ? 4 : 5);
   static constexpr int TILE_BYTES = STAGES * STAGE_BYTES;
   static constexpr int BAR_BYTES = 256;
   static constexpr int TOTAL = TILE_BYTES + BAR_BYTES + 1024;  // +1024: manual 1 KB alignment of the tiles

@@ -171,6 +171,12 @@ def test_fused_decode_path_matches_unfused(pkg, tiny_hf, monkeypatch):
     monkeypatch.setenv("TUTOR_NO_FUSED", "1")
     plain = pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="bf16")
     monkeypatch.delenv("TUTOR_NO_FUSED")
+    monkeypatch.setenv("TUTOR_NO_CLUSTER", "1")  # the 8-launch-per-layer chain with separate reduce kernels
+    splitk = pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="bf16")
+    monkeypatch.delenv("TUTOR_NO_CLUSTER")
+    splitk.prefill(ids, max_new_tokens=24, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
+    splitk.step(12)
+    ref_logits = splitk.last_logits().float().cpu()
     logits = []
     for eng in (fused, plain):
         eng.prefill(ids, max_new_tokens=24, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
@@ -179,6 +185,9 @@ def test_fused_decode_path_matches_unfused(pkg, tiny_hf, monkeypatch):
     err = ((logits[0] - logits[1]).abs().max() / logits[1].abs().max()).item()
     print(f"fused vs unfused bf16 decode: relative logit difference {err:.3e}")
     assert err < 2e-2
+    err_c = ((logits[0] - ref_logits).abs().max() / ref_logits.abs().max()).item()
+    print(f"cluster (LN-operand / DSMEM reduce) vs split-K + reduce kernels: relative logit difference {err_c:.3e}")
+    assert err_c < 2e-2
     a = fused.generate(ids, max_new_tokens=24, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
     b = plain.generate(ids, max_new_tokens=24, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
     assert (a == b).float().mean().item() > 0.9
