@@ -100,9 +100,11 @@ int k_lmhead_logits(const void* xn, int x_dtype, const void* wte, int w_dtype, i
 
 // ---- relevance_tc.cu : the corpus scan on the tensor cores (3xTF32, fp32-equivalent accuracy); scratch holds the
 // split queries.  scores[q][n] = cos(query q, corpus row n), the same contract as the SIMT scan in relevance.cu
-size_t k_cosine_scan_tc_scratch_bytes(int d);
+// and the exact top-k [Q,k] taken from per-32-row group maxima the scan leaves behind (k <= 32, N <= 1.6 M rows)
+size_t k_cosine_scan_tc_scratch_bytes(int d, int N);
 int k_cosine_scan_tc(const float* queries, const float* corpus, const float* corpus_inv_norm, int Q, int N, int d,
-                     float eps, float* scores, void* scratch, cudaStream_t st);
+                     float eps, float* scores, void* scratch, int k, float* out_scores, int32_t* out_idx, int idx_base,
+                     cudaStream_t st);
 
 // ---- relevance.cu : corpus scan
 size_t k_cosine_topk_scratch_bytes(int Q, int N, int k);

@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(256) topk_merge_kernel(const float* __restrict
 
 size_t k_cosine_topk_scratch_bytes(int Q, int N, int k) {
   size_t nchunks = (size_t)ceil_div(N, CHUNK);
-  return k_cosine_scan_tc_scratch_bytes(768) + round_up((size_t)Q * N * sizeof(float), 256) +
+  return k_cosine_scan_tc_scratch_bytes(768, N) + round_up((size_t)Q * N * sizeof(float), 256) +
          round_up((size_t)Q * nchunks * k * sizeof(float), 256) + round_up((size_t)Q * nchunks * k * sizeof(int32_t), 256);
 }
 
@@ -390,13 +390,9 @@ int k_cosine_topk(const float* queries, const void* corpus, int corpus_dtype, co
   void* tc_scratch = p;
   const float eps = 1e-8f;
   static const bool use_tc = getenv("TUTOR_SCAN_SIMT") == nullptr;  // A/B: the fp32 FFMA2 scan below
-  if (use_tc && Q <= 32 && d % 32 == 0 && d <= 768) {
-    TRY(k_cosine_scan_tc(queries, (const float*)corpus, corpus_inv_norm, Q, N, d, eps, scores, tc_scratch, st));
-    if (k <= 32) topk_chunk_fast_kernel<<<dim3(nchunks, Q), 256, 0, st>>>(scores, N, k, cand_v, cand_i, idx_base);
-    else topk_chunk_kernel<<<dim3(nchunks, Q), 256, 0, st>>>(scores, N, k, cand_v, cand_i, idx_base);
-    KERNEL_LAUNCHED();
-    return k_topk_merge(cand_v, cand_i, Q, nchunks * k, k, out_scores, out_idx, st);
-  }
+  if (use_tc && Q <= 32 && d % 32 == 0 && d <= 768 && k <= 32 && (size_t)ceil_div(N, 128) * 16 <= 200 * 1024)
+    return k_cosine_scan_tc(queries, (const float*)corpus, corpus_inv_norm, Q, N, d, eps, scores, tc_scratch, k, out_scores,
+                            out_idx, idx_base, st);
   const int grid = 148;
   const size_t smem2 = ((size_t)SC_QMAX * d + SC_QMAX + (size_t)8 * SC_STAGES * SC_ROWS * SC_LD) * sizeof(float);
   if (Q <= SC_QMAX && d % SC_K == 0 && smem2 <= 220 * 1024) {

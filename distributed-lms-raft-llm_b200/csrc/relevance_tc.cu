@@ -21,6 +21,7 @@
 //               c_lo x q_hi (N=32), into one of two TMEM accumulator sets
 //   warps 6-9   epilogue: tcgen05.ld, scale by the inverse norms, coalesced stores (32 consecutive rows per query)
 #include <cuda.h>
+#include <math_constants.h>
 
 #include "kernels.h"
 #include "tc_ptx.cuh"
@@ -84,7 +85,7 @@ __global__ void __launch_bounds__(TS_THREADS) cosine_scan_tf32x3_kernel(const __
                                                                       const __grid_constant__ CUtensorMap tmQl,
                                                                       const float* __restrict__ inv_norm,
                                                                       const float* __restrict__ qinv, int Q, int N, int D,
-                                                                      float* __restrict__ scores) {
+                                                                      float* __restrict__ scores, float* __restrict__ gmax) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + TS_STAGES * TS_STAGE_BYTES);
@@ -216,11 +217,28 @@ __global__ void __launch_bounds__(TS_THREADS) cosine_scan_tf32x3_kernel(const __
 #pragma unroll
         for (int q = 0; q < 32; ++q) sum[q] += vm[q] + (vc[q] + vd[q]);  // round-to-nearest adds of the segment sums
       }
-      if (row < N) {
+      // scores out (32 consecutive rows per query: coalesced), and the maximum of this warp's 32 rows per query:
+      // the k best rows of a query lie in at most k such groups, so the top-k only has to look at k x 32 scores
+      float gv[TS_NQ];
 #pragma unroll
-        for (int q = 0; q < TS_NQ; ++q)
-          if (q < Q) scores[(size_t)q * N + row] = sum[q] * qinv[q] * ci;
+      for (int q = 0; q < TS_NQ; ++q) {
+        gv[q] = (row < N && q < Q) ? sum[q] * qinv[q] * ci : -CUDART_INF_F;
+        if (row < N && q < Q) scores[(size_t)q * N + row] = gv[q];
       }
+      // transposing butterfly: 31 shuffles leave the maximum over the warp's 32 rows of query q in lane q
+      // (a warp_max per query would take 160)
+#pragma unroll
+      for (int step = 16; step >= 1; step >>= 1) {
+        const bool upper = (lane & step) != 0;
+#pragma unroll
+        for (int i = 0; i < step; ++i) {
+          const float send = upper ? gv[i] : gv[i + step];
+          const float keep = upper ? gv[i + step] : gv[i];
+          gv[i] = fmaxf(keep, __shfl_xor_sync(0xffffffffu, send, step));
+        }
+      }
+      const float mine = gv[0];
+      if (gmax && lane < Q) gmax[(size_t)lane * ((size_t)ntiles * 4) + (size_t)t * 4 + quad] = mine;
     }
   }
 
@@ -231,16 +249,100 @@ __global__ void __launch_bounds__(TS_THREADS) cosine_scan_tf32x3_kernel(const __
   }
 }
 
+// block-wide arg-max of (value desc, key asc); every thread gets the winner.  red_v / red_k: 8 floats / ints of smem
+__device__ __forceinline__ void block_argmax(float& v, int& key, float* red_v, int* red_k) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, v, o);
+    const int ok = __shfl_xor_sync(0xffffffffu, key, o);
+    if (ov > v || (ov == v && ok < key)) { v = ov; key = ok; }
+  }
+  __syncthreads();  // red_* may still be read from the previous round
+  if (lane == 0) { red_v[warp] = v; red_k[warp] = key; }
+  __syncthreads();
+  v = red_v[0]; key = red_k[0];
+#pragma unroll
+  for (int w = 1; w < 8; ++w)
+    if (red_v[w] > v || (red_v[w] == v && red_k[w] < key)) { v = red_v[w]; key = red_k[w]; }
+}
+
+// Exact top-k of one query from the 32-row group maxima the scan left behind: (1) the k groups with the largest maxima
+// (ties to the lower group, i.e. the lower rows), (2) the k best of their k x 32 scores (ties to the lower row).
+// grid (Q), 256 threads, G floats of dynamic shared memory.  k <= 32.
+__global__ void __launch_bounds__(256) topk_from_groups_kernel(const float* __restrict__ scores,
+                                                              const float* __restrict__ gmax, int N, int G, int k,
+                                                              float* __restrict__ out_v, int32_t* __restrict__ out_i,
+                                                              int idx_base) {
+  extern __shared__ float sg[];  // [G] group maxima of this query
+  __shared__ float red_v[8];
+  __shared__ int red_k[8];
+  __shared__ int sel[32];
+  const int q = blockIdx.x, tid = threadIdx.x;
+  const int ngroups = (N + 31) / 32;  // groups past this are padding of the last tile
+  for (int g = tid; g < G; g += 256) sg[g] = g < ngroups ? gmax[(size_t)q * G + g] : -CUDART_INF_F;
+  __syncthreads();
+  auto rescan = [&](float& bv, int& bk) {
+    bv = -CUDART_INF_F; bk = 0x7fffffff;
+    for (int g = tid; g < G; g += 256) {
+      const float v = sg[g];
+      if (v > bv) { bv = v; bk = g; }  // ascending g: strict > keeps the lowest group
+    }
+  };
+  float bv; int bk;
+  rescan(bv, bk);
+  for (int round = 0; round < k; ++round) {
+    float v = bv; int key = bk;
+    block_argmax(v, key, red_v, red_k);
+    if (tid == 0) sel[round] = (v == -CUDART_INF_F) ? -1 : key;
+    if (key != 0x7fffffff && (key & 255) == tid) {  // the owner drops the winner and refreshes its cached best
+      sg[key] = -CUDART_INF_F;
+      rescan(bv, bk);
+    }
+  }
+  __syncthreads();
+  // candidates: up to k x 32 rows, four per thread
+  float cv[4]; int ck[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int c = tid + 256 * j;
+    const int g = c < k * 32 ? sel[c >> 5] : -1;
+    const int row = g >= 0 ? g * 32 + (c & 31) : N;
+    cv[j] = row < N ? scores[(size_t)q * N + row] : -CUDART_INF_F;
+    ck[j] = row < N ? row : 0x7fffffff;
+  }
+  for (int round = 0; round < k; ++round) {
+    float v = -CUDART_INF_F; int key = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (ck[j] != 0x7fffffff && (cv[j] > v || (cv[j] == v && ck[j] < key))) { v = cv[j]; key = ck[j]; }
+    block_argmax(v, key, red_v, red_k);
+    if (tid == 0) {
+      out_v[(size_t)q * k + round] = key != 0x7fffffff ? v : -CUDART_INF_F;
+      out_i[(size_t)q * k + round] = key != 0x7fffffff ? idx_base + key : -1;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (ck[j] == key) ck[j] = 0x7fffffff;  // rows are unique
+  }
+}
+
 }  // namespace
 
-size_t k_cosine_scan_tc_scratch_bytes(int d) { return round_up((size_t)2 * TS_NQ * d * sizeof(float) + TS_NQ * sizeof(float), 256); }
+size_t k_cosine_scan_tc_scratch_bytes(int d, int N) {
+  return round_up((size_t)2 * TS_NQ * d * sizeof(float) + TS_NQ * sizeof(float), 256) +
+         round_up((size_t)TS_NQ * ceil_div(N, TS_BM) * 4 * sizeof(float), 256);  // split queries + group maxima
+}
 
 int k_cosine_scan_tc(const float* queries, const float* corpus, const float* corpus_inv_norm, int Q, int N, int d,
-                     float eps, float* scores, void* scratch, cudaStream_t st) {
+                     float eps, float* scores, void* scratch, int k, float* out_scores, int32_t* out_idx, int idx_base,
+                     cudaStream_t st) {
   ARG_CHECK(Q >= 1 && Q <= TS_NQ && d % TS_BK == 0 && N >= 1, "cosine_scan_tc: unsupported Q=%d d=%d N=%d", Q, d, N);
   float* q_hi = reinterpret_cast<float*>(scratch);
   float* q_lo = q_hi + (size_t)TS_NQ * d;
   float* qinv = q_lo + (size_t)TS_NQ * d;
+  float* gmax = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) +
+                                         round_up((size_t)2 * TS_NQ * d * sizeof(float) + TS_NQ * sizeof(float), 256));
   split_queries_kernel<<<TS_NQ, 256, 0, st>>>(queries, Q, d, eps, q_hi, q_lo, qinv);
   KERNEL_LAUNCHED();
   CUtensorMap tc, th, tl;
@@ -253,7 +355,13 @@ int k_cosine_scan_tc(const float* queries, const float* corpus, const float* cor
   CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const int ntiles = ceil_div(N, TS_BM);
   cosine_scan_tf32x3_kernel<<<ntiles < sms ? ntiles : sms, TS_THREADS, TS_SMEM, st>>>(tc, th, tl, corpus_inv_norm, qinv, Q, N, d,
-                                                                                scores);
+                                                                                scores, gmax);
+  KERNEL_LAUNCHED();
+  // top-k straight from the group maxima (k <= 32, and the maxima of one query must fit in shared memory)
+  const int G = ntiles * 4;
+  ARG_CHECK(k >= 1 && k <= 32 && (size_t)G * 4 <= 200 * 1024, "cosine_scan_tc: k=%d / %d row groups unsupported", k, G);
+  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(topk_from_groups_kernel), 200 * 1024));
+  topk_from_groups_kernel<<<Q, 256, (size_t)G * 4, st>>>(scores, gmax, N, G, k, out_scores, out_idx, idx_base);
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }
