@@ -981,9 +981,18 @@ int k_attn_decode_splits(int B, int H, int len_hint, int num_sms) {
   // fewer (b,h) streams than SMs: split until every SM has work
   int n = 1;
   while (n < 8 && B * H * n < num_sms && len_hint / (2 * n) >= 64) n *= 2;
-  // more streams than SMs: one CTA per (b,h).  768 equal CTAs leave 28 of 148 SMs with six streams and 120 with
-  // five, but cutting the key range to even that out measured slower with every kernel flavour (see use_mma_decode)
-  return n;
+  // more streams than SMs: aim at one full wave of the ring kernels' 6 CTAs per SM.  B*H = 768 (GPT-2 small, B = 64):
+  // one CTA per (b,h) is already 5.2 per SM and every split measured slower (see use_mma_decode).  B*H = 320 (GPT-2
+  // large, B = 16) leaves the SMs a third empty: 3 key-range splits of the register kernel (960 CTAs, last-arriver merge)
+  // took the decode forward from 1.91 to 1.74 ms, while 2 / 4 / 5 / 6 / 8 splits gave 1.88 / 1.94 / 1.90 / 1.92 / 1.99 ms
+  // and the tensor-core ring kernel with 3 splits 1.97 ms.
+  int best = 1;
+  long best_gap = labs((long)B * H - 6L * num_sms);
+  for (int c = 2; c <= 4 && len_hint / c >= 128; ++c) {
+    const long gap = labs((long)B * H * c - 6L * num_sms);
+    if (gap < best_gap) { best_gap = gap; best = c; }
+  }
+  return best;
 }
 size_t k_attn_decode_scratch_bytes(int B, int H) { return (size_t)B * H * (8 * 66 * sizeof(float) + sizeof(int)); }
 
