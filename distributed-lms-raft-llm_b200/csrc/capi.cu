@@ -61,11 +61,18 @@ int tutor_require_device(int device) {
     return TUTOR_ERR_CUDA;
   }
   ARG_CHECK(device >= 0 && device < n, "device %d out of range (have %d)", device, n);
-  cudaDeviceProp p;
-  CUDA_TRY(cudaGetDeviceProperties(&p, device));
-  if (p.major != 10) {
-    tutor_set_error("device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, p.major, p.minor);
-    return TUTOR_ERR_CUDA;
+  // the architecture check is remembered per device: cudaGetDeviceProperties costs ~2 ms a call, which was a third of a
+  // host-path relevance batch (tutor_cosine_pairs_host comes through here on every request)
+  static std::atomic<int> checked[64];
+  if (device >= 64 || checked[device].load(std::memory_order_relaxed) == 0) {
+    int major = 0, minor = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+    CUDA_TRY(cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, device));
+    if (major != 10) {
+      tutor_set_error("device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, major, minor);
+      return TUTOR_ERR_CUDA;
+    }
+    if (device < 64) checked[device].store(1, std::memory_order_relaxed);
   }
   CUDA_TRY(cudaSetDevice(device));
   return TUTOR_OK;

@@ -45,3 +45,28 @@ def test_shard_bounds_partition(pkg, n, ws):
 def test_relevance_decision_boundary(pkg):
     assert pkg.is_relevant(0.6) and pkg.is_relevant(0.61) and not pkg.is_relevant(0.5999)
     assert pkg.SIMILARITY_THRESHOLD == 0.6
+
+
+def test_assignment_index_chunking_frames_every_window():
+    """serving.AssignmentIndex.chunk_ids (no GPU): [CLS] + <= chunk_tokens-2 word pieces + [SEP] windows that cover the
+    whole text in order; chunk 0 equals the reference's truncated tokenisation (REF/lms_server.py:98)."""
+    import importlib
+
+    import torch
+    serving = importlib.import_module("distributed-lms-raft-llm_b200.serving")
+
+    class Tok:
+        def __call__(self, text, truncation=True, max_length=512, **kw):
+            body = [1000 + int(w) for w in text.split()]
+            if truncation:
+                body = body[:max_length - 2]
+            return {"input_ids": torch.tensor([[101] + body + [102]], dtype=torch.int64)}
+
+    index = serving.AssignmentIndex(model=None, tokenizer=Tok(), chunk_tokens=10)
+    text = " ".join(str(i) for i in range(21))  # 21 word pieces -> windows of 8, 8, 5
+    chunks = index.chunk_ids(text)
+    assert [c.numel() for c in chunks] == [10, 10, 7]
+    assert all(int(c[0]) == 101 and int(c[-1]) == 102 for c in chunks)
+    assert torch.cat([c[1:-1] for c in chunks]).tolist() == [1000 + i for i in range(21)]
+    assert torch.equal(chunks[0], Tok()(text, truncation=True, max_length=10)["input_ids"][0])
+    assert [c.numel() for c in index.chunk_ids("7")] == [3]
