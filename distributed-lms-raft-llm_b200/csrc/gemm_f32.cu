@@ -3,6 +3,8 @@
 // transposed once at load; BERT nn.Linear weights and the tied LM head already are [out,in].
 //   M <= 8  : weight-streaming GEMV, one warp per output column, 128-bit coalesced loads (HBM-bound)
 //   M  > 8  : 64x64x16 register-tiled SIMT GEMM (fp32 FMA only - TF32 would break the 1e-3 logit gate)
+#include <cstdlib>
+
 #include "kernels.h"
 
 namespace {
@@ -142,6 +144,15 @@ __global__ void __launch_bounds__(256) gemv_f32_ln_kernel(const float* __restric
   }
 }
 
+// 16-byte read-only load the compiler may not move: the kernels below want their weights requested BEFORE
+// griddepcontrol.wait, and a plain load of a const __restrict__ pointer gets sunk below it (checked in SASS: every
+// LDG.CONSTANT sat after ACQBULK) - volatile asm statements keep their order relative to the wait.
+__device__ __forceinline__ float4 ldg_pinned(const float* p) {
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
 // Decode GEMV for one or two rows (the reference's own configuration is batch 1) built for the dependent-launch
 // chain: the whole weight row of this warp's output column - NV float4 per lane - and the LayerNorm parameters are
 // loaded into registers BEFORE griddepcontrol.wait (weights never change), so what remains on the critical path after
@@ -163,10 +174,10 @@ __global__ void __launch_bounds__(256) gemv_f32_reg_kernel(const float* __restri
   const float* w = W + (size_t)min(n, N - 1) * K + lane * 4;
   float4 wv[NV], gv[LN ? NV : 1], bv[LN ? NV : 1];
 #pragma unroll
-  for (int j = 0; j < NV; ++j) wv[j] = load4(w + j * 128);
+  for (int j = 0; j < NV; ++j) wv[j] = ldg_pinned(w + j * 128);
   if (LN) {
 #pragma unroll
-    for (int j = 0; j < NV; ++j) { gv[j] = load4(gamma + lane * 4 + j * 128); bv[j] = load4(beta + lane * 4 + j * 128); }
+    for (int j = 0; j < NV; ++j) { gv[j] = ldg_pinned(gamma + lane * 4 + j * 128); bv[j] = ldg_pinned(beta + lane * 4 + j * 128); }
   }
   // (hoisting the epilogue's bias / residual loads up here measured slower: 381 vs 336 us per decode forward)
   pdl_wait();
@@ -213,10 +224,105 @@ __global__ void __launch_bounds__(256) gemv_f32_reg_kernel(const float* __restri
   }
 }
 
+// Two shapes of the batch-1 chain do not fill the machine with one warp per output column:
+//  * mlp c_proj (N = 768, K = 3072): 96 CTAs on 148 SMs, 24 float4 of weights per lane.  WPC = 2 warps share a column
+//    (half of K each, partial sums meet in shared memory): 192 CTAs, 12 float4 per lane.
+//  * ln_2 + c_fc (N = 3072, K = 768): 384 CTAs of which 296 are resident - a second wave whose weight loads overlap
+//    nothing.  NC = 2 columns per warp: 192 CTAs, and LayerNorm is computed once for both columns.
+template <int MB, int NV, bool LN, int NC, int WPC>
+__global__ void __launch_bounds__(256) gemv_f32_reg2_kernel(const float* __restrict__ X, const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, float eps,
+                                                             const float* __restrict__ W, int N, GemmEpilogue epi) {
+  constexpr int K = NV * 128, NVW = NV / WPC;  // float4 per lane of one column that this warp owns
+  static_assert(NV % WPC == 0 && (WPC == 1 || !LN), "LayerNorm needs the whole row in one warp");
+  __shared__ float part[8][MB * NC];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int col0 = (blockIdx.x * (8 / WPC) + warp / WPC) * NC;  // first of this warp's NC columns
+  const int j0 = (warp % WPC) * NVW;                            // first float4 group of this warp's K range
+  pdl_launch_dependents();
+  float4 wv[NC][NVW], gv[LN ? NV : 1], bv[LN ? NV : 1];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    const float* w = W + (size_t)min(col0 + c, N - 1) * K + lane * 4;
+#pragma unroll
+    for (int j = 0; j < NVW; ++j) wv[c][j] = ldg_pinned(w + (j0 + j) * 128);
+  }
+  if (LN) {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) { gv[j] = ldg_pinned(gamma + lane * 4 + j * 128); bv[j] = ldg_pinned(beta + lane * 4 + j * 128); }
+  }
+  pdl_wait();
+#pragma unroll
+  for (int m = 0; m < MB; ++m) {
+    const float* xr = X + (size_t)m * K + lane * 4;
+    float4 xv[NVW];
+#pragma unroll
+    for (int j = 0; j < NVW; ++j) xv[j] = __ldcg((const float4*)(xr + (j0 + j) * 128));  // (.cg: see gemv_f32_reg_kernel)
+    if (LN) {
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < NVW; ++j) s += (xv[j].x + xv[j].y) + (xv[j].z + xv[j].w);
+      const float mean = warp_sum(s) / K;
+      float q = 0.f;
+#pragma unroll
+      for (int j = 0; j < NVW; ++j) {
+        const float a = xv[j].x - mean, b = xv[j].y - mean, c = xv[j].z - mean, d = xv[j].w - mean;
+        q += (a * a + b * b) + (c * c + d * d);
+      }
+      const float rstd = 1.0f / sqrtf(warp_sum(q) / K + eps);
+#pragma unroll
+      for (int j = 0; j < NVW; ++j) {
+        xv[j].x = (xv[j].x - mean) * rstd * gv[j].x + bv[j].x; xv[j].y = (xv[j].y - mean) * rstd * gv[j].y + bv[j].y;
+        xv[j].z = (xv[j].z - mean) * rstd * gv[j].z + bv[j].z; xv[j].w = (xv[j].w - mean) * rstd * gv[j].w + bv[j].w;
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      float acc = 0.f;
+#pragma unroll
+      for (int j = 0; j < NVW; ++j)
+        acc += wv[c][j].x * xv[j].x + wv[c][j].y * xv[j].y + wv[c][j].z * xv[j].z + wv[c][j].w * xv[j].w;
+      const float s = warp_sum(acc);
+      if (WPC == 1) {
+        if (lane == 0 && col0 + c < N) epilogue_store(epi, m, col0 + c, s);
+      } else if (lane == 0) {
+        part[warp][m * NC + c] = s;
+      }
+    }
+  }
+  if (WPC > 1) {
+    __syncthreads();
+    if (warp % WPC == 0 && lane < MB * NC) {
+      float s = 0.f;
+#pragma unroll
+      for (int h = 0; h < WPC; ++h) s += part[warp + h][lane];  // fixed order: deterministic
+      const int m = lane / NC, c = lane % NC;
+      if (col0 + c < N) epilogue_store(epi, m, col0 + c, s);
+    }
+  }
+}
+
 template <int MB, bool LN>
 int launch_gemv_reg(const float* X, const float* gamma, const float* beta, float eps, const float* W, int N, int K,
                     const GemmEpilogue& epi, float* xn_out, cudaStream_t st) {
-  const dim3 grid(ceil_div(N, 8)), block(256);
+  const dim3 block(256);
+  static const bool plain = getenv("TUTOR_GEMV_PLAIN") != nullptr;  // A/B: one warp per column everywhere
+  if constexpr (LN) {
+    if (!plain && K == 768 && N >= 2048 && !xn_out) {  // ln_2 + c_fc: two columns per warp
+      CUDA_TRY(tutor_launch(gemv_f32_reg2_kernel<MB, 6, true, 2, 1>, dim3(ceil_div(N, 16)), block, 0, st, X, gamma, beta, eps,
+                            W, N, epi));
+      KERNEL_LAUNCHED();
+      return TUTOR_OK;
+    }
+  } else {
+    if (!plain && K == 3072) {  // mlp c_proj: two warps per column
+      CUDA_TRY(tutor_launch(gemv_f32_reg2_kernel<MB, 24, false, 1, 2>, dim3(ceil_div(N, 4)), block, 0, st, X, gamma, beta, eps,
+                            W, N, epi));
+      KERNEL_LAUNCHED();
+      return TUTOR_OK;
+    }
+  }
+  const dim3 grid(ceil_div(N, 8));
 #define GEMV_REG(nv)                                                                                                 \
   case nv:                                                                                                           \
     CUDA_TRY(tutor_launch(gemv_f32_reg_kernel<MB, nv, LN>, grid, block, 0, st, X, gamma, beta, eps, W, N, epi, xn_out)); \
