@@ -5,5 +5,3 @@ timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --mas
 echo "bench exit $?"; grep "^{" gpurun_out/bench_n$N.log | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('N', d['n_gpus'], 'value', round(d['value']), 'e2e', round(d['e2e']['value']), 'ms', round(d['ms_per_step'],2), d['clocks'])"
 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 tools/multi_gpu_check.py > gpurun_out/relevance_n$N.log 2>&1
 echo "relevance exit $?"; tail -2 gpurun_out/relevance_n$N.log
-timeout 600 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.log 2>&1
-grep "^{" gpurun_out/bench.log | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('N1 value', round(d['value'])); print(d.get('extras'))"
