@@ -14,7 +14,10 @@ def corpus(n, d=768, seed=3):
     return c / c.norm(dim=1, keepdim=True)
 
 
-@pytest.mark.parametrize("N,Q,k,d", [(50_000, 32, 10, 768), (4097, 3, 5, 768), (7, 2, 10, 128), (20_000, 1, 1, 128)])
+# the last two leave the tensor-core path: more than 32 queries (SIMT scan, register-row kernel) and k > 32 (SIMT scan,
+# block-wide chunk selection)
+@pytest.mark.parametrize("N,Q,k,d", [(50_000, 32, 10, 768), (4097, 3, 5, 768), (7, 2, 10, 128), (20_000, 1, 1, 128),
+                                     (3000, 40, 5, 768), (5000, 4, 40, 128), (9000, 32, 32, 768)])
 def test_topk_matches_oracle(pkg, N, Q, k, d):
     c = corpus(N, d)
     q = torch.randn(Q, d, generator=torch.Generator().manual_seed(9)) * 3
