@@ -10,6 +10,8 @@
 #include <string>
 #include <vector>
 
+#include <cstdlib>
+
 #include "engine_common.h"
 
 struct BertLayer {
@@ -33,13 +35,25 @@ struct tutor_bert {
   bf16* xb = nullptr;
   void *q = nullptr, *kbuf = nullptr, *vbuf = nullptr, *att = nullptr, *hbuf = nullptr;
   int Bcap = 0;
+  // One captured CUDA graph per (B, T) shape seen twice: a forward is ~85 launches, and for a single query the host
+  // side of those launches (tensor-map encoding + cudaLaunchKernelEx) was the whole 1.0 ms of its latency.
+  struct ShapeGraph { cudaGraphExec_t exec = nullptr; uint64_t kernels = 0; int seen = 0; };
+  std::map<std::pair<int, int>, ShapeGraph> graphs;
+  bool use_graph = true;  // TUTOR_BERT_NO_GRAPH=1: eager launches (A/B measurements)
   size_t esz() const { return dt == DT_F32 ? 4 : 2; }
 };
 
 namespace {
 
+void drop_graphs(tutor_bert* e) {
+  for (auto& g : e->graphs)
+    if (g.second.exec) cudaGraphExecDestroy(g.second.exec);
+  e->graphs.clear();
+}
+
 int ensure_capacity(tutor_bert* e, int B, int T) {
   const int M = B * T;
+  if (M > e->Mcap || B > e->Bcap) drop_graphs(e);  // the captured launches hold the old buffer addresses
   if (M > e->Mcap) {
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     dev_free(e->ids); dev_free(e->x); dev_free(e->tmp); dev_free(e->xb); dev_free(e->q); dev_free(e->kbuf);
@@ -104,6 +118,36 @@ int forward(tutor_bert* e, int B, int T) {
   return k_meanpool(e->x, e->emb, B, T, d, st);  // unmasked mean over all T positions (REF/lms_server.py:101)
 }
 
+// forward() through the shape's captured graph: the first call of a shape runs eagerly (it also sets every kernel
+// attribute), the second is captured and replayed from then on.  At most 64 shapes are kept.
+int run_forward(tutor_bert* e, int B, int T) {
+  if (!e->use_graph) return forward(e, B, T);
+  if (e->graphs.size() > 64) drop_graphs(e);
+  tutor_bert::ShapeGraph& sg = e->graphs[{B, T}];
+  if (sg.exec) {
+    CUDA_TRY(cudaGraphLaunch(sg.exec, e->stream));
+    tutor_count_launches(sg.kernels);
+    return TUTOR_OK;
+  }
+  if (sg.seen++ == 0) return forward(e, B, T);
+  cudaGraph_t g = nullptr;
+  const uint64_t before = tutor_launch_count();
+  CUDA_TRY(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+  const int rc = forward(e, B, T);
+  const cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
+  const uint64_t n = tutor_launch_count() - before;
+  tutor_count_launches((uint64_t)0 - n);  // captured launches did not run
+  if (rc != TUTOR_OK) { if (g) cudaGraphDestroy(g); return rc; }
+  if (ce != cudaSuccess) return tutor_cuda_fail(ce, "cudaStreamEndCapture", __FILE__, __LINE__);
+  const cudaError_t ci = cudaGraphInstantiate(&sg.exec, g, 0);
+  cudaGraphDestroy(g);
+  if (ci != cudaSuccess) { sg.exec = nullptr; return tutor_cuda_fail(ci, "cudaGraphInstantiate", __FILE__, __LINE__); }
+  sg.kernels = n;
+  CUDA_TRY(cudaGraphLaunch(sg.exec, e->stream));
+  tutor_count_launches(sg.kernels);
+  return TUTOR_OK;
+}
+
 // copy a [rows, cols] fp32 host block into rows [row0, row0+rows) of a device matrix of dtype dt
 int upload_rows(void* base, int64_t row0, const float* src, int64_t rows, int64_t cols, int dt) {
   void* tmp = nullptr;
@@ -139,6 +183,7 @@ int tutor_bert_create(const tutor_bert_config* cfg, int device, tutor_bert_t** o
   e->d = cfg->hidden_size; e->H = cfg->num_attention_heads; e->L = cfg->num_hidden_layers;
   e->F = cfg->intermediate_size; e->V = cfg->vocab_size; e->P = cfg->max_position_embeddings;
   e->layers.resize(e->L);
+  e->use_graph = getenv("TUTOR_BERT_NO_GRAPH") == nullptr;
   if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) {
     int rc = tutor_cuda_fail(cudaGetLastError(), "bert_create", __FILE__, __LINE__);
     delete e;
@@ -152,6 +197,7 @@ void tutor_bert_destroy(tutor_bert_t* e) {
   if (!e) return;
   cudaSetDevice(e->device);
   cudaStreamSynchronize(e->stream);
+  drop_graphs(e);
   dev_free(e->word); dev_free(e->pos); dev_free(e->type0); dev_free(e->emb_g); dev_free(e->emb_b);
   for (auto& l : e->layers) {
     for (Linear* w : {&l.qkv, &l.attn_out, &l.inter, &l.out}) { dev_free(w->w); dev_free(w->b); }
@@ -271,7 +317,7 @@ int tutor_bert_embed(tutor_bert_t* e, const int64_t* ids_host, int B, int T, flo
     tmp[i] = (int32_t)ids_host[i];
   }
   CUDA_TRY(cudaMemcpyAsync(e->ids, tmp.data(), tmp.size() * 4, cudaMemcpyHostToDevice, e->stream));
-  TRY(forward(e, B, T));
+  TRY(run_forward(e, B, T));
   CUDA_TRY(cudaMemcpyAsync(emb_host, e->emb, (size_t)B * e->d * 4, cudaMemcpyDeviceToHost, e->stream));
   if (hidden_host)
     CUDA_TRY(cudaMemcpyAsync(hidden_host, e->x, (size_t)B * T * e->d * 4, cudaMemcpyDeviceToHost, e->stream));
@@ -287,7 +333,7 @@ int tutor_bert_embed_dev(tutor_bert_t* e, const int32_t* ids_dev, int B, int T, 
   TRY(tutor_bert_check_loaded(e));
   TRY(ensure_capacity(e, B, T));
   CUDA_TRY(cudaMemcpyAsync(e->ids, ids_dev, (size_t)B * T * 4, cudaMemcpyDeviceToDevice, e->stream));
-  TRY(forward(e, B, T));
+  TRY(run_forward(e, B, T));
   CUDA_TRY(cudaMemcpyAsync(emb_dev, e->emb, (size_t)B * e->d * 4, cudaMemcpyDeviceToDevice, e->stream));
   CUDA_TRY(cudaStreamSynchronize(e->stream));
   return TUTOR_OK;

@@ -969,7 +969,11 @@ int k_gemm_bf16(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpi
   ARG_CHECK(K % BK == 0, "gemm_bf16: K=%d must be a multiple of %d", K, BK);
   if (M == 0 || N == 0) return TUTOR_OK;
   ArgmaxArgs am{};
-  if (M <= 128) return launch_swapped<EPI_SWAPPED>(W, N, A, M, K, epi, am, st);
+  // few rows: the weight matrix as the 128-row UMMA operand, the rows as its N dimension.  Above TUTOR_SWAP_MAX_M rows
+  // (default 32) the row-major kernel's single row tile is faster: a 128-token BERT query took 2.7 ms through the
+  // swapped kernel's per-element epilogue.
+  static const int swap_max = getenv("TUTOR_SWAP_MAX_M") ? atoi(getenv("TUTOR_SWAP_MAX_M")) : 32;
+  if (M <= (swap_max < 128 ? swap_max : 128)) return launch_swapped<EPI_SWAPPED>(W, N, A, M, K, epi, am, st);
   // 128x256 tiles halve the operand bytes per FLOP of 128x128 ones (the 128x128 kernel measured L2-bandwidth
   // bound: 32 KB of operands per 4 MMAs = 6.2 TB/s at 410 TFLOP/s); two 97 KB CTAs still share an SM
   static const bool wide = getenv("TUTOR_GEMM_BN128") == nullptr;
