@@ -213,6 +213,9 @@ int tutor_bert_load_tensor(tutor_bert_t* e, const char* name, const float* data,
   ARG_CHECK(e && name && data && shape, "bert_load_tensor: null argument");
   std::lock_guard<std::mutex> lock(e->mu);
   CUDA_TRY(cudaSetDevice(e->device));
+  // weight buffers are about to be replaced: captured forwards hold their addresses
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  drop_graphs(e);
   std::string n(name);
   if (n.rfind("bert.", 0) == 0) n = n.substr(5);
   if (n.rfind("pooler.", 0) == 0 || n == "embeddings.position_ids" || n == "embeddings.token_type_ids")

@@ -69,6 +69,10 @@ struct tutor_gpt2 {
   int* h_counters = nullptr;  // pinned
   // current generation
   int cur_B = 0, cur_T = 0, cur_total = 0;
+  // prompt rows the decode attention may stream ahead of its programmatic-launch wait.  The value is baked into the
+  // captured graph, so it is quantised to what the kernels can use (whole chunks, at most the ring depth = 128 rows)
+  // and is part of the graph key: a shorter prompt after a longer one re-captures instead of replaying a stale bound.
+  int safe_rows = 0;
   float cur_penalty = 1.f;
   int cur_eos = -1, cur_pad = 0;
   // decode graph
@@ -190,7 +194,7 @@ int forward_decode_fused(tutor_gpt2* e, int lane, int b0, int B) {
     TRY(k_gemm_bf16_splitk(xn, (const bf16*)w.qkv.w, B, 3 * d, d, ks, partial, st));
     TRY(k_attn_decode_fused(partial, ks, w.qkv.b, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
                             e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, npad,
-                            e->cur_T, (e->cur_T + e->cur_total) / 2, st));
+                            e->safe_rows, (e->cur_T + e->cur_total) / 2, st));
     ks = k_pick_splitk(d, d, e->num_sms);
     TRY(k_gemm_bf16_splitk(att, (const bf16*)w.proj.w, B, d, d, ks, partial, st));
     TRY(k_reduce_bias_residual_ln(partial, ks, B, d, w.proj.b, x, w.ln2_g, w.ln2_b, eps, nullptr, xn, st));
@@ -261,7 +265,7 @@ int forward_decode_cluster(tutor_gpt2* e, int lane, int b0, int B) {
     if (!strchr(skip, 'a'))
       TRY(k_attn_decode_fused(partial, ks_qkv, w.qkv.b, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
                               e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, npad,
-                              e->cur_T, (e->cur_T + e->cur_total) / 2, st));
+                              e->safe_rows, (e->cur_T + e->cur_total) / 2, st));
     if (!strchr(skip, 'p'))
       TRY(k_gemm_resid_stats(att, (const bf16*)w.proj.w, w.proj.b, B, d, d, ks_proj, bn_res, x, stats, st));
     if (!strchr(skip, 'f'))
@@ -332,7 +336,9 @@ int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
         const size_t n = (size_t)k_pick_splitk(s[0], s[1], e->num_sms) * nb * s[0];
         if (n > elems) elems = n;
       }
-      const size_t qkv_elems = (size_t)decode_plan(e, nb).ks_qkv * nb * 3 * d;  // the cluster path's c_attn partials
+      // the cluster path's c_attn partials: a live batch below capacity has fewer batch tiles and may split K deeper
+      // than decode_plan(nb) does, so size for the deepest split (8) of the full capacity
+      const size_t qkv_elems = (size_t)8 * nb * 3 * d;
       if (qkv_elems > elems) elems = qkv_elems;
       e->partial_lane_elems = elems;  // every lane slice can hold the whole batch (lanes only ever hold a part of it)
       TRY(dev_alloc(&e->partial, tutor_gpt2::MAX_LANES * elems * sizeof(float)));
@@ -400,6 +406,9 @@ int start_generation(tutor_gpt2* e, int B, int T, int total, float penalty, int 
   if (const char* sv = getenv("TUTOR_ATTN_SPLITS")) splits = atoi(sv) < 1 ? 1 : (atoi(sv) > 8 ? 8 : atoi(sv));
   if (splits != e->attn_splits) drop_graph(e);
   e->attn_splits = splits;
+  const int safe = (T < 128 ? T : 128) / 64 * 64;
+  if (safe != e->safe_rows) drop_graph(e);
+  e->safe_rows = safe;
   e->cur_B = B; e->cur_T = T; e->cur_total = total; e->cur_penalty = penalty; e->cur_eos = eos; e->cur_pad = pad;
   cudaStream_t st = e->stream;
   e->h_counters[0] = T; e->h_counters[1] = 0;
@@ -564,6 +573,9 @@ int tutor_gpt2_load_tensor(tutor_gpt2_t* e, const char* name, const float* data,
   ARG_CHECK(e && name && data && shape, "gpt2_load_tensor: null argument");
   std::lock_guard<std::mutex> lock(e->mu);
   CUDA_TRY(cudaSetDevice(e->device));
+  // weight buffers are about to be replaced: the captured decode step holds their addresses
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  drop_graph(e);
   const std::string full(name);
   if (full == "lm_head.weight") return TUTOR_OK;  // tied to wte
   NameParts p = split_name(full);

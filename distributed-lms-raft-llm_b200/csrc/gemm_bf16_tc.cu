@@ -247,7 +247,7 @@ __global__ void __launch_bounds__(EPI == EPI_ROWMAJOR ? NTHREADS_WIDE : NTHREADS
           if (c0 + i >= BN) break;  // BN = 16: only half of the 32-column load is real
           const int b = b_row0 + c0 + i;
           float val = v[i];
-          if (b < am.B && am.penalty != 1.0f) {
+          if (b < am.B && row < am.V && am.penalty != 1.0f) {
             // 32 lanes = 32 consecutive vocabulary rows = one word of the seen-bitmap
             uint32_t w = am.seen[(size_t)b * am.seen_words + (row >> 5)];
             if ((w >> (row & 31)) & 1u) val = (val < 0.f) ? val * am.penalty : val / am.penalty;

@@ -24,6 +24,7 @@ class B200GPT2LMHeadModel:
         self.config = config
         self.dtype = dtype
         self.device_index = device
+        self.n_positions = int(config.n_positions)
         self.generation_config = SimpleNamespace(max_length=20, eos_token_id=getattr(config, "eos_token_id", 50256),
                                                  pad_token_id=getattr(config, "pad_token_id", None))
         cfg = _lib.Gpt2Config(config.n_layer, config.n_head, config.n_embd, config.vocab_size, config.n_positions,

@@ -165,7 +165,18 @@ class BatchingModel:
                 while len(self._queue) < self.max_batch and time.monotonic() < deadline and not self._stop:
                     self._cv.wait(timeout=max(0.0, deadline - time.monotonic()))
                 key = self._queue[0]["key"]
-                batch = [r for r in self._queue if r["key"] == key][:self.max_batch]
+                # a padded batch runs max(T) + max(new) positions for every row: admit a request only while that
+                # stays inside the model's position table, so rows that are legal on their own never fail together
+                limit = getattr(self.engine, "n_positions", None)
+                batch, bt, bn = [], 0, 0
+                for r in self._queue:
+                    if r["key"] != key or len(batch) >= self.max_batch:
+                        continue
+                    t, n = max(bt, r["ids"].numel()), max(bn, r["new"])
+                    if batch and limit is not None and t + n > limit + 1:
+                        continue
+                    batch.append(r)
+                    bt, bn = t, n
                 self._queue = [r for r in self._queue if all(r is not b for b in batch)]
             try:
                 pen, eos, pad = key
