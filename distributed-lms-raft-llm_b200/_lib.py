@@ -49,6 +49,7 @@ SIGNATURES = {
     "tutor_gpt2_logits": (c_int, [c_void_p, c_void_p]),
     "tutor_gpt2_decode_bytes": (C.c_double, [c_void_p, c_int, c_int]),
     "tutor_gpt2_stream": (c_void_p, [c_void_p]),
+    "tutor_gpt2_decode_trace": (c_int, [c_void_p, c_int, c_void_p, c_int]),
     "tutor_bert_create": (c_int, [P(BertConfig), c_int, P(c_void_p)]),
     "tutor_bert_destroy": (None, [c_void_p]),
     "tutor_bert_load_tensor": (c_int, [c_void_p, c_char_p, c_void_p, P(C.c_int64), c_int]),

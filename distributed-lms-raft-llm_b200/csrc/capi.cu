@@ -111,6 +111,37 @@ int upload_matrix(void** dst, const float* src, int64_t rows, int64_t cols, bool
   return TUTOR_OK;
 }
 
+// LayerNorm folded into the Conv1D that consumes it (decode_mega.cu): src is the Conv1D weight [K, N] ([in, out]),
+// gamma / beta the LayerNorm parameters [K].  Uploads W'[n,k] = bf16(gamma[k] * src[k,n]) as [N, K], s[n] = sum_k W'[n,k]
+// (of the rounded values, so that subtracting mean * s removes exactly what the tensor core accumulated) and
+// c[n] = sum_k beta[k] * src[k,n].
+int upload_ln_folded(void** dst_w, float** dst_s, float** dst_c, const float* src, int64_t K, int64_t N, const float* gamma,
+                     const float* beta) {
+  std::vector<uint16_t> w((size_t)N * K);
+  std::vector<double> s(N, 0.0), c(N, 0.0);
+  constexpr int64_t TB = 32;
+  for (int64_t k0 = 0; k0 < K; k0 += TB)
+    for (int64_t n0 = 0; n0 < N; n0 += TB)
+      for (int64_t k = k0; k < K && k < k0 + TB; ++k)
+        for (int64_t n = n0; n < N && n < n0 + TB; ++n) {
+          const float v = src[(size_t)k * N + n];
+          const uint16_t h = f32_to_bf16_rne(gamma[k] * v);
+          w[(size_t)n * K + k] = h;
+          const uint32_t bits = (uint32_t)h << 16;
+          float f;
+          memcpy(&f, &bits, 4);
+          s[n] += f;
+          c[n] += (double)beta[k] * v;
+        }
+  std::vector<float> sf(N), cf(N);
+  for (int64_t n = 0; n < N; ++n) { sf[n] = (float)s[n]; cf[n] = (float)c[n]; }
+  dev_free(*dst_w);
+  TRY(dev_alloc(dst_w, w.size() * 2));
+  CUDA_TRY(cudaMemcpy(*dst_w, w.data(), w.size() * 2, cudaMemcpyHostToDevice));
+  TRY(upload_f32(dst_s, sf.data(), (size_t)N));
+  return upload_f32(dst_c, cf.data(), (size_t)N);
+}
+
 extern "C" {
 
 const char* tutor_last_error(void) { return g_err; }

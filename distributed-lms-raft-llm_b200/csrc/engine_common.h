@@ -27,3 +27,7 @@ void tutor_count_launches(uint64_t n);      // bumps the counter behind tutor_la
 int upload_f32(float** dst, const float* src, size_t n);
 // rows x cols fp32 host matrix -> device matrix of `dt`; transpose=true stores it as [cols, rows]
 int upload_matrix(void** dst, const float* src, int64_t rows, int64_t cols, bool transpose, int dt);
+// LayerNorm folded into the linear that follows it (bf16 decode): W' = gamma (.) W as bf16 [N, K], s[n] = sum_k W'[n,k],
+// c[n] = sum_k beta[k] W[n,k]; src is the Conv1D weight [K, N]
+int upload_ln_folded(void** dst_w, float** dst_s, float** dst_c, const float* src, int64_t K, int64_t N, const float* gamma,
+                     const float* beta);

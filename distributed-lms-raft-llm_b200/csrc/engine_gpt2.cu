@@ -12,11 +12,18 @@
 #include <string>
 #include <vector>
 
+#include "decode_mega.h"
 #include "engine_common.h"
 
 struct Gpt2Layer {
   float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
   Linear qkv, proj, fc, proj2;
+  // bf16 decode: ln_1 / ln_2 folded into c_attn / c_fc (decode_mega.h).  Built when the Conv1D weight is loaded after
+  // its LayerNorm's parameters (the order of a transformers state_dict); a LayerNorm tensor loaded later invalidates it.
+  std::vector<float> h_ln[4];  // host copies of ln_1.weight, ln_1.bias, ln_2.weight, ln_2.bias
+  void *qkv_f = nullptr, *fc_f = nullptr;
+  float *qkv_s = nullptr, *qkv_c = nullptr, *fc_s = nullptr, *fc_c = nullptr;
+  bool fold_qkv = false, fold_fc = false;
 };
 
 struct tutor_gpt2 {
@@ -75,6 +82,25 @@ struct tutor_gpt2 {
   int safe_rows = 0;
   float cur_penalty = 1.f;
   int cur_eos = -1, cur_pad = 0;
+  // persistent decode-step kernel (decode_mega.cu): the whole transformer stack of a step in one launch.  Opt-in
+  // (TUTOR_MEGA=1): on B200 it measured slower than the 5-launches-per-layer chain of gemm_decode_fused.cu at every
+  // shape tried (configs[2]: 640 vs 594 us per forward; profiles/r2a_*) - every hand-off between SMs through L2 costs
+  // 1-2.5 us under load, and a step of the chain needs two of them
+  int mega_mode = 0;
+  uint64_t alloc_epoch = 1;  // bumped whenever a buffer or weight the plan points at is (re)allocated
+  struct Mega {
+    uint64_t epoch = 0;
+    int B = 0, gn = 0, nsteps = 0;
+    MegaParams mp{};
+    void* maps = nullptr;
+    MegaLayerW* lw = nullptr;
+    MegaStep* steps = nullptr;
+    int* flags = nullptr;
+    float* partial[4] = {nullptr, nullptr, nullptr, nullptr};
+    bf16* xb = nullptr;
+    long long* trace = nullptr;  // tutor_gpt2_decode_trace
+    int trace_cta = -1;
+  } mega;
   // decode graph
   cudaGraphExec_t graph_exec = nullptr;
   uint64_t graph_kernels = 0;
@@ -280,12 +306,163 @@ int forward_decode_cluster(tutor_gpt2* e, int lane, int b0, int B) {
                          (uint8_t*)e->lm_scratch + (size_t)lane * e->lm_scratch_lane_bytes, st);
 }
 
+
+bool mega_applies(const tutor_gpt2* e, int B) {
+  if (!(e->dt == DT_BF16 && e->use_fused && e->mega_mode > 0 && B <= 128 && e->d % 128 == 0 && e->d <= 1280)) return false;
+  for (const Gpt2Layer& l : e->layers)
+    if (!l.fold_qkv || !l.fold_fc) return false;  // weights were loaded ahead of their LayerNorm: use the launch chain
+  return true;
+}
+
+void mega_free(tutor_gpt2* e) {
+  tutor_gpt2::Mega& m = e->mega;
+  if (m.maps) cudaFree(m.maps);
+  m.maps = nullptr;
+  dev_free(m.lw); dev_free(m.steps); dev_free(m.flags); dev_free(m.xb);
+  for (auto& q : m.partial) dev_free(q);
+  m.epoch = 0;
+}
+
+
+// Split plan of one linear: ks K-splits of the N/128 weight tiles; a CTA runs ceil(units / CTAs) units one after the other.
+// Cost of a round ~ k-blocks per unit + a fixed ~3 k-block-equivalents for operand load, drain, partial store and flags;
+// ties go to fewer splits (fewer partials through L2).
+int mega_pick_ks(int ntiles, int nkb, int nctas) {
+  int best = 1, best_cost = 1 << 30;
+  for (int ks = 1; ks <= nkb && ks <= 12; ++ks) {  // 12: what the closing epilogue keeps in flight per row
+    if (nkb % ks) continue;
+    const int rounds = ceil_div(ntiles * ks, nctas);
+    const int cost = rounds * (nkb / ks + 3);
+    if (cost < best_cost) { best_cost = cost; best = ks; }
+  }
+  return best;
+}
+
+// (Re)builds the plan of the persistent decode kernel for batch B: tensor maps, per-layer pointers, the step program,
+// counters and partial-sum buffers.  Cheap to call: does nothing unless B or an underlying allocation changed.
+int mega_prepare(tutor_gpt2* e, int B) {
+  tutor_gpt2::Mega& m = e->mega;
+  if (m.epoch == e->alloc_epoch && m.B == B) return TUTOR_OK;
+  drop_graph(e);
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  mega_free(e);
+  const int d = e->d, L = e->L, nctas = e->num_sms;
+  MegaParams mp{};
+  mp.B = B; mp.d = d; mp.H = e->H; mp.L = L; mp.Smax = e->Smax;
+  int G = B >= 32 ? 2 : 1;
+  if (const char* s = getenv("TUTOR_MEGA_GROUPS")) G = atoi(s) < 1 ? 1 : (atoi(s) > 4 ? 4 : atoi(s));
+  if (G > B) G = B;
+  while (ceil_div(B, G) > 64) ++G;  // a row group is one UMMA N tile: at most 64 rows
+  mp.G = G; mp.rpg = ceil_div(B, G);
+  mp.G = ceil_div(B, mp.rpg);
+  G = mp.G;
+  m.gn = k_decode_mega_gn(mp.rpg);
+  const int nout[4] = {3 * d, d, 4 * d, d}, kin[4] = {d, d, d, 4 * d};
+  int rot = 0;
+  int team = nctas / G;  // CTAs whose GEMM engine serves one row group
+  if (const char* s = getenv("TUTOR_MEGA_TEAM")) team = atoi(s) < 1 ? 1 : (atoi(s) < team ? atoi(s) : team);
+  mp.team = team;
+  for (int ph = 0; ph < 4; ++ph) {
+    mp.nout[ph] = nout[ph];
+    mp.ntiles[ph] = nout[ph] / 128;
+    const int nkb = kin[ph] / 64;
+    mp.ks[ph] = mega_pick_ks(mp.ntiles[ph], nkb, team);
+    mp.kpu[ph] = nkb / mp.ks[ph];
+    mp.nunits[ph] = mp.ntiles[ph] * mp.ks[ph];
+    mp.rot[ph] = rot;  // phases with few units land on different CTAs
+    rot = (rot + mp.nunits[ph]) % team;
+    TRY(dev_alloc(&m.partial[ph], (size_t)mp.ks[ph] * B * nout[ph] * sizeof(float)));
+    mp.partial[ph] = m.partial[ph];
+  }
+  // weight tensor maps and per-layer pointers
+  std::vector<CUtensorMap> maps((size_t)L * 4 + 3);
+  std::vector<MegaLayerW> lw(L);
+  for (int l = 0; l < L; ++l) {
+    const Gpt2Layer& w = e->layers[l];
+    const Linear* lin[4] = {&w.qkv, &w.proj, &w.fc, &w.proj2};
+    const void* wp[4] = {w.qkv_f, w.proj.w, w.fc_f, w.proj2.w};  // c_attn / c_fc with their LayerNorm folded in
+    for (int ph = 0; ph < 4; ++ph) TRY(k_make_map_bf16(&maps[(size_t)l * 4 + ph], (const bf16*)wp[ph], lin[ph]->N, lin[ph]->K, 128));
+    lw[l] = MegaLayerW{w.qkv_s, w.qkv_c, w.fc_s, w.fc_c, w.qkv.b, w.proj.b, w.fc.b, w.proj2.b,
+                       (bf16*)e->kcache(l), (bf16*)e->vcache(l)};
+  }
+  // activation operands: one row group x 64 columns per box; rows past the batch read as zeros
+  TRY(dev_alloc(&m.xb, (size_t)B * d * sizeof(bf16)));
+  TRY(k_make_map_bf16(&maps[(size_t)L * 4 + 0], m.xb, B, d, m.gn));
+  TRY(k_make_map_bf16(&maps[(size_t)L * 4 + 1], (const bf16*)e->att, B, d, m.gn));
+  TRY(k_make_map_bf16(&maps[(size_t)L * 4 + 2], (const bf16*)e->hbuf, B, 4 * d, m.gn));
+  CUDA_TRY(cudaMalloc(&m.maps, maps.size() * sizeof(CUtensorMap)));
+  CUDA_TRY(cudaMemcpy(m.maps, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
+  TRY(dev_alloc(&m.lw, lw.size() * sizeof(MegaLayerW)));
+  CUDA_TRY(cudaMemcpy(m.lw, lw.data(), lw.size() * sizeof(MegaLayerW), cudaMemcpyHostToDevice));
+  mp.maps = reinterpret_cast<const CUtensorMap*>(m.maps);
+  mp.lw = m.lw;
+  // counters: [0] queue, [1] finished CTAs, then XR[(L+1)*G], QKV, ATT, X1, HH [L*G each], tile counters
+  mp.maxtiles = 4 * d / 128;
+  const int xr0 = 2, qkv0 = xr0 + (L + 1) * G, att0 = qkv0 + L * G, x10 = att0 + L * G, hh0 = x10 + L * G;
+  mp.tc0 = hh0 + L * G;
+  mp.nflags = mp.tc0 + L * G * 3 * mp.maxtiles;
+  mp.flag_qkv0 = qkv0; mp.flag_att0 = att0;
+  TRY(dev_alloc(&m.flags, ((size_t)mp.nflags * MG_FLAG_STRIDE + 8) * sizeof(int)));
+  CUDA_TRY(cudaMemset(m.flags, 0, ((size_t)mp.nflags * MG_FLAG_STRIDE + 8) * sizeof(int)));
+  mp.flags = m.flags;
+  mp.err = m.flags + (size_t)mp.nflags * MG_FLAG_STRIDE;  // behind the counters: the kernel's clearing pass stops short of it
+  // the step program of the GEMM engines
+  std::vector<MegaStep> steps;
+  auto rows_of = [&](int g) { return (mp.rpg < B - g * mp.rpg) ? mp.rpg : B - g * mp.rpg; };
+  for (int g = 0; g < G; ++g) steps.push_back(MegaStep{MG_EMBED, 0, g, 0, -1, 0, xr0 + g, 0});
+  for (int g = 0; g < G; ++g) steps.push_back(MegaStep{MG_GEMM, 0, g, 0, xr0 + g, rows_of(g), qkv0 + g, 0});
+  for (int l = 0; l < L; ++l)
+    for (int g = 0; g < G; ++g) {
+      const int lg = l * G + g;
+      steps.push_back(MegaStep{MG_GEMM, l, g, 1, att0 + lg, rows_of(g) * e->H, x10 + lg, 0});
+      steps.push_back(MegaStep{MG_GEMM, l, g, 2, x10 + lg, mp.nunits[1], hh0 + lg, 0});
+      steps.push_back(MegaStep{MG_GEMM, l, g, 3, hh0 + lg, mp.nunits[2], xr0 + (l + 1) * G + g, 0});
+      if (l + 1 < L)
+        steps.push_back(MegaStep{MG_GEMM, l + 1, g, 0, xr0 + (l + 1) * G + g, mp.nunits[3], qkv0 + (l + 1) * G + g, 0});
+      else
+        steps.push_back(MegaStep{MG_FINAL, l, g, 0, xr0 + (l + 1) * G + g, mp.nunits[3], -1, 0});
+    }
+  m.nsteps = (int)steps.size();
+  TRY(dev_alloc(&m.steps, steps.size() * sizeof(MegaStep)));
+  CUDA_TRY(cudaMemcpy(m.steps, steps.data(), steps.size() * sizeof(MegaStep), cudaMemcpyHostToDevice));
+  mp.steps = m.steps;
+  mp.x = e->x; mp.xb = m.xb; mp.stats = e->ln_stats; mp.att = (bf16*)e->att; mp.hbuf = (bf16*)e->hbuf;
+  mp.ids = e->ids; mp.ids_ld = e->ids_ld; mp.len = e->counters; mp.npad = nullptr;
+  mp.wte = (const bf16*)e->wte; mp.wpe = e->wpe; mp.lnf_g = e->lnf_g; mp.lnf_b = e->lnf_b;
+  mp.xn_last = (bf16*)e->xn_last; mp.eps = e->cfg.layer_norm_epsilon;
+  m.mp = mp;
+  m.B = B;
+  m.epoch = e->alloc_epoch;
+  return TUTOR_OK;
+}
+
+// One decode forward: the persistent kernel runs the transformer stack, the LM head follows as its own launches.
+int forward_decode_mega(tutor_gpt2* e, int B) {
+  tutor_gpt2::Mega& m = e->mega;
+  cudaStream_t st = e->stream;
+  MegaParams mp = m.mp;
+  mp.npad = e->padded ? e->npad : nullptr;
+  mp.trace = m.trace_cta >= 0 ? m.trace : nullptr;
+  mp.trace_cta = m.trace_cta;
+  mp.step_begin = 0; mp.step_end = m.nsteps;
+  mp.attn_begin = 0; mp.attn_end = e->L * B * e->H; mp.attn_wait = 1;
+  mp.l2_prefetch = getenv("TUTOR_MEGA_L2PF") != nullptr;  // measured slower: 774 vs 662 us (the prefetch traffic delays the chain)
+  TRY(k_decode_mega(mp, m.gn, e->num_sms, st));
+  return k_lmhead_argmax(e->xn_last, e->dt, e->wte, e->dt, B, e->V, e->d, e->dstate(), e->lm_scratch, st);
+}
+
 int decode_forward(tutor_gpt2* e, int B) {
   if (!(e->dt == DT_BF16 && e->use_fused && B <= 128)) {
     // parity (fp32) path: same kernel chain as prefill, with PDL when every GEMM is the weight-streaming GEMV
     // (M <= 8), all of whose kernels wait before touching dependent data
     tutor_pdl_enabled = e->use_pdl && e->dt == DT_F32 && B <= 8;
     int rc = forward(e, B, 1, true);
+    tutor_pdl_enabled = false;
+    return rc;
+  }
+  if (mega_applies(e, B) && e->nlanes == 1) {
+    tutor_pdl_enabled = e->use_pdl;
+    int rc = forward_decode_mega(e, B);
     tutor_pdl_enabled = false;
     return rc;
   }
@@ -314,6 +491,7 @@ int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
   const size_t es = e->esz();
   if (B > e->Bcap || Smax > e->Smax) {
     drop_graph(e);
+    ++e->alloc_epoch;
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     const int nb = B > e->Bcap ? B : e->Bcap, ns = Smax > e->Smax ? Smax : e->Smax;
     if (e->kv) CUDA_TRY(cudaFree(e->kv));
@@ -359,6 +537,7 @@ int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
   const int M = B * T;
   if (M > e->Mcap) {
     drop_graph(e);
+    ++e->alloc_epoch;
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     dev_free(e->x); dev_free(e->xn); dev_free(e->q); dev_free(e->att); dev_free(e->hbuf);
     const size_t d = e->d;
@@ -410,6 +589,7 @@ int start_generation(tutor_gpt2* e, int B, int T, int total, float penalty, int 
   if (safe != e->safe_rows) drop_graph(e);
   e->safe_rows = safe;
   e->cur_B = B; e->cur_T = T; e->cur_total = total; e->cur_penalty = penalty; e->cur_eos = eos; e->cur_pad = pad;
+  if (mega_applies(e, B) && nl == 1) TRY(mega_prepare(e, B));
   cudaStream_t st = e->stream;
   e->h_counters[0] = T; e->h_counters[1] = 0;
   CUDA_TRY(cudaMemcpyAsync(e->counters, e->h_counters, 2 * sizeof(int), cudaMemcpyHostToDevice, st));
@@ -465,6 +645,16 @@ int read_counters(tutor_gpt2* e, int* len, int* stop_len) {
   CUDA_TRY(cudaMemcpyAsync(e->h_counters, e->counters, 2 * tutor_gpt2::MAX_LANES * sizeof(int), cudaMemcpyDeviceToHost,
                            e->stream));
   CUDA_TRY(cudaStreamSynchronize(e->stream));
+  if (e->mega.flags && e->mega.epoch) {  // a wait inside the persistent decode kernel gave up: the ids are garbage
+    int err[5] = {0, 0, 0, 0, 0};
+    CUDA_TRY(cudaMemcpy(err, e->mega.mp.err, sizeof(err), cudaMemcpyDeviceToHost));
+    if (err[0] != 0) {
+      tutor_set_error("decode kernel: a wait timed out (kind %d, %d %d) in block %d thread %d", err[0], err[1], err[2],
+                      err[3], err[4]);
+      CUDA_TRY(cudaMemset(e->mega.mp.err, 0, 8 * sizeof(int)));
+      return TUTOR_ERR_CUDA;
+    }
+  }
   *len = e->h_counters[0];
   int stop = 0;
   for (int i = 0; i < e->nlanes; ++i) {
@@ -520,6 +710,8 @@ int tutor_gpt2_create(const tutor_gpt2_config* cfg, int device, tutor_gpt2_t** o
   e->use_fused = getenv("TUTOR_NO_FUSED") == nullptr;  // debugging aids: unfused decode kernels / no PDL
   e->use_pdl = getenv("TUTOR_NO_PDL") == nullptr;
   e->use_cluster = getenv("TUTOR_NO_CLUSTER") == nullptr;
+  if (const char* mm = getenv("TUTOR_MEGA")) e->mega_mode = atoi(mm);
+  if (!e->use_cluster) e->mega_mode = 0;
   e->use_ln_gemv = getenv("TUTOR_LN_GEMV") != nullptr;
   e->no_ln_gemv = getenv("TUTOR_NO_LN_GEMV") != nullptr;
   {
@@ -550,11 +742,14 @@ void tutor_gpt2_destroy(tutor_gpt2_t* e) {
   cudaSetDevice(e->device);
   cudaStreamSynchronize(e->stream);
   drop_graph(e);
+  mega_free(e);
+  dev_free(e->mega.trace);
   dev_free(e->wte); dev_free(e->wpe); dev_free(e->lnf_g); dev_free(e->lnf_b);
   for (auto& l : e->layers) {
     dev_free(l.ln1_g); dev_free(l.ln1_b); dev_free(l.ln2_g); dev_free(l.ln2_b);
     dev_free(l.qkv.w); dev_free(l.qkv.b); dev_free(l.proj.w); dev_free(l.proj.b);
     dev_free(l.fc.w); dev_free(l.fc.b); dev_free(l.proj2.w); dev_free(l.proj2.b);
+    dev_free(l.qkv_f); dev_free(l.fc_f); dev_free(l.qkv_s); dev_free(l.qkv_c); dev_free(l.fc_s); dev_free(l.fc_c);
   }
   dev_free(e->kv); dev_free(e->x); dev_free(e->xn); dev_free(e->q); dev_free(e->att); dev_free(e->hbuf);
   dev_free(e->xn_last); dev_free(e->ids); dev_free(e->counters); dev_free(e->seen); dev_free(e->finished);
@@ -576,6 +771,7 @@ int tutor_gpt2_load_tensor(tutor_gpt2_t* e, const char* name, const float* data,
   // weight buffers are about to be replaced: the captured decode step holds their addresses
   CUDA_TRY(cudaStreamSynchronize(e->stream));
   drop_graph(e);
+  ++e->alloc_epoch;
   const std::string full(name);
   if (full == "lm_head.weight") return TUTOR_OK;  // tied to wte
   NameParts p = split_name(full);
@@ -602,13 +798,32 @@ int tutor_gpt2_load_tensor(tutor_gpt2_t* e, const char* name, const float* data,
     struct { const char* n; float** ptr; } vecs[] = {
         {"ln_1.weight", &l.ln1_g}, {"ln_1.bias", &l.ln1_b}, {"ln_2.weight", &l.ln2_g}, {"ln_2.bias", &l.ln2_b}};
     bool found = false;
-    for (auto& v : vecs)
-      if (p.rest == v.n) { TRY(want(d, -1)); rc = upload_f32(v.ptr, data, d); found = true; }
+    for (int vi = 0; vi < 4; ++vi)
+      if (p.rest == vecs[vi].n) {
+        TRY(want(d, -1));
+        rc = upload_f32(vecs[vi].ptr, data, d);
+        found = true;
+        if (e->dt == DT_BF16) {
+          l.h_ln[vi].assign(data, data + d);
+          (vi < 2 ? l.fold_qkv : l.fold_fc) = false;  // a fold made with the old parameters is stale
+        }
+      }
     for (auto& li : lins) {
       if (p.rest == std::string(li.n) + ".weight") {
         TRY(want(li.K, li.N));  // Conv1D stores [in,out]; transpose to [out,in]
         rc = upload_matrix(&li.lin->w, data, li.K, li.N, true, e->dt);
         li.lin->N = li.N; li.lin->K = li.K; found = true;
+        const bool is_qkv = li.lin == &l.qkv, is_fc = li.lin == &l.fc;
+        if (rc == TUTOR_OK && e->dt == DT_BF16 && (is_qkv || is_fc)) {
+          const int g = is_qkv ? 0 : 2;
+          bool& ok = is_qkv ? l.fold_qkv : l.fold_fc;
+          ok = false;
+          if ((int)l.h_ln[g].size() == d && (int)l.h_ln[g + 1].size() == d) {
+            rc = upload_ln_folded(is_qkv ? &l.qkv_f : &l.fc_f, is_qkv ? &l.qkv_s : &l.fc_s, is_qkv ? &l.qkv_c : &l.fc_c,
+                                  data, li.K, li.N, l.h_ln[g].data(), l.h_ln[g + 1].data());
+            ok = rc == TUTOR_OK;
+          }
+        }
       } else if (p.rest == std::string(li.n) + ".bias") {
         TRY(want(li.N, -1));
         rc = upload_f32(&li.lin->b, data, li.N); found = true;
@@ -740,5 +955,25 @@ double tutor_gpt2_decode_bytes(tutor_gpt2_t* e, int B, int S) {
 }
 
 void* tutor_gpt2_stream(tutor_gpt2_t* e) { return e ? (void*)e->stream : nullptr; }
+
+int tutor_gpt2_decode_trace(tutor_gpt2_t* e, int cta, long long* out_host, int capacity) {
+  ARG_CHECK(e, "gpt2_decode_trace: null handle");
+  std::lock_guard<std::mutex> lock(e->mu);
+  CUDA_TRY(cudaSetDevice(e->device));
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  tutor_gpt2::Mega& m = e->mega;
+  if (out_host) {
+    ARG_CHECK(m.trace, "gpt2_decode_trace: no trace has been armed");
+    const int n = capacity < MG_TRACE_WORDS ? capacity : MG_TRACE_WORDS;
+    CUDA_TRY(cudaMemcpy(out_host, m.trace, (size_t)n * sizeof(long long), cudaMemcpyDeviceToHost));
+  }
+  if (cta >= 0 || !out_host) {
+    if (cta >= 0 && !m.trace) TRY(dev_alloc(&m.trace, MG_TRACE_WORDS * sizeof(long long)));
+    if (m.trace) CUDA_TRY(cudaMemset(m.trace, 0, MG_TRACE_WORDS * sizeof(long long)));
+    if (cta != m.trace_cta) drop_graph(e);  // the trace pointer is a captured kernel argument
+    m.trace_cta = cta;
+  }
+  return MG_TRACE_WORDS;
+}
 
 }  // extern "C"

@@ -98,6 +98,12 @@ int tutor_gpt2_logits(tutor_gpt2_t* h, float* logits_dev /* [B, vocab] */);
 double tutor_gpt2_decode_bytes(tutor_gpt2_t* h, int B, int S);
 /* Stream the engine enqueues on (a cudaStream_t), so callers can bracket it with CUDA events. */
 void* tutor_gpt2_stream(tutor_gpt2_t* h);
+/* Profiling aid of the persistent decode kernel (bf16 mode; no counterpart in the reference): cta >= 0 arms a
+ * per-phase clock64() trace of that CTA for the following decode steps (re-captures the step graph); out_host, if
+ * non-null, receives up to `capacity` 64-bit words of the trace recorded by the most recent step.  Layout:
+ * 128 steps x 8 stamps of the GEMM engine, then 64 units x 8 stamps of attention stream 0 (csrc/decode_mega.h).
+ * cta < 0 with out_host == NULL disarms it.  Returns the number of words available (> 0) or a negative error.  */
+int tutor_gpt2_decode_trace(tutor_gpt2_t* h, int cta, long long* out_host, int capacity);
 
 /* ----------------------------------------------------------------------------------------------------------
  * BERT: replaces BertModel.forward + mean(dim=1) inside compute_embeddings (REF/lms_server.py:97-101).         */

@@ -292,3 +292,27 @@ def test_bf16_ragged_shapes_against_oracle_logits(pkg, tiny_hf, B, T):
     b = eng.generate(ids, max_new_tokens=12, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
     assert tuple(a.shape) == (B, T + 12) and torch.equal(a, b) and torch.equal(a[:, :T], ids)
     assert int(a.min()) >= 0 and int(a.max()) < 1000
+
+
+@pytest.mark.parametrize("B,T", [(1, 9), (5, 40), (16, 70), (33, 20), (64, 130), (100, 20)])
+def test_persistent_decode_kernel_matches_launch_chain(pkg, tiny_hf, monkeypatch, B, T):
+    """The opt-in persistent decode kernel (TUTOR_MEGA=1: LayerNorm folded into the weights, TMA operands, split-K
+    closed through L2 counters, queue-fed attention streams) against the default launch chain: same prompt, one decode
+    step (so both see the same context), logits within the bf16 tolerance; generation is run-to-run deterministic."""
+    ids = rp.gpt2_prompt_ids(B, T, seed=21 + B, vocab=1000)
+    logits, outs = [], []
+    for mode in ("0", "1"):
+        monkeypatch.setenv("TUTOR_MEGA", mode)
+        eng = pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="bf16")
+        eng.prefill(ids, max_new_tokens=12, eos_token_id=999, pad_token_id=999)
+        eng.step(1)
+        logits.append(eng.last_logits().float().cpu())
+        outs.append([eng.generate(ids, max_new_tokens=12, eos_token_id=999, pad_token_id=999) for _ in range(2)])
+    monkeypatch.delenv("TUTOR_MEGA")
+    err = ((logits[0] - logits[1]).abs().max() / logits[0].abs().max()).item()
+    print(f"persistent kernel vs launch chain, B={B}: relative logit difference {err:.3e}")
+    assert err < 2e-2
+    with torch.no_grad():
+        ref = tiny_hf(outs[1][0][:, :T + 1]).logits[:, -1].float()  # fp32 oracle at the context of that step
+    assert ((logits[1] - ref).abs().max() / ref.abs().max()).item() < 5e-2 or not torch.equal(outs[0][0][:, :T + 1], outs[1][0][:, :T + 1])
+    assert torch.equal(outs[1][0], outs[1][1]), "the persistent kernel must be run-to-run deterministic"
