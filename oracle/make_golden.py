@@ -185,6 +185,28 @@ def make_cfg2(tut, lms):
         out[f"gap_{name}"] = gaps(scores).astype(np.float32)  # [256,64]
         print("cfg2", name, time.time() - t0, "s; min gap", out[f"gap_{name}"].min())
     np.savez_compressed(os.path.join(OUT, "gpt2_cfg2.npz"), **out)
+    make_cfg2_logits(tut, lms)
+
+
+CFG2_TF = ((0, 1), (21, 64), (42, 128), (63, 255))  # (row, decode step): cache lengths 512, 575, 639, 766
+
+
+def make_cfg2_logits(tut, lms, seq=None):
+    """Teacher-forced fp32 logits of configs[2] for the bf16 decode gate: for (row b, decode step s) the oracle's logits
+    at the forward that consumes token 512+s-1 (cache length 512+s-1) - what one engine decode step must reproduce after
+    a prefill of the oracle's own ids[:, :512+s-1]."""
+    model = tut.model
+    if seq is None:  # from the committed ids (the generation itself takes many CPU-minutes)
+        g = np.load(os.path.join(OUT, "gpt2_cfg2.npz"))
+        seq = torch.cat([rp.gpt2_prompt_ids(64, 512, seed=1), torch.from_numpy(g["ids_p10"].astype(np.int64))], dim=1)
+    out = {"rows": np.array([b for b, _ in CFG2_TF]), "steps": np.array([s for _, s in CFG2_TF])}
+    for i, (b, s) in enumerate(CFG2_TF):
+        with torch.no_grad():
+            lg = model(seq[b:b + 1, :512 + s]).logits[0, -1].float()
+        assert int(lg.argmax()) == int(seq[b, 512 + s]), "teacher-forced logits do not reproduce the oracle's token"
+        out[f"logits_{i}"] = lg.numpy()
+    np.savez_compressed(os.path.join(OUT, "gpt2_cfg2_logits.npz"), **out)
+    print("cfg2 teacher-forced logits for", CFG2_TF)
 
 
 def make_cfg3(tut, lms):
@@ -222,12 +244,15 @@ def make_padded(tut, lms):
 
 
 MAKERS = dict(padded=make_padded, cfg0=make_cfg0, as_written=make_as_written, tiny=make_tiny, bert=make_bert, bert_tiny=make_bert_tiny,
-              cfg2=make_cfg2, cfg3=make_cfg3)
+              cfg2=make_cfg2, cfg2_logits=make_cfg2_logits, cfg3=make_cfg3)
+# every fixture under tests/golden/, in the order they are cheapest to make (cfg2 and cfg3 take many CPU-minutes each;
+# cfg2 writes gpt2_cfg2_logits.npz too, `cfg2_logits` alone rebuilds it from the committed ids)
+ALL = ["cfg0", "as_written", "tiny", "padded", "bert", "bert_tiny", "cfg2", "cfg3"]
 
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--only", nargs="*", default=["cfg0", "as_written", "tiny", "bert", "bert_tiny"])
+    ap.add_argument("--only", nargs="*", default=ALL, help="fixtures to (re)generate; default: all of them")
     args = ap.parse_args()
     os.makedirs(OUT, exist_ok=True)
     torch.set_grad_enabled(False)

@@ -146,7 +146,44 @@ def test_cfg2_full_size(small_bf16, golden):
     prefix = np.where(same.all(axis=1), 256, np.argmin(same, axis=1))
     print(f"cfg2 bf16 vs fp32 oracle: first-token agreement {first:.3f}, overall {same.mean():.3f}, "
           f"median identical prefix {np.median(prefix):.0f} tokens")
+    # stated bf16 tolerance for configs[2]: a greedy sequence stays on the oracle's path until the
+    # first near-tie flips, after which the two contexts differ for good - hence a prefix length, not a per-token rate
     assert first >= 0.9
+    assert same.mean() >= CFG2_MIN_AGREEMENT and np.median(prefix) >= CFG2_MIN_MEDIAN_PREFIX
+
+
+CFG2_MIN_AGREEMENT, CFG2_MIN_MEDIAN_PREFIX = 0.40, 16  # measured on B200: 0.601 overall, median prefix 46
+CFG2_DECODE_LOGIT_TOL = 2e-2                            # max |logit - oracle| / max |oracle| per row; measured 6.4e-3 .. 7.3e-3
+
+
+def test_cfg2_bf16_decode_logits_teacher_forced(small_bf16, golden):
+    """The benchmarked path itself - the bf16 decode forward at B=64 over a 512..766-row cache - against the fp32 oracle:
+    the engine prefills the ORACLE's ids up to decode step s, runs ONE decode forward, and its logits are compared with
+    the oracle's teacher-forced logits for that position (tests/golden/gpt2_cfg2_logits.npz, made by
+    oracle/make_golden.py from the unmodified transformers path).  Stated tolerance: 2e-2 of the row's largest logit, and >= 0.85 of the
+    rows must pick the oracle's next token."""
+    g, gl = golden("gpt2_cfg2"), golden("gpt2_cfg2_logits")
+    seq = torch.cat([rp.gpt2_prompt_ids(64, 512, seed=1), torch.from_numpy(g["ids_p10"].astype(np.int64))], dim=1)
+    checked = 0
+    for i, (b, s) in enumerate(zip(gl["rows"], gl["steps"])):
+        b, s = int(b), int(s)
+        small_bf16.prefill(seq[:, :512 + s - 1], max_new_tokens=2)  # selects token 512+s-1 (from prefill logits)
+        fed = small_bf16.read_ids()[:, -1]
+        small_bf16.step(1)                                          # the decode forward under test: cache length 512+s-1
+        logits = small_bf16.last_logits().float().cpu().numpy()
+        ok_rows = (fed == seq[:, 512 + s - 1]).numpy()              # rows whose decode input is the oracle's token
+        nxt = (logits.argmax(axis=1) == seq[:, 512 + s].numpy())[ok_rows].mean()
+        print(f"decode step {s}: {ok_rows.mean():.3f} of the rows were fed the oracle's token; teacher-forced next-token "
+              f"agreement of those rows {nxt:.3f}")
+        assert ok_rows.mean() >= 0.9 and nxt >= 0.85
+        if ok_rows[b]:
+            ref = gl[f"logits_{i}"]
+            err = float(np.abs(logits[b] - ref).max() / np.abs(ref).max())
+            print(f"  row {b}, cache length {512 + s - 1}: relative logit error {err:.3e}, "
+                  f"arg-max {'same' if logits[b].argmax() == ref.argmax() else 'differs'}")
+            assert err < CFG2_DECODE_LOGIT_TOL
+            checked += 1
+    assert checked >= 3
 
 
 def test_cfg2_fp32_parity_subset(small_f32, golden):
@@ -157,10 +194,14 @@ def test_cfg2_fp32_parity_subset(small_f32, golden):
     out = small_f32.generate(ids, max_new_tokens=64, repetition_penalty=1.2)
     ref, gap = g["ids_p12"][:8, :64], g["gap_p12"][:64, :8].T
     mine = out[:, 512:].numpy()
+    excused = 0
     for b in range(8):
         mism = np.nonzero(mine[b] != ref[b])[0]
         if mism.size:
             assert gap[b, mism[0]] < 1e-4, (b, mism[0], gap[b, mism[0]])
+            excused += 1
+    print(f"cfg2 fp32 subset: {8 - excused} of 8 rows identical over 64 tokens, {excused} diverge at an oracle near-tie (< 1e-4)")
+    assert excused <= 2
 
 
 def test_fused_decode_path_matches_unfused(pkg, tiny_hf, monkeypatch):
@@ -219,13 +260,25 @@ def test_cfg3_gpt2_large_prefill_heavy(pkg, golden):
     assert tuple(out.shape) == (16, 1024) and torch.equal(out[:, :896], ids)
     same = out[:, 896:].numpy() == g["ids_p10"]
     print(f"cfg3 bf16 vs fp32 oracle: first-token agreement {same[:, 0].mean():.3f}, overall {same.mean():.3f}")
-    assert same[:, 0].mean() >= 0.8
+    assert same[:, 0].mean() >= 0.8 and same.mean() >= 0.5  # measured 0.938 / 0.794
     assert torch.equal(out, eng.generate(ids, max_new_tokens=128, repetition_penalty=1.0))
     eng.prefill(ids, max_new_tokens=128)
     logits = eng.last_logits()[0].float().cpu().numpy()
     err = float(np.abs(logits - g["logits_step0_row0"]).max() / np.abs(g["logits_step0_row0"]).max())
     print(f"cfg3 bf16 step-0 relative logit error {err:.3e}")
     assert err < 5e-2
+    # the decode path, teacher-forced: prefill the oracle's ids up to decode step s, one decode forward, and the arg-max
+    # of every row that was fed the oracle's token must be the oracle's next token (stated: >= 0.8 of the rows)
+    seq = torch.cat([ids, torch.from_numpy(g["ids_p10"].astype(np.int64))], dim=1)
+    for s in (1, 64, 127):
+        eng.prefill(seq[:, :896 + s - 1], max_new_tokens=2)
+        fed = eng.read_ids()[:, -1]
+        eng.step(1)
+        nxt = eng.read_ids()[:, -1]
+        ok_rows = fed == seq[:, 896 + s - 1]
+        agree = (nxt == seq[:, 896 + s])[ok_rows].float().mean().item()
+        print(f"cfg3 decode step {s}: {ok_rows.float().mean():.3f} rows fed the oracle's token, next-token agreement {agree:.3f}")
+        assert ok_rows.float().mean() >= 0.8 and agree >= 0.8
     with pytest.raises(Exception, match="n_positions"):
         eng.generate(rp.gpt2_prompt_ids(1, 1000, seed=2), max_new_tokens=128)  # would index past wpe
 
