@@ -7,8 +7,8 @@ from . import _lib
 from .bert import (NOT_RELATED_MESSAGE, SIMILARITY_THRESHOLD, B200BertModel, compute_embeddings, cosine_similarity,
                    cosine_similarity_batch, is_relevant)
 from .gpt2 import B200GPT2LMHeadModel
-from .relevance import CorpusShard, exchange_candidates, shard_bounds
+from .relevance import CorpusShard, close_exchange, exchange_candidates, init_exchange, shard_bounds
 
 __all__ = ["B200GPT2LMHeadModel", "B200BertModel", "compute_embeddings", "cosine_similarity", "cosine_similarity_batch",
-           "is_relevant", "CorpusShard", "exchange_candidates", "shard_bounds", "SIMILARITY_THRESHOLD",
+           "is_relevant", "CorpusShard", "exchange_candidates", "init_exchange", "close_exchange", "shard_bounds", "SIMILARITY_THRESHOLD",
            "NOT_RELATED_MESSAGE", "_lib"]

@@ -64,6 +64,13 @@ SIGNATURES = {
     "tutor_cosine_topk": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int,
                                   c_void_p, c_void_p]),
     "tutor_topk_merge": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "tutor_nccl_load": (c_int, [c_char_p]),
+    "tutor_nccl_unique_id": (c_int, [c_void_p]),
+    "tutor_nccl_comm_create": (c_int, [c_void_p, c_int, c_int, P(c_void_p)]),
+    "tutor_nccl_comm_destroy": (None, [c_void_p]),
+    "tutor_topk_merge_allgather_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "tutor_topk_merge_allgather": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                           c_void_p]),
     "tutor_layernorm": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "tutor_linear": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                              c_int, c_void_p]),

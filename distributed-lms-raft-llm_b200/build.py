@@ -54,7 +54,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         for _, log in results:
             sys.stderr.write(log)
     objs = [o for o, _ in results]
-    cmd = [NVCC, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
+    cmd = [NVCC, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-ldl"]
     p = subprocess.run(cmd, capture_output=True, text=True)
     if p.returncode != 0:
         raise RuntimeError(f"link failed:\n{p.stdout}\n{p.stderr}")

@@ -59,9 +59,10 @@ __device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uin
 // queries [Q, D] -> q_hi, q_lo [32, D] (rows >= Q zero) and 1 / max(|q|, eps); one block per query row
 __global__ void __launch_bounds__(256) split_queries_kernel(const float* __restrict__ queries, int Q, int D, float eps,
                                                            float* __restrict__ q_hi, float* __restrict__ q_lo,
-                                                           float* __restrict__ qinv) {
+                                                           float* __restrict__ qinv, int* __restrict__ counters) {
   __shared__ float red[8];
   const int q = blockIdx.x;
+  if (threadIdx.x == 0) counters[q] = 0;  // arrival counters of the re-scoring CTAs (topk_rescore_kernel)
   float s = 0.f;
   for (int i = threadIdx.x; i < D; i += blockDim.x) {
     const float x = q < Q ? queries[(size_t)q * D + i] : 0.f;
@@ -223,7 +224,7 @@ __global__ void __launch_bounds__(TS_THREADS) cosine_scan_tf32x3_kernel(const __
 #pragma unroll
       for (int q = 0; q < TS_NQ; ++q) {
         gv[q] = (row < N && q < Q) ? sum[q] * qinv[q] * ci : -CUDART_INF_F;
-        if (row < N && q < Q) scores[(size_t)q * N + row] = gv[q];
+        if (scores && row < N && q < Q) scores[(size_t)q * N + row] = gv[q];
       }
       // transposing butterfly: 31 shuffles leave the maximum over the warp's 32 rows of query q in lane q
       // (a warp_max per query would take 160)
@@ -249,42 +250,52 @@ __global__ void __launch_bounds__(TS_THREADS) cosine_scan_tf32x3_kernel(const __
   }
 }
 
-// block-wide arg-max of (value desc, key asc); every thread gets the winner.  red_v / red_k: 8 floats / ints of smem
-__device__ __forceinline__ void block_argmax(float& v, int& key, float* red_v, int* red_k) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+// warp-wide arg-max of (value desc, key asc); every lane gets the winner
+__device__ __forceinline__ void warp_argmax(float& v, int& key) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const float ov = __shfl_xor_sync(0xffffffffu, v, o);
     const int ok = __shfl_xor_sync(0xffffffffu, key, o);
     if (ov > v || (ov == v && ok < key)) { v = ov; key = ok; }
   }
-  __syncthreads();  // red_* may still be read from the previous round
-  if (lane == 0) { red_v[warp] = v; red_k[warp] = key; }
-  __syncthreads();
-  v = red_v[0]; key = red_k[0];
-#pragma unroll
-  for (int w = 1; w < 8; ++w)
-    if (red_v[w] > v || (red_v[w] == v && red_k[w] < key)) { v = red_v[w]; key = red_k[w]; }
+}
+// k best of 32 per-warp lists, each sorted (value desc, key asc) in lv / lk [32][32]: lane l walks list l; run by ONE warp.
+// The winners go to out(round, value, key).
+template <typename Out>
+__device__ __forceinline__ void merge_sorted_lists(const float (*lv)[32], const int (*lk)[32], int k, int lane, Out out) {
+  int head = 0;
+  for (int round = 0; round < k; ++round) {
+    float v = head < k ? lv[lane][head] : -CUDART_INF_F;
+    int key = head < k ? lk[lane][head] : 0x7fffffff;
+    const int mine = key;
+    warp_argmax(v, key);
+    if (key != 0x7fffffff && key == mine) ++head;  // keys are unique
+    out(round, v, key);
+  }
 }
 
-// Exact top-k of one query from the 32-row group maxima the scan left behind: (1) the k groups with the largest maxima
-// (ties to the lower group, i.e. the lower rows), (2) the k best of their k x 32 scores (ties to the lower row).
-// grid (Q), 256 threads, G floats of dynamic shared memory.  k <= 32.
-__global__ void __launch_bounds__(256) topk_from_groups_kernel(const float* __restrict__ scores,
-                                                              const float* __restrict__ gmax, int N, int G, int k,
-                                                              float* __restrict__ out_v, int32_t* __restrict__ out_i,
-                                                              int idx_base) {
+// Exact top-k of one query from the 32-row group maxima the scan left behind, in two launches:
+// (1) topk_select_groups_kernel: the k groups with the largest maxima (ties to the lower group, i.e. the lower rows);
+// (2) topk_rescore_kernel: the k x 32 rows of those groups are scored again in fp32 straight from the corpus - the scan
+//     does not write its 4 Q N bytes of scores at all, they were 4 % of its traffic and only these few were ever read -
+//     one CTA per (group, query) with every load of its 32 rows in flight at once; the last CTA of a query to arrive
+//     takes the k best of the k x 32 scores (ties to the lower row).
+// The selections are two-level: every warp extracts the k best of its own slice with shuffles only, then one warp merges
+// the sorted lists (k block-wide arg-max rounds with two barriers each took 10x longer).  k <= 32.
+constexpr int TK_THREADS = 1024;
+__global__ void __launch_bounds__(TK_THREADS) topk_select_groups_kernel(const float* __restrict__ gmax, int N, int G, int k,
+                                                                       int* __restrict__ sel_out) {
   extern __shared__ float sg[];  // [G] group maxima of this query
-  __shared__ float red_v[8];
-  __shared__ int red_k[8];
-  __shared__ int sel[32];
-  const int q = blockIdx.x, tid = threadIdx.x;
+  __shared__ float lv[32][32];   // per-warp sorted lists
+  __shared__ int lk[32][32];
+  const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int ngroups = (N + 31) / 32;  // groups past this are padding of the last tile
-  for (int g = tid; g < G; g += 256) sg[g] = g < ngroups ? gmax[(size_t)q * G + g] : -CUDART_INF_F;
+  for (int g = tid; g < G; g += TK_THREADS) sg[g] = g < ngroups ? gmax[(size_t)q * G + g] : -CUDART_INF_F;
   __syncthreads();
+  // thread t owns the groups t, t + 1024, ...; its warp extracts the k best of the warp's 32 slices
   auto rescan = [&](float& bv, int& bk) {
     bv = -CUDART_INF_F; bk = 0x7fffffff;
-    for (int g = tid; g < G; g += 256) {
+    for (int g = tid; g < G; g += TK_THREADS) {
       const float v = sg[g];
       if (v > bv) { bv = v; bk = g; }  // ascending g: strict > keeps the lowest group
     }
@@ -293,45 +304,108 @@ __global__ void __launch_bounds__(256) topk_from_groups_kernel(const float* __re
   rescan(bv, bk);
   for (int round = 0; round < k; ++round) {
     float v = bv; int key = bk;
-    block_argmax(v, key, red_v, red_k);
-    if (tid == 0) sel[round] = (v == -CUDART_INF_F) ? -1 : key;
-    if (key != 0x7fffffff && (key & 255) == tid) {  // the owner drops the winner and refreshes its cached best
+    warp_argmax(v, key);
+    if (lane == 0) { lv[warp][round] = v; lk[warp][round] = (v == -CUDART_INF_F) ? 0x7fffffff : key; }
+    if (key != 0x7fffffff && key == bk) {  // the owner drops the winner and refreshes its cached best
       sg[key] = -CUDART_INF_F;
       rescan(bv, bk);
     }
   }
   __syncthreads();
-  // candidates: up to k x 32 rows, four per thread
-  float cv[4]; int ck[4];
+  if (warp == 0)
+    merge_sorted_lists(lv, lk, k, lane, [&](int round, float v, int key) {
+      if (lane == 0) sel_out[q * 32 + round] = (key == 0x7fffffff || v == -CUDART_INF_F) ? -1 : key;
+    });
+}
+
+// grid (k, Q), 256 threads: warp w scores rows 4w .. 4w+3 of group sel[q][blockIdx.x]
+template <int NV>  // float4 per lane and row: d = 128 NV
+__global__ void __launch_bounds__(256) topk_rescore_kernel(const float* __restrict__ queries, const float* __restrict__ qinv,
+                                                          const float* __restrict__ corpus,
+                                                          const float* __restrict__ inv_norm, const int* __restrict__ sel,
+                                                          int N, int k, float* __restrict__ cand, int* __restrict__ counters,
+                                                          float* __restrict__ out_v, int32_t* __restrict__ out_i,
+                                                          int idx_base) {
+  constexpr int D = 128 * NV;
+  __shared__ int s_last;
+  const int r = blockIdx.x, q = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = sel[q * 32 + r];
+  float4 cv[4][NV], qv[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) qv[i] = *reinterpret_cast<const float4*>(queries + (size_t)q * D + (i * 32 + lane) * 4);
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    const int c = tid + 256 * j;
-    const int g = c < k * 32 ? sel[c >> 5] : -1;
-    const int row = g >= 0 ? g * 32 + (c & 31) : N;
-    cv[j] = row < N ? scores[(size_t)q * N + row] : -CUDART_INF_F;
-    ck[j] = row < N ? row : 0x7fffffff;
+    const int row = g >= 0 ? g * 32 + warp * 4 + j : N;
+#pragma unroll
+    for (int i = 0; i < NV; ++i)
+      cv[j][i] = row < N ? *reinterpret_cast<const float4*>(corpus + (size_t)row * D + (i * 32 + lane) * 4)
+                         : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  const float qi = qinv[q];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int row = g >= 0 ? g * 32 + warp * 4 + j : N;
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i)
+      dot = fmaf(cv[j][i].x, qv[i].x, fmaf(cv[j][i].y, qv[i].y, fmaf(cv[j][i].z, qv[i].z, fmaf(cv[j][i].w, qv[i].w, dot))));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+    if (lane == 0) cand[(size_t)q * 1024 + r * 32 + warp * 4 + j] = row < N ? dot * qi * inv_norm[row] : -CUDART_INF_F;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(&counters[q], 1) == k - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // the query's last CTA takes the k best of the k x 32 scores, two-level: warp w owns the groups 4w .. 4w+3 (lane l their
+  // rows l), extracts the k best of its 128 candidates with shuffles, and warp 0 merges the eight sorted lists
+  __shared__ float lv[32][32];
+  __shared__ int lk[32][32];
+  float v[4];
+  int rk[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int gi = warp * 4 + j;
+    const int gj = gi < k ? sel[q * 32 + gi] : -1;
+    const int row = gj >= 0 ? gj * 32 + lane : N;
+    rk[j] = row < N ? row : 0x7fffffff;
+    v[j] = row < N ? __ldcg(cand + (size_t)q * 1024 + gi * 32 + lane) : -CUDART_INF_F;
   }
   for (int round = 0; round < k; ++round) {
-    float v = -CUDART_INF_F; int key = 0x7fffffff;
+    float bv = -CUDART_INF_F;
+    int bk = 0x7fffffff;
 #pragma unroll
     for (int j = 0; j < 4; ++j)
-      if (ck[j] != 0x7fffffff && (cv[j] > v || (cv[j] == v && ck[j] < key))) { v = cv[j]; key = ck[j]; }
-    block_argmax(v, key, red_v, red_k);
-    if (tid == 0) {
-      out_v[(size_t)q * k + round] = key != 0x7fffffff ? v : -CUDART_INF_F;
-      out_i[(size_t)q * k + round] = key != 0x7fffffff ? idx_base + key : -1;
-    }
+      if (rk[j] != 0x7fffffff && (v[j] > bv || (v[j] == bv && rk[j] < bk))) { bv = v[j]; bk = rk[j]; }
+    warp_argmax(bv, bk);
+    if (lane == 0) { lv[warp][round] = bv; lk[warp][round] = bk; }
 #pragma unroll
     for (int j = 0; j < 4; ++j)
-      if (ck[j] == key) ck[j] = 0x7fffffff;  // rows are unique
+      if (rk[j] == bk) rk[j] = 0x7fffffff;  // rows are unique
   }
+  __syncthreads();
+  if (warp == 0) {
+    if (lane >= 8)  // only eight lists exist
+      for (int j = 0; j < k; ++j) { lv[lane][j] = -CUDART_INF_F; lk[lane][j] = 0x7fffffff; }
+    __syncwarp();
+    merge_sorted_lists(lv, lk, k, lane, [&](int round, float bv, int bk) {
+      if (lane == 0) {
+        out_v[(size_t)q * k + round] = bk != 0x7fffffff ? bv : -CUDART_INF_F;
+        out_i[(size_t)q * k + round] = bk != 0x7fffffff ? idx_base + bk : -1;
+      }
+    });
+  }
+  if (threadIdx.x == 0) counters[q] = 0;
 }
 
 }  // namespace
 
 size_t k_cosine_scan_tc_scratch_bytes(int d, int N) {
   return round_up((size_t)2 * TS_NQ * d * sizeof(float) + TS_NQ * sizeof(float), 256) +
-         round_up((size_t)TS_NQ * ceil_div(N, TS_BM) * 4 * sizeof(float), 256);  // split queries + group maxima
+         round_up((size_t)TS_NQ * ceil_div(N, TS_BM) * 4 * sizeof(float), 256) +  // split queries + group maxima
+         (size_t)TS_NQ * (32 * sizeof(int) + 1024 * sizeof(float) + sizeof(int));  // selected groups, re-scored rows, counters
 }
 
 int k_cosine_scan_tc(const float* queries, const float* corpus, const float* corpus_inv_norm, int Q, int N, int d,
@@ -343,7 +417,11 @@ int k_cosine_scan_tc(const float* queries, const float* corpus, const float* cor
   float* qinv = q_lo + (size_t)TS_NQ * d;
   float* gmax = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) +
                                          round_up((size_t)2 * TS_NQ * d * sizeof(float) + TS_NQ * sizeof(float), 256));
-  split_queries_kernel<<<TS_NQ, 256, 0, st>>>(queries, Q, d, eps, q_hi, q_lo, qinv);
+  int* sel = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(gmax) +
+                                    round_up((size_t)TS_NQ * ceil_div(N, TS_BM) * 4 * sizeof(float), 256));
+  float* cand = reinterpret_cast<float*>(sel + TS_NQ * 32);
+  int* counters = reinterpret_cast<int*>(cand + (size_t)TS_NQ * 1024);
+  split_queries_kernel<<<TS_NQ, 256, 0, st>>>(queries, Q, d, eps, q_hi, q_lo, qinv, counters);
   KERNEL_LAUNCHED();
   CUtensorMap tc, th, tl;
   TRY(k_make_map_2d(&tc, corpus, 4, N, d, TS_BM, TS_BK));
@@ -354,14 +432,24 @@ int k_cosine_scan_tc(const float* queries, const float* corpus, const float* cor
   CUDA_TRY(cudaGetDevice(&dev));
   CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const int ntiles = ceil_div(N, TS_BM);
+  // scores == nullptr: the score matrix is not written (the top-k below re-scores the few rows it looks at)
   cosine_scan_tf32x3_kernel<<<ntiles < sms ? ntiles : sms, TS_THREADS, TS_SMEM, st>>>(tc, th, tl, corpus_inv_norm, qinv, Q, N, d,
-                                                                                scores, gmax);
+                                                                                nullptr, gmax);
   KERNEL_LAUNCHED();
   // top-k straight from the group maxima (k <= 32, and the maxima of one query must fit in shared memory)
   const int G = ntiles * 4;
-  ARG_CHECK(k >= 1 && k <= 32 && (size_t)G * 4 <= 200 * 1024, "cosine_scan_tc: k=%d / %d row groups unsupported", k, G);
-  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(topk_from_groups_kernel), 200 * 1024));
-  topk_from_groups_kernel<<<Q, 256, (size_t)G * 4, st>>>(scores, gmax, N, G, k, out_scores, out_idx, idx_base);
+  ARG_CHECK(k >= 1 && k <= 32 && (d == 128 || d == 768) && (size_t)G * 4 <= 200 * 1024,
+            "cosine_scan_tc: k=%d / %d row groups / d=%d unsupported", k, G, d);
+  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(topk_select_groups_kernel), 200 * 1024));
+  topk_select_groups_kernel<<<Q, TK_THREADS, (size_t)G * 4, st>>>(gmax, N, G, k, sel);
+  KERNEL_LAUNCHED();
+  if (d == 768)
+    topk_rescore_kernel<6><<<dim3(k, Q), 256, 0, st>>>(queries, qinv, corpus, corpus_inv_norm, sel, N, k, cand, counters,
+                                                       out_scores, out_idx, idx_base);
+  else
+    topk_rescore_kernel<1><<<dim3(k, Q), 256, 0, st>>>(queries, qinv, corpus, corpus_inv_norm, sel, N, k, cand, counters,
+                                                       out_scores, out_idx, idx_base);
+  (void)scores;
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }

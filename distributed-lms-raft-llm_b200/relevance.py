@@ -5,6 +5,8 @@ exchanged with one all-gather (NCCL over NVLink on GPUs; gloo in the CPU tests) 
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -39,6 +41,52 @@ def exchange_candidates(scores, idx, group=None):
             all_i.permute(1, 0, 2).reshape(Q, ws * k).contiguous())
 
 
+class _Exchange:
+    """This process's NCCL communicator for the candidate exchange, owned by libtutor_b200.so (tutor_nccl_*)."""
+    comm, world, rank = None, 1, 0
+
+
+def _nccl_library_path():
+    """The NCCL PyTorch ships (site-packages/nvidia/nccl/lib/libnccl.so.2); None lets the loader search."""
+    try:
+        import nvidia.nccl
+        for d in list(nvidia.nccl.__path__):
+            p = os.path.join(d, "lib", "libnccl.so.2")
+            if os.path.exists(p):
+                return p
+    except ImportError:
+        pass
+    return None
+
+
+def init_exchange(group=None):
+    """Create the library's own NCCL communicator over the ranks of `group` (default: the world).  The unique id is made
+    on rank 0 and broadcast through torch.distributed; after this, CorpusShard.search runs its exchange as ONE
+    ncclAllGather issued by the C library on the caller's stream (tutor_topk_merge_allgather) instead of two
+    torch.distributed all-gathers and two layout copies issued from Python."""
+    import ctypes as C
+    lib = _lib.load()
+    ws, rank = dist.get_world_size(group), dist.get_rank(group)
+    path = _nccl_library_path()
+    _lib.check(lib.tutor_nccl_load(path.encode() if path else None))
+    uid = C.create_string_buffer(128)
+    if rank == 0:
+        _lib.check(lib.tutor_nccl_unique_id(uid))
+    box = [uid.raw]
+    dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    uid = C.create_string_buffer(box[0], 128)
+    comm = C.c_void_p()
+    _lib.check(lib.tutor_nccl_comm_create(uid, ws, rank, C.byref(comm)))
+    _Exchange.comm, _Exchange.world, _Exchange.rank = comm, ws, rank
+    return comm
+
+
+def close_exchange():
+    if _Exchange.comm is not None:
+        _lib.load().tutor_nccl_comm_destroy(_Exchange.comm)
+        _Exchange.comm, _Exchange.world, _Exchange.rank = None, 1, 0
+
+
 class CorpusShard:
     """One rank's rows [row_lo, row_hi) of the corpus, resident in HBM with their inverse norms."""
 
@@ -50,6 +98,7 @@ class CorpusShard:
         self.row_lo = int(row_lo)
         self.inv_norm = torch.empty((rows.shape[0],), dtype=torch.float32, device=rows.device)
         self._scratch = None
+        self._xscratch = None
         _lib.check(self.lib.tutor_row_inv_norm(self.rows.data_ptr(), self.inv_norm.data_ptr(), rows.shape[0],
                                                rows.shape[1], torch.cuda.current_stream(rows.device).cuda_stream))
 
@@ -71,6 +120,17 @@ class CorpusShard:
     def search(self, queries: torch.Tensor, k: int, group=None):
         """Global top-k over every rank's shard: local top-k, all-gather of [Q,k] candidates, device merge."""
         scores, idx = self.topk(queries, k)
+        if _Exchange.comm is not None and _Exchange.world > 1 and scores.is_cuda:
+            # the C library's own exchange: pack -> one ncclAllGather -> merge, all on the current stream
+            ws, Q = _Exchange.world, scores.shape[0]
+            need = self.lib.tutor_topk_merge_allgather_scratch_bytes(Q, k, ws)
+            if self._xscratch is None or self._xscratch.numel() < need:
+                self._xscratch = torch.empty((need,), dtype=torch.uint8, device=scores.device)
+            out_s, out_i = torch.empty_like(scores), torch.empty_like(idx)
+            _lib.check(self.lib.tutor_topk_merge_allgather(_Exchange.comm, scores.data_ptr(), idx.data_ptr(), Q, k, ws,
+                                                           self._xscratch.data_ptr(), out_s.data_ptr(), out_i.data_ptr(),
+                                                           torch.cuda.current_stream(scores.device).cuda_stream))
+            return out_s, out_i
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
             return scores, idx
         ws = dist.get_world_size(group)

@@ -147,6 +147,20 @@ int tutor_cosine_topk(const float* queries_dev, const float* corpus_dev, const f
 int tutor_topk_merge(const float* cand_scores_dev, const int32_t* cand_idx_dev, int Q, int ncand, int k,
                      float* out_scores_dev, int32_t* out_idx_dev, void* stream);
 
+/* The exchange step of the sharded search on GPUs (SURVEY.md section 8b "topk_merge_allgather(ncclComm_t, ...)"; the
+ * reference itself compares against one text, REF/lms_server.py:1254-1266, and has no collective): every rank's [Q,k]
+ * candidates -> one ncclAllGather of 8-byte (score, row) elements on `stream` -> merge on every rank.  NCCL is bound at
+ * run time: tutor_nccl_load(path or NULL) dlopens the library (the one PyTorch ships), rank 0 makes a unique id, every
+ * rank creates its communicator from it (the id travels by any side channel, e.g. torch.distributed).  scratch holds
+ * tutor_topk_merge_allgather_scratch_bytes(Q, k, world) bytes.  k <= 32, world * k <= 256.  Capturable in a CUDA graph. */
+int tutor_nccl_load(const char* path);
+int tutor_nccl_unique_id(void* id128 /* 128 bytes, host */);
+int tutor_nccl_comm_create(const void* id128, int world, int rank, void** comm);
+void tutor_nccl_comm_destroy(void* comm);
+size_t tutor_topk_merge_allgather_scratch_bytes(int Q, int k, int world);
+int tutor_topk_merge_allgather(void* comm, const float* scores, const int32_t* idx, int Q, int k, int world, void* scratch,
+                               float* out_scores, int32_t* out_idx, void* stream);
+
 /* ----------------------------------------------------------------------------------------------------------
  * Single kernels, for unit tests and ncu (device pointers, caller's stream).  Each stands in for the ATen op
  * listed in SURVEY.md §2.2.                                                                                   */

@@ -26,17 +26,43 @@ for start in range(0, N, 100_000):
 queries = torch.randn(Q, 768, generator=g)
 shard = lms_b200.CorpusShard(torch.cat(rows).cuda(), row_lo=lo)
 qd = queries.cuda()
+s_py, i_py = shard.search(qd, k)        # exchange through torch.distributed (two all-gathers + layout copies)
+lms_b200.init_exchange()                 # from here on: the library's own ncclAllGather of packed candidates
 s, i = shard.search(qd, k)
 torch.cuda.synchronize()
+assert torch.equal(i, i_py) and torch.equal(s, s_py), "the two exchange paths disagree"
 dist.barrier()
-e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-e0.record()
-for _ in range(5):
-    s, i = shard.search(qd, k)
-e1.record()
-torch.cuda.synchronize()
-ms = torch.tensor([e0.elapsed_time(e1) / 5], device="cuda")
-dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+
+
+def timed(fn, n=20):
+    fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / n], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t
+
+
+ms = timed(lambda: shard.search(qd, k))
+# the same search captured once and replayed: scan -> top-k -> pack -> all-gather -> merge as one CUDA graph
+side = torch.cuda.Stream()
+graph = torch.cuda.CUDAGraph()
+with torch.cuda.stream(side):
+    shard.search(qd, k)
+    side.synchronize()
+    with torch.cuda.graph(graph, stream=side):
+        gs, gi = shard.search(qd, k)
+    ms_graph = timed(graph.replay)
+assert torch.equal(gi, i) and torch.equal(gs, s)
+if rank == 0:
+    print(f"eager {ms.item() * 1e3:.1f} us, CUDA graph {ms_graph.item() * 1e3:.1f} us per search")
+ms = ms_graph
 if rank == 0:
     g = torch.Generator().manual_seed(3)
     full = torch.cat([torch.randn(min(100_000, N - st), 768, generator=g) for st in range(0, N, 100_000)])
