@@ -77,6 +77,8 @@ SIGNATURES = {
     "tutor_attn_prefill": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                                    c_void_p]),
     "tutor_attn_decode": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "tutor_attn_decode_fused": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
+                                        c_void_p]),
     "tutor_lmhead_scratch_bytes": (c_size_t, [c_int]),
     "tutor_lmhead_argmax": (c_int, [c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_float, c_void_p,
                                     c_void_p, c_void_p]),

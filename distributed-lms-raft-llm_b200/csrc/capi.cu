@@ -181,6 +181,15 @@ int tutor_attn_decode(int dtype, const void* q, const void* k, const void* v, vo
   return k_attn_decode(q, dtype, k, v, dtype, out, dtype, B, H, Smax, nullptr, len, nullptr, (cudaStream_t)stream);
 }
 
+int tutor_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias, void* k, void* v, void* out, int B,
+                            int H, int Smax, int len, void* stream) {
+  ARG_CHECK(qkv_partial && qkv_bias && k && v && out, "attn_decode_fused: null argument");
+  ARG_CHECK(len >= 1 && len <= Smax, "attn_decode_fused: len %d outside [1,%d]", len, Smax);
+  const int safe = ((len - 1 < 128 ? len - 1 : 128) / 64) * 64;  // what the engine allows to stream ahead of the wait
+  return k_attn_decode_fused(qkv_partial, ks, qkv_bias, k, v, DT_BF16, out, DT_BF16, B, H, Smax, nullptr, len, 1, nullptr,
+                             nullptr, safe, len, (cudaStream_t)stream);
+}
+
 size_t tutor_lmhead_scratch_bytes(int B) { return k_lmhead_scratch_bytes(B, 0); }
 
 int tutor_lmhead_argmax(int dtype, const void* x, const void* wte, int B, int V, int d, const uint32_t* seen,

@@ -177,6 +177,12 @@ int tutor_attn_prefill(int dtype, const void* q_dev, const void* k_dev, const vo
                        int T, int Smax, int causal, void* stream);
 int tutor_attn_decode(int dtype, const void* q_dev, const void* k_dev, const void* v_dev, void* out_dev, int B, int H,
                       int Smax, int len, void* stream);
+/* The instance the bf16 decode step actually launches (GPT2Attention.forward at T = 1, modeling_gpt2.py:185-226 with
+ * DynamicLayer.update, cache_utils.py:102-121): sums the ks split-K partials [ks][B][3*H*64] of c_attn in a fixed order,
+ * adds the bias, appends the new K/V row at cache position len-1 (bf16 cache, written in place) and attends over rows
+ * [0, len).  out bf16 [B, H*64].  Exposed for unit tests, ncu and bench.py's roofline leg.                      */
+int tutor_attn_decode_fused(const float* qkv_partial_dev, int ks, const float* qkv_bias_dev, void* k_dev, void* v_dev,
+                            void* out_dev, int B, int H, int Smax, int len, void* stream);
 /* Fused LM head + repetition penalty + argmax (modeling_gpt2.py:705; logits_process.py:404-410;
  * utils.py:2793): x [B,d] (fp32 for F32, bf16 for BF16) against wte [V,d]; seen_dev [B, ceil(V/32)] bitmap of
  * ids to penalise (may be null when penalty == 1); out_idx_dev [B] int32.  scratch_dev of

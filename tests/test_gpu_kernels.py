@@ -136,6 +136,31 @@ def test_attn_decode(pkg, lib, dtype, B, H, S):
     assert (out.float() - ref).abs().max().item() < tol
 
 
+@pytest.mark.parametrize("B,H,S,ks", [(1, 2, 5, 1), (5, 12, 130, 3), (64, 12, 640, 6), (16, 20, 961, 4)])
+def test_attn_decode_fused(pkg, lib, B, H, S, ks):
+    """The decode step's own attention instance: split-K partials of c_attn summed in order + bias, K/V row appended at
+    position S-1, attention over S rows - against fp64 SDPA on the same (bf16-rounded) q, k, v."""
+    g = torch.Generator().manual_seed(S + ks)
+    d = H * 64
+    Smax = (S + 63) // 64 * 64
+    part = (torch.randn(ks, B, 3 * d, generator=g) * 0.5).to(DEV)
+    bias = (torch.randn(3 * d, generator=g) * 0.1).to(DEV)
+    k = torch.randn(B, H, Smax, 64, generator=g).to(DEV).bfloat16()
+    v = torch.randn(B, H, Smax, 64, generator=g).to(DEV).bfloat16()
+    k0, v0 = k.clone(), v.clone()
+    out = torch.empty(B, d, device=DEV, dtype=torch.bfloat16)
+    pkg._lib.check(lib.tutor_attn_decode_fused(ptr(part), ks, ptr(bias), ptr(k), ptr(v), ptr(out), B, H, Smax, S, None))
+    sync()
+    qkv = bias.clone()[None].repeat(B, 1)
+    for z in range(ks):  # the kernel's summation order
+        qkv = qkv + part[z]
+    q, kn, vn = qkv[:, :d], qkv[:, d:2 * d].bfloat16(), qkv[:, 2 * d:].bfloat16()
+    assert torch.equal(k[:, :, S - 1], kn.view(B, H, 64)) and torch.equal(v[:, :, S - 1], vn.view(B, H, 64)), "cache append"
+    assert torch.equal(k[:, :, :S - 1], k0[:, :, :S - 1]) and torch.equal(k[:, :, S:], k0[:, :, S:]), "other rows untouched"
+    ref = _sdpa_ref(q.view(B, 1, H, 64), k[:, :, :S], v[:, :, :S], 0)
+    assert (out.float().view(B, 1, H, 64) - ref).abs().max().item() < 2e-2
+
+
 @pytest.mark.parametrize("dtype,B,V,d", [(F32, 1, 50257, 768), (F32, 4, 1000, 128), (F32, 11, 5000, 256),
                                          (BF16, 1, 1000, 128), (BF16, 64, 50257, 768), (BF16, 16, 50257, 1280),
                                          (BF16, 100, 3000, 128)])
