@@ -35,6 +35,15 @@ WORKLOAD = ("configs[2]: GPT-2 small bf16, 64 requests/GPU x (512-token prompt -
             "random-init weights, synthetic ids")
 
 
+def log(msg):
+    """progress on stderr (the JSON line is the only thing on stdout)"""
+    if os.environ.get("TUTOR_BENCH_VERBOSE"):
+        print(f"[bench rank {os.environ.get('RANK', '0')} +{time.perf_counter() - T0:.1f}s] {msg}", file=sys.stderr, flush=True)
+
+
+T0 = time.perf_counter()
+
+
 def config(world, new=NEW):
     """The same dict in both arms (the reference arm computes in fp32 on the host; see `dtype`)."""
     return {"workload": WORKLOAD, "requests_per_gpu": B_PER_GPU, "prompt_len": T_PROMPT, "new_tokens": new,
@@ -361,9 +370,13 @@ def leg_cfg4(pkg, rp, torch, pk, local, world, rank, with_cpu):
     shard = pkg.CorpusShard(torch.cat(rows), row_lo=lo)
     del rows
     qd = queries.cuda()
+    log(f"cfg4: shard rows [{lo}, {hi}) resident")
     if world > 1:
         pkg.init_exchange()
+        log("cfg4: exchange communicator up")
     shard.search(qd, k)
+    torch.cuda.synchronize()
+    log("cfg4: first search done")
     side = torch.cuda.Stream()
     graph = torch.cuda.CUDAGraph()
     with torch.cuda.stream(side):
@@ -373,6 +386,7 @@ def leg_cfg4(pkg, rp, torch, pk, local, world, rank, with_cpu):
             gs, gi = shard.search(qd, k)
         graph.replay()
         side.synchronize()
+        log("cfg4: graph captured and replayed once")
         if world > 1:
             dist.barrier()
         with ClockSampler(local) as clocks:
@@ -386,8 +400,19 @@ def leg_cfg4(pkg, rp, torch, pk, local, world, rank, with_cpu):
     if world > 1:
         dist.all_reduce(us, op=dist.ReduceOp.MAX)
     us = us.item()
+    log(f"cfg4: timed, {us:.1f} us per search")
+    gs, gi = gs.clone(), gi.clone()
+    del graph  # NCCL keeps a communicator alive while a captured graph still refers to it: ncclCommDestroy would wait
+    if world > 1:  # every rank tears its communicator down together, before rank 0 goes off to check against the oracle
+        import gc
+        gc.collect()
+        torch.cuda.synchronize()
+        dist.barrier()
+        pkg.close_exchange()
+        log("cfg4: exchange communicator closed")
     res = None
     if rank == 0:
+        host_threads()
         bytes_per_gpu = (hi - lo) * 768 * 4
         res = {"workload": f"configs[4]: 1M x 768 fp32 corpus sharded over {world} GPU(s), 32 queries, top-10"
                            + ("; per-GPU scan + top-k, one ncclAllGather of packed candidates, merge; one CUDA graph" if world > 1 else ""),
@@ -405,8 +430,6 @@ def leg_cfg4(pkg, rp, torch, pk, local, world, rank, with_cpu):
         if with_cpu:
             res["cpu_baseline"] = {"value": Q / t_cpu, "unit": "queries/s", "kind": "reference",
                                    "sample": "the whole 1 M-row search: torch normalise + matmul + topk on the host (oracle.corpus_topk)"}
-    if world > 1:
-        pkg.close_exchange()
     return res
 
 
@@ -516,6 +539,7 @@ def main():
     step_bytes = sum(eng.decode_bytes(B_PER_GPU, T_PROMPT + i) for i in range(1, new)) / max(1, new - 1)
     step_gbs = step_bytes / (ms_decode * 1e-3) / 1e9
 
+    log(f"headline timed: {value:.0f} tok/s")
     line = None
     if rank == 0:
         line = {

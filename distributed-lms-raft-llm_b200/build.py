@@ -13,6 +13,8 @@ LIB = os.path.join(HERE, "libtutor_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--expt-relaxed-constexpr",
          "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
+if os.environ.get("TUTOR_EXPERIMENTS"):  # A/B knobs for tools/ (csrc/common.cuh); never set for the shipped library
+    FLAGS.append("-DTUTOR_EXPERIMENTS")
 
 
 def sources():

@@ -726,6 +726,7 @@ __global__ void __launch_bounds__(128) attn_prefill_mma_kernel(const bf16* __res
 }
 
 
+#ifdef TUTOR_EXPERIMENTS  // measured no faster than the SIMT consumers (see use_mma_decode): not in the shipped library
 // ------------------------------------------------------------------- decode on tensor cores (bf16)
 // Same producer / ring structure as attn_decode_tma_kernel, with the arithmetic moved to mma.sync m16n8k16: the
 // SIMT consumers needed ~50 instructions per key per lane (unpack, FMA, shuffles) and held the kernel at 80 % of
@@ -970,10 +971,11 @@ __global__ void __launch_bounds__(DM_THREADS, 6) attn_decode_mma_kernel(
 // same ring in 20.4-20.6 us without arithmetic and take 27.1 us under ncu: what is left is the per-CTA prologue and
 // epilogue latency of a one-wave launch, which neither fewer instructions nor more (smaller) CTAs remove.
 bool use_mma_decode() {
-  static const bool mma = getenv("TUTOR_ATTN_MMA") != nullptr;
+  static const bool mma = tutor_experiment("TUTOR_ATTN_MMA") != nullptr;
   return mma;
 }
 
+#endif  // TUTOR_EXPERIMENTS
 }  // namespace
 
 // number of key-range splits: enough CTAs for ~8 per SM, at least 64 keys per split
@@ -1003,7 +1005,7 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
   dim3 grid(H, B), block(128);
   // the fp32 kernel is launched without the programmatic-launch attribute unless TUTOR_ATTN_PDL=1: with it the batch-1
   // decode forward measured 392 us against 381 us (its dependents' early weight loads compete with this kernel)
-  static const bool f32_plain = getenv("TUTOR_ATTN_PDL") == nullptr;
+  static const bool f32_plain = tutor_experiment("TUTOR_ATTN_PDL") == nullptr;
   if (q_dtype == DT_F32 && kv_dtype == DT_F32 && out_dtype == DT_F32 && f32_plain)
     attn_decode_kernel<float, float, float, false, false><<<grid, block, 0, st>>>(
         (const float*)q, (float*)k, (float*)v, (float*)out, H, Smax, len_dev, len_host, nullptr, 0, nullptr, B, nullptr,
@@ -1014,6 +1016,7 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
                           (float*)k, (float*)v, (float*)out, H, Smax, len_dev, len_host, (const float*)nullptr, 0,
                           (const float*)nullptr, B, (float*)nullptr, (int*)nullptr, npad));
   else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16) {
+#ifdef TUTOR_EXPERIMENTS
     if (use_mma_decode()) {
       CUtensorMap tk, tv;  // the cache as a [B*H*Smax, 64] bf16 matrix, 64-row boxes, 128-byte swizzle
       TRY(k_make_map_bf16(&tk, (const bf16*)k, B * H * Smax, 64, DM_CHUNK));
@@ -1021,7 +1024,9 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
       attn_decode_mma_kernel<false, true><<<grid, DM_THREADS, 0, st>>>(tk, tv, (const bf16*)q, (bf16*)k, (bf16*)v, (bf16*)out, H,
                                                                  Smax, len_dev, len_host, nullptr, 0, nullptr, B, npad, 0,
                                                                  0, nullptr, nullptr);
-    } else {
+    } else
+#endif
+    {
       attn_decode_tma_kernel<false, 64, 2, true><<<grid, DK_THREADS, 0, st>>>((const bf16*)q, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax,
                                                                  len_dev, len_host, nullptr, 0, nullptr, B, npad, 0);
     }
@@ -1044,6 +1049,7 @@ int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias,
   ARG_CHECK(nsplit >= 1 && nsplit <= 8 && (nsplit == 1 || split_scratch), "attn_decode_fused: bad split setup");
   float* sc = reinterpret_cast<float*>(split_scratch);
   int* counters = reinterpret_cast<int*>(sc + (size_t)B * H * 8 * 66);  // zeroed by the owner; self-resetting
+#ifdef TUTOR_EXPERIMENTS
   if (use_mma_decode()) {
     CUtensorMap tk, tv;
     TRY(k_make_map_bf16(&tk, (const bf16*)k, B * H * Smax, 64, DM_CHUNK));
@@ -1056,6 +1062,7 @@ int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias,
     KERNEL_LAUNCHED();
     return TUTOR_OK;
   }
+#endif
   if (nsplit == 1) {
     CUDA_TRY(tutor_launch(attn_decode_tma_kernel<true, 64, 2, true>, dim3(H, B), dim3(DK_THREADS), 0, st, (const bf16*)nullptr,
                           (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B,

@@ -30,6 +30,7 @@ void tutor_set_error(const char* fmt, ...) {
 }
 
 int tutor_cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  cudaGetLastError();  // a failed call (e.g. an allocation that did not fit) must not resurface at the next launch check
   const char* base = strrchr(file, '/');
   tutor_set_error("CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), base ? base + 1 : file, line, what);
   return TUTOR_ERR_CUDA;

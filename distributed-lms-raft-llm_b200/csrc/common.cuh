@@ -89,6 +89,17 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 #endif
 
+// A/B knobs that select paths measured slower than the default, or (TUTOR_SKIP) that drop kernels and produce meaningless
+// tokens, exist only in builds made with -DTUTOR_EXPERIMENTS (TUTOR_EXPERIMENTS=1 python -m ...build, used by tools/):
+// the shipped library has one path per shape.  Knobs that select another CORRECT path and are exercised by the tests
+// (TUTOR_NO_FUSED, TUTOR_NO_CLUSTER, TUTOR_NO_PDL, TUTOR_NO_GRAPH, TUTOR_ATTN_SPLITS, TUTOR_MEGA) stay.
+#ifdef TUTOR_EXPERIMENTS
+#include <cstdlib>
+static inline const char* tutor_experiment(const char* name) { return getenv(name); }
+#else
+static inline const char* tutor_experiment(const char*) { return nullptr; }
+#endif
+
 enum { ACT_NONE = 0, ACT_GELU_TANH = 1, ACT_GELU_ERF = 2 };
 enum { DT_F32 = 0, DT_BF16 = 1 };
 

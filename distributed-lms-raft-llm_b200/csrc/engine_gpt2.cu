@@ -246,7 +246,7 @@ DecodePlan decode_plan(const tutor_gpt2* e, int B) {
   const int d = e->d, cap = e->num_sms * 4 / 3;
   DecodePlan p;
   p.bn_qkv = p.bn_fc = p.bn_res = 16;
-  auto env = [](const char* name, int& v) { if (const char* s = getenv(name)) v = atoi(s); };
+  auto env = [](const char* name, int& v) { if (const char* s = tutor_experiment(name)) v = atoi(s); };
   env("TUTOR_BN_QKV", p.bn_qkv); env("TUTOR_BN_FC", p.bn_fc); env("TUTOR_BN_RES", p.bn_res);  // A/B knobs
   p.ks_qkv = k_pick_cluster_splitk(3 * d, d, ceil_div(B, p.bn_qkv), cap);
   p.ks_proj = k_pick_cluster_splitk(d, d, ceil_div(B, p.bn_res), cap);
@@ -274,7 +274,7 @@ int forward_decode_cluster(tutor_gpt2* e, int lane, int b0, int B) {
   const size_t kv_off = (size_t)b0 * e->H * e->Smax * 64 * e->esz();
   const int* npad = e->padded ? e->npad + b0 : nullptr;
   const DecodePlan pl = decode_plan(e, B);
-  const char* skip = getenv("TUTOR_SKIP") ? getenv("TUTOR_SKIP") : "";
+  const char* skip = tutor_experiment("TUTOR_SKIP") ? tutor_experiment("TUTOR_SKIP") : "";
   const int bn_qkv = pl.bn_qkv, bn_fc = pl.bn_fc, bn_res = pl.bn_res;
   const int ks_qkv = pl.ks_qkv, ks_proj = pl.ks_proj, ks_fc = pl.ks_fc, ks_proj2 = pl.ks_proj2;
   TRY(k_gpt2_embed(e->ids + (size_t)b0 * e->ids_ld, e->ids_ld, len, 1, e->wte, e->dt, e->wpe, d, x, B, npad, st));
@@ -350,7 +350,7 @@ int mega_prepare(tutor_gpt2* e, int B) {
   MegaParams mp{};
   mp.B = B; mp.d = d; mp.H = e->H; mp.L = L; mp.Smax = e->Smax;
   int G = B >= 32 ? 2 : 1;
-  if (const char* s = getenv("TUTOR_MEGA_GROUPS")) G = atoi(s) < 1 ? 1 : (atoi(s) > 4 ? 4 : atoi(s));
+  if (const char* s = tutor_experiment("TUTOR_MEGA_GROUPS")) G = atoi(s) < 1 ? 1 : (atoi(s) > 4 ? 4 : atoi(s));
   if (G > B) G = B;
   while (ceil_div(B, G) > 64) ++G;  // a row group is one UMMA N tile: at most 64 rows
   mp.G = G; mp.rpg = ceil_div(B, G);
@@ -360,7 +360,7 @@ int mega_prepare(tutor_gpt2* e, int B) {
   const int nout[4] = {3 * d, d, 4 * d, d}, kin[4] = {d, d, d, 4 * d};
   int rot = 0;
   int team = nctas / G;  // CTAs whose GEMM engine serves one row group
-  if (const char* s = getenv("TUTOR_MEGA_TEAM")) team = atoi(s) < 1 ? 1 : (atoi(s) < team ? atoi(s) : team);
+  if (const char* s = tutor_experiment("TUTOR_MEGA_TEAM")) team = atoi(s) < 1 ? 1 : (atoi(s) < team ? atoi(s) : team);
   mp.team = team;
   for (int ph = 0; ph < 4; ++ph) {
     mp.nout[ph] = nout[ph];
@@ -446,7 +446,7 @@ int forward_decode_mega(tutor_gpt2* e, int B) {
   mp.trace_cta = m.trace_cta;
   mp.step_begin = 0; mp.step_end = m.nsteps;
   mp.attn_begin = 0; mp.attn_end = e->L * B * e->H; mp.attn_wait = 1;
-  mp.l2_prefetch = getenv("TUTOR_MEGA_L2PF") != nullptr;  // measured slower: 774 vs 662 us (the prefetch traffic delays the chain)
+  mp.l2_prefetch = tutor_experiment("TUTOR_MEGA_L2PF") != nullptr;  // measured slower: 774 vs 662 us (the prefetch traffic delays the chain)
   TRY(k_decode_mega(mp, m.gn, e->num_sms, st));
   return k_lmhead_argmax(e->xn_last, e->dt, e->wte, e->dt, B, e->V, e->d, e->dstate(), e->lm_scratch, st);
 }
@@ -494,10 +494,13 @@ int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
     ++e->alloc_epoch;
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     const int nb = B > e->Bcap ? B : e->Bcap, ns = Smax > e->Smax ? Smax : e->Smax;
-    if (e->kv) CUDA_TRY(cudaFree(e->kv));
-    e->kv = nullptr;
+    // From here until the last allocation succeeds the engine has NO capacity: if one of them fails, the next request -
+    // however small - comes back through this branch and allocates everything again, instead of running on freed or
+    // half-replaced buffers.
+    e->Bcap = 0; e->Smax = 0;
+    dev_free(e->kv);
     const size_t bytes = (size_t)e->L * 2 * nb * e->H * ns * 64 * es;
-    CUDA_TRY(cudaMalloc(&e->kv, bytes));
+    TRY(dev_alloc(&e->kv, bytes));
     // rows past the current length are read (masked) by the attention kernels: they must hold finite values
     CUDA_TRY(cudaMemsetAsync(e->kv, 0, bytes, e->stream));
     dev_free(e->ids); dev_free(e->seen); dev_free(e->finished); dev_free(e->lm_scratch); dev_free(e->xn_last);
@@ -539,6 +542,7 @@ int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
     drop_graph(e);
     ++e->alloc_epoch;
     CUDA_TRY(cudaStreamSynchronize(e->stream));
+    e->Mcap = 0;  // same rule as above
     dev_free(e->x); dev_free(e->xn); dev_free(e->q); dev_free(e->att); dev_free(e->hbuf);
     const size_t d = e->d;
     TRY(dev_alloc(&e->x, (size_t)M * d * 4));
@@ -712,13 +716,13 @@ int tutor_gpt2_create(const tutor_gpt2_config* cfg, int device, tutor_gpt2_t** o
   e->use_cluster = getenv("TUTOR_NO_CLUSTER") == nullptr;
   if (const char* mm = getenv("TUTOR_MEGA")) e->mega_mode = atoi(mm);
   if (!e->use_cluster) e->mega_mode = 0;
-  e->use_ln_gemv = getenv("TUTOR_LN_GEMV") != nullptr;
-  e->no_ln_gemv = getenv("TUTOR_NO_LN_GEMV") != nullptr;
+  e->use_ln_gemv = tutor_experiment("TUTOR_LN_GEMV") != nullptr;
+  e->no_ln_gemv = tutor_experiment("TUTOR_NO_LN_GEMV") != nullptr;
   {
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) e->num_sms = prop.multiProcessorCount;
   }
-  if (const char* nl = getenv("TUTOR_LANES")) e->cfg_lanes = atoi(nl);
+  if (const char* nl = tutor_experiment("TUTOR_LANES")) e->cfg_lanes = atoi(nl);
   if (e->cfg_lanes < 1) e->cfg_lanes = 1;
   if (e->cfg_lanes > tutor_gpt2::MAX_LANES) e->cfg_lanes = tutor_gpt2::MAX_LANES;
   bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess;

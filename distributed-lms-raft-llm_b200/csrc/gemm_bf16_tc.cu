@@ -972,16 +972,16 @@ int k_gemm_bf16(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpi
   // few rows: the weight matrix as the 128-row UMMA operand, the rows as its N dimension.  Above TUTOR_SWAP_MAX_M rows
   // (default 32) the row-major kernel's single row tile is faster: a 128-token BERT query took 2.7 ms through the
   // swapped kernel's per-element epilogue.
-  static const int swap_max = getenv("TUTOR_SWAP_MAX_M") ? atoi(getenv("TUTOR_SWAP_MAX_M")) : 32;
+  static const int swap_max = tutor_experiment("TUTOR_SWAP_MAX_M") ? atoi(tutor_experiment("TUTOR_SWAP_MAX_M")) : 32;
   if (M <= (swap_max < 128 ? swap_max : 128)) return launch_swapped<EPI_SWAPPED>(W, N, A, M, K, epi, am, st);
   // 128x256 tiles halve the operand bytes per FLOP of 128x128 ones (the 128x128 kernel measured L2-bandwidth
   // bound: 32 KB of operands per 4 MMAs = 6.2 TB/s at 410 TFLOP/s); two 97 KB CTAs still share an SM
-  static const bool wide = getenv("TUTOR_GEMM_BN128") == nullptr;
-  static const bool persistent = getenv("TUTOR_GEMM_NONPERSISTENT") == nullptr;  // debugging aid / A-B measurements
-  static const bool tma_epi = getenv("TUTOR_GEMM_NO_TMA_EPILOGUE") == nullptr;  // A/B measurements
+  static const bool wide = tutor_experiment("TUTOR_GEMM_BN128") == nullptr;
+  static const bool persistent = tutor_experiment("TUTOR_GEMM_NONPERSISTENT") == nullptr;  // debugging aid / A-B measurements
+  static const bool tma_epi = tutor_experiment("TUTOR_GEMM_NO_TMA_EPILOGUE") == nullptr;  // A/B measurements
   if (persistent && tma_epi && N >= 128 && tma_epilogue_ok(epi, M, N)) {
     // long K: the mainloop hides an 8-warp epilogue and gains a 4th pipeline stage (TUTOR_GEMM_EW16=1 forces 16 warps)
-    static const bool ew16 = getenv("TUTOR_GEMM_EW16") != nullptr;
+    static const bool ew16 = tutor_experiment("TUTOR_GEMM_EW16") != nullptr;
     if (K >= 2048 && !ew16) return launch_persistent_tma<8>(A, M, W, N, K, epi, st);
     return launch_persistent_tma<16>(A, M, W, N, K, epi, st);
   }

@@ -306,7 +306,7 @@ template <int MB, bool LN>
 int launch_gemv_reg(const float* X, const float* gamma, const float* beta, float eps, const float* W, int N, int K,
                     const GemmEpilogue& epi, float* xn_out, cudaStream_t st) {
   const dim3 block(256);
-  static const bool plain = getenv("TUTOR_GEMV_PLAIN") != nullptr;  // A/B: one warp per column everywhere
+  static const bool plain = tutor_experiment("TUTOR_GEMV_PLAIN") != nullptr;  // A/B: one warp per column everywhere
   if constexpr (LN) {
     if (!plain && K == 768 && N >= 2048 && !xn_out) {  // ln_2 + c_fc: two columns per warp
       CUDA_TRY(tutor_launch(gemv_f32_reg2_kernel<MB, 6, true, 2, 1>, dim3(ceil_div(N, 16)), block, 0, st, X, gamma, beta, eps,

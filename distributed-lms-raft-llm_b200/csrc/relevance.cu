@@ -389,7 +389,7 @@ int k_cosine_topk(const float* queries, const void* corpus, int corpus_dtype, co
   p += round_up((size_t)Q * nchunks * k * sizeof(int32_t), 256);
   void* tc_scratch = p;
   const float eps = 1e-8f;
-  static const bool use_tc = getenv("TUTOR_SCAN_SIMT") == nullptr;  // A/B: the fp32 FFMA2 scan below
+  static const bool use_tc = tutor_experiment("TUTOR_SCAN_SIMT") == nullptr;  // A/B: the fp32 FFMA2 scan below
   if (use_tc && Q <= 32 && (d == 128 || d == 768) && k <= 32 && (size_t)ceil_div(N, 128) * 16 <= 200 * 1024)
     return k_cosine_scan_tc(queries, (const float*)corpus, corpus_inv_norm, Q, N, d, eps, scores, tc_scratch, k, out_scores,
                             out_idx, idx_base, st);

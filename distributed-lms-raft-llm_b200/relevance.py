@@ -82,6 +82,9 @@ def init_exchange(group=None):
 
 
 def close_exchange():
+    """Destroy the communicator.  Every rank must call this together, and any CUDA graph that captured a search through it
+    must have been deleted first: NCCL keeps a communicator alive while a captured graph still refers to it, and
+    ncclCommDestroy then waits for ever."""
     if _Exchange.comm is not None:
         _lib.load().tutor_nccl_comm_destroy(_Exchange.comm)
         _Exchange.comm, _Exchange.world, _Exchange.rank = None, 1, 0

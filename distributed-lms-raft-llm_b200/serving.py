@@ -79,15 +79,23 @@ def add_to_server(servicer, server):
     server.add_generic_rpc_handlers((grpc.method_handlers_generic_handler("lms.Tutoring", {"GetLLMAnswer": handler}),))
 
 
-def serve(model, tokenizer, address="[::]:50054", max_workers=10):
-    """REF/tutoring_server.py:39-49 (same port, same 10-thread pool); returns the started server."""
+def serve(model, tokenizer, address="[::]:50054", max_workers=10, batching=True, max_batch=64, max_wait_ms=4.0):
+    """REF/tutoring_server.py:39-49 (same port, same 10-thread pool); returns the started server.
+
+    The engine serialises its callers (one generation at a time per engine instance), so with the reference's ten handler
+    threads each request would wait for the ones before it at ~20 ms apiece.  By default the model is therefore wrapped in
+    a BatchingModel: concurrent requests run as ONE left-padded batch and each caller gets exactly its batch-1 result.
+    `batching=False` passes the model through untouched (e.g. when the caller already wrapped it)."""
     import grpc
 
+    if batching and not isinstance(model, BatchingModel) and hasattr(model, "_resolve"):
+        model = BatchingModel(model, max_batch=max_batch, max_wait_ms=max_wait_ms)
     server = grpc.server(futures.ThreadPoolExecutor(max_workers=max_workers))
     add_to_server(TutoringService(model, tokenizer), server)
     port = server.add_insecure_port(address)
     server.start()
     server.bound_port = port
+    server.model = model
     return server
 
 

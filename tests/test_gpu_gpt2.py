@@ -369,3 +369,33 @@ def test_persistent_decode_kernel_matches_launch_chain(pkg, tiny_hf, monkeypatch
         ref = tiny_hf(outs[1][0][:, :T + 1]).logits[:, -1].float()  # fp32 oracle at the context of that step
     assert ((logits[1] - ref).abs().max() / ref.abs().max()).item() < 5e-2 or not torch.equal(outs[0][0][:, :T + 1], outs[1][0][:, :T + 1])
     assert torch.equal(outs[1][0], outs[1][1]), "the persistent kernel must be run-to-run deterministic"
+
+
+def test_long_prompt_then_short_prompt_on_one_bf16_engine(pkg, tiny_hf):
+    """The captured decode graph bakes in how many prompt rows the attention may stream ahead of its wait.  A long prompt
+    followed by a short one on the SAME engine must not replay the long prompt's bound (advisor finding, round 1): the
+    short generation equals a fresh engine's."""
+    long_ids = rp.gpt2_prompt_ids(3, 140, seed=31, vocab=1000)
+    short_ids = rp.gpt2_prompt_ids(3, 20, seed=32, vocab=1000)
+    kw = dict(max_new_tokens=24, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
+    eng = pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="bf16")
+    eng.generate(long_ids, **kw)
+    again = eng.generate(short_ids, **kw)
+    fresh = pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="bf16").generate(short_ids, **kw)
+    assert torch.equal(again, fresh)
+    assert torch.equal(eng.generate(long_ids, **kw), pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="bf16").generate(long_ids, **kw))
+
+
+def test_allocation_failure_leaves_the_engine_usable(pkg, tiny_hf):
+    """A request whose KV cache cannot be allocated fails with an error, and the next (small) request on the same engine
+    still runs correctly - capacity bookkeeping is reset before anything is freed (engine_gpt2.cu ensure_capacity)."""
+    eng = pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="fp32")
+    small = rp.gpt2_prompt_ids(2, 9, seed=33, vocab=1000)
+    kw = dict(max_new_tokens=10, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
+    before = eng.generate(small, **kw)
+    huge = torch.zeros((1_500_000, 4), dtype=torch.int64)  # 2 layers x 2 x 1.5 M rows x 2 heads x 256 x 64 fp32 = 393 GB of cache
+    with pytest.raises(pkg._lib.TutorError):
+        eng.generate(huge, max_new_tokens=250, eos_token_id=999, pad_token_id=999)
+    after = eng.generate(small, **kw)
+    assert torch.equal(before, after)
+    assert torch.equal(after, rp.generate(tiny_hf, small, **kw))

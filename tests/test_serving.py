@@ -75,10 +75,14 @@ def test_grpc_drop_in_with_engine(pkg, golden):
     server = serving.serve(eng, tok, address="127.0.0.1:0")
     try:
         addr = f"127.0.0.1:{server.bound_port}"
+        queries = [str(g[f"query_{i}"]) for i in range(3)]  # read here: an NpzFile must not be read from several threads
+        texts = [str(g[f"text_{i}"]) for i in range(3)]
         with ThreadPoolExecutor(6) as ex:  # concurrent clients, like the LMS leader's handler threads
-            rs = list(ex.map(lambda i: serving.call(addr, "t", str(g[f"query_{i % 3}"])), range(6)))
+            rs = list(ex.map(lambda i: serving.call(addr, "t", queries[i % 3]), range(6)))
         for i, r in enumerate(rs):
-            assert r.success and r.response == str(g[f"text_{i % 3}"])  # identical to the unmodified reference's text
+            assert r.success and r.response == texts[i % 3]  # identical to the unmodified reference's text
+        # serve() put the micro-batching queue in front of the engine: the six concurrent requests did not run one by one
+        assert isinstance(server.model, serving.BatchingModel) and max(server.model.batches) > 1
     finally:
         server.stop(0)
 
@@ -231,3 +235,50 @@ def test_assignment_index_chunks_embeds_and_finds(pkg):
     assert hits[0][2] > hits[1][2]
     ok, best = index.is_relevant(" ".join(f"x{i}" for i in range(30)), threshold=0.99)
     assert ok and best[:2] == ("hw2", 0)
+
+
+@pytest.mark.gpu
+def test_relevance_gate_over_b200_bert(pkg):
+    """SURVEY section 8f rank 2 on the GPU: RelevanceGate over B200BertModel (load once, assignment embedding cached)
+    gives the reference's similarity (REF/lms_server.py:1262-1266, via the oracle on the same weights, <= 1e-4), the same
+    relevant / not-relevant decision at the reference's 0.6 and across a threshold sweep, one BERT forward per request
+    after the first, and the canned reply of REF/lms_server.py:1270 for an unrelated query."""
+    import torch
+    from importlib import import_module
+    serving = import_module("distributed-lms-raft-llm_b200.serving")
+
+    class Tok:  # deterministic ids per text (no vocabulary offline), the reference's tokenizer call shape
+        def __call__(self, text, **kw):
+            n = min(kw.get("max_length", 512), 8 + (sum(text.encode()) % 90))
+            ids = rp.bert_ids(1, n, seed=sum(text.encode()), vocab=2000)
+            return {"input_ids": ids, "token_type_ids": torch.zeros_like(ids), "attention_mask": torch.ones_like(ids)}
+
+    hf = rp.build_bert(seed=6, hidden_size=128, num_hidden_layers=2, num_attention_heads=2, intermediate_size=512,
+                       vocab_size=2000, max_position_embeddings=128)
+    bert = pkg.B200BertModel.from_hf(hf, dtype="fp32")
+    launches = pkg._lib.load().tutor_launch_count
+    gate = serving.RelevanceGate(bert, Tok(), threshold=0.6)
+    text = "write a report about distributed consensus and log replication " * 2
+    queries = ["how does raft elect a leader", "what is log replication?", "best pizza topping", "x"]
+    sims = []
+    for i, qtext in enumerate(queries):
+        n0 = launches()
+        relevant, sim = gate.check(qtext, text)
+        n1 = launches()
+        ref = rp.cosine_similarity(rp.compute_embeddings(qtext, hf, Tok()), rp.compute_embeddings(text, hf, Tok()))
+        assert abs(sim - ref) < 1e-4, (qtext, sim, ref)
+        assert relevant == rp.relevance_decision(ref)
+        sims.append((sim, ref))
+        if i == 1:
+            per_forward = n1 - n0
+        if i >= 2:
+            assert n1 - n0 == per_forward, "a cached assignment costs exactly one BERT forward per request"
+    assert gate.misses == 1 and gate.hits == len(queries) - 1
+    for sim, ref in sims:  # decisions identical wherever the threshold falls
+        for thr in (ref - 1e-3, ref + 1e-3, 0.0, 0.6, 0.99):
+            gate.threshold = thr
+            assert (not (sim < thr)) == (not (ref < thr))
+    gate.threshold = 2.0
+    assert gate.answer(queries[0], text, lambda q: "tutor says hi") == rp.NOT_RELATED_MESSAGE
+    gate.threshold = -2.0
+    assert gate.answer(queries[0], text, lambda q: "tutor says hi") == "tutor says hi"
