@@ -433,6 +433,42 @@ def leg_cfg4(pkg, rp, torch, pk, local, world, rank, with_cpu):
     return res
 
 
+def leg_tokenize(pkg):
+    """The host step either side of the GPU work: prompt templating + GPT-2 BPE encode,
+    decode of the 150-token reply, BERT WordPiece of a query and of an assignment text - us per request through the C
+    library, with transformers' own tokenizers (the reference's) timed beside them.  Vocabularies: tests/golden/vocab."""
+    import random
+    from transformers import BertTokenizer, GPT2Tokenizer
+    d = os.path.join(ROOT, "tests", "golden", "vocab")
+    v, m, bv = os.path.join(d, "gpt2_vocab.json"), os.path.join(d, "gpt2_merges.txt"), os.path.join(d, "bert_vocab.txt")
+    mine_g, hf_g = pkg.B200GPT2Tokenizer(v, m), GPT2Tokenizer(vocab=v, merges=m)
+    mine_b = pkg.B200BertTokenizer(bv)
+    hf_b = BertTokenizer(vocab={l.rstrip("\n"): i for i, l in enumerate(open(bv, encoding="utf-8"))})
+    rng = random.Random(3)
+    words = open(os.path.join(ROOT, "SURVEY.md"), encoding="utf-8").read().split()
+    text = lambda n: " ".join(rng.choice(words) for _ in range(n))
+    prompts = ["Answer the following question as a helpful tutor: " + text(20) for _ in range(200)]
+    replies = [mine_g.encode(text(110))[:150] for _ in range(200)]
+    docs = [text(600) for _ in range(50)]
+
+    def clock(fn, items):
+        fn(items[0])
+        t0 = time.perf_counter()
+        for x in items:
+            fn(x)
+        return (time.perf_counter() - t0) / len(items) * 1e6
+    kw = dict(return_tensors="pt", padding=True, truncation=True, max_length=512)
+    return {"workload": "prompt template + GPT-2 BPE encode; decode of a 150-token reply; BERT WordPiece of a 20-word query and "
+                        "a 600-word assignment text (cut at 512 ids); synthetic vocabularies (tests/golden/vocab)",
+            "us_per_request": {"gpt2_encode": clock(lambda p: mine_g.encode(p, return_tensors="pt"), prompts),
+                               "gpt2_decode": clock(lambda r: mine_g.decode(r, skip_special_tokens=True), replies),
+                               "bert_query": clock(lambda p: mine_b(p, **kw), prompts), "bert_assignment": clock(lambda t: mine_b(t, **kw), docs)},
+            "cpu_baseline": {"kind": "reference", "unit": "us/request", "sample": "transformers GPT2Tokenizer / BertTokenizer on the same inputs",
+                             "gpt2_encode": clock(lambda p: hf_g.encode(p, return_tensors="pt"), prompts),
+                             "gpt2_decode": clock(lambda r: hf_g.decode(r, skip_special_tokens=True), replies),
+                             "bert_query": clock(lambda p: hf_b(p, **kw), prompts), "bert_assignment": clock(lambda t: hf_b(t, **kw), docs)}}
+
+
 def leg_cfg3(pkg, rp, torch, pk, local):
     """configs[3]: GPT-2 large bf16, B=16 - (ii) prefill-only over the full 1024-token context (one forward, first token
     only; 24.74 TFLOP) and (i) 896-token prompt -> +128 tokens end to end (1024 total: wpe has 1024 rows)."""
@@ -587,7 +623,8 @@ def main():
             for name, fn in (("cfg0", lambda: leg_cfg0(lms_b200, rp, torch, hf, pk, local, True)),
                              ("cfg1", lambda: leg_cfg1(lms_b200, rp, torch, pk, local, True)),
                              ("cfg4", lambda: leg_cfg4(lms_b200, rp, torch, pk, local, 1, 0, True)),
-                             ("cfg3", lambda: leg_cfg3(lms_b200, rp, torch, pk, local))):
+                             ("cfg3", lambda: leg_cfg3(lms_b200, rp, torch, pk, local)),
+                             ("tokenize", lambda: leg_tokenize(lms_b200))):
                 try:
                     legs[name] = fn()
                 except Exception as e:

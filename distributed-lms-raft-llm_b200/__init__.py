@@ -7,8 +7,9 @@ from . import _lib
 from .bert import (NOT_RELATED_MESSAGE, SIMILARITY_THRESHOLD, B200BertModel, compute_embeddings, cosine_similarity,
                    cosine_similarity_batch, is_relevant)
 from .gpt2 import B200GPT2LMHeadModel
+from .tokenization import B200BertTokenizer, B200GPT2Tokenizer
 from .relevance import CorpusShard, close_exchange, exchange_candidates, init_exchange, shard_bounds
 
-__all__ = ["B200GPT2LMHeadModel", "B200BertModel", "compute_embeddings", "cosine_similarity", "cosine_similarity_batch",
+__all__ = ["B200GPT2LMHeadModel", "B200BertModel", "B200GPT2Tokenizer", "B200BertTokenizer", "compute_embeddings", "cosine_similarity", "cosine_similarity_batch",
            "is_relevant", "CorpusShard", "exchange_candidates", "init_exchange", "close_exchange", "shard_bounds", "SIMILARITY_THRESHOLD",
            "NOT_RELATED_MESSAGE", "_lib"]

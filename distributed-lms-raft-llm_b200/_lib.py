@@ -90,6 +90,15 @@ SIGNATURES = {
                                            c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "tutor_decode_linear_residual": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                              c_void_p, c_void_p]),
+    "tutor_bpe_create": (c_int, [c_char_p, c_char_p, P(c_void_p)]),
+    "tutor_bpe_destroy": (None, [c_void_p]),
+    "tutor_bpe_eos_id": (c_int, [c_void_p]),
+    "tutor_bpe_vocab_size": (c_int, [c_void_p]),
+    "tutor_bpe_encode": (c_int, [c_void_p, c_char_p, C.c_int64, c_void_p, c_int, P(c_int)]),
+    "tutor_bpe_decode": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, P(c_int)]),
+    "tutor_wordpiece_create": (c_int, [c_char_p, P(c_void_p)]),
+    "tutor_wordpiece_destroy": (None, [c_void_p]),
+    "tutor_wordpiece_encode": (c_int, [c_void_p, c_char_p, C.c_int64, c_int, c_void_p, c_int, P(c_int)]),
     "tutor_lmhead_argmax_static": (c_int, [c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_float, c_void_p,
                                            c_void_p]),
 }

@@ -18,7 +18,7 @@ if os.environ.get("TUTOR_EXPERIMENTS"):  # A/B knobs for tools/ (csrc/common.cuh
 
 
 def sources():
-    return sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
+    return sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cpp")))
 
 
 def _newest_input():
@@ -32,8 +32,8 @@ def up_to_date():
 
 
 def _compile(src, force=False):
-    obj = os.path.join(OBJ, src[:-3] + ".o")
-    hdr_time = max(os.path.getmtime(os.path.join(CSRC, f)) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh")))
+    obj = os.path.join(OBJ, os.path.splitext(src)[0] + ".o")
+    hdr_time = max(os.path.getmtime(os.path.join(CSRC, f)) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh", ".inc")))
     hdr_time = max(hdr_time, os.path.getmtime(os.path.join(HERE, "..", "include", "tutor_b200.h")))
     if not force and os.path.exists(obj) and os.path.getmtime(obj) >= max(os.path.getmtime(os.path.join(CSRC, src)), hdr_time):
         return obj, ""

@@ -224,6 +224,30 @@ int tutor_decode_linear_residual(const void* A_dev, const void* W_dev, const flo
 int tutor_lmhead_argmax_static(int dtype, const void* x_dev, const void* wte_dev, int B, int V, int d,
                                const uint32_t* seen_dev, float penalty, int32_t* out_idx_dev, void* stream);
 
+/* ----------------------------------------------------------------------------------------------------------
+ * Host tokenisation, the step either side of the GPU work (no CUDA involved; plain host code in the same library).
+ * GPT-2 byte-level BPE: replaces tokenizer.encode / tokenizer.decode of REF/tutoring_server.py:20,30 (transformers'
+ * GPT2Tokenizer = `tokenizers` BPE + ByteLevel).  Built from the reference's file formats: vocab.json + merges.txt.
+ * encode adds no special tokens (GPT2Tokenizer's default); a literal "<|endoftext|>" in the text becomes its id.
+ * decode returns raw bytes (the caller decodes UTF-8 with errors="replace", as GPT2Tokenizer does).            */
+typedef struct tutor_bpe tutor_bpe_t;
+int tutor_bpe_create(const char* vocab_json_path, const char* merges_txt_path, tutor_bpe_t** out);
+void tutor_bpe_destroy(tutor_bpe_t* h);
+int tutor_bpe_eos_id(tutor_bpe_t* h);
+int tutor_bpe_vocab_size(tutor_bpe_t* h);
+int tutor_bpe_encode(tutor_bpe_t* h, const char* utf8, int64_t nbytes, int32_t* ids_out, int capacity, int* n_out);
+int tutor_bpe_decode(tutor_bpe_t* h, const int32_t* ids, int n, int skip_special_tokens, char* out, int capacity,
+                     int* nbytes_out);
+/* BERT WordPiece: replaces tokenizer(text, return_tensors="pt", padding=True, truncation=True, max_length=512) of
+ * REF/lms_server.py:98 (transformers' BertTokenizer = BertNormalizer + BertPreTokenizer + WordPiece + "[CLS] $A [SEP]",
+ * lower-casing and accent stripping on, as for bert-base-uncased).  Built from vocab.txt.  ids_out = [CLS] pieces [SEP],
+ * cut to max_length ids in all when max_length > 0.                                                             */
+typedef struct tutor_wordpiece tutor_wordpiece_t;
+int tutor_wordpiece_create(const char* vocab_txt_path, tutor_wordpiece_t** out);
+void tutor_wordpiece_destroy(tutor_wordpiece_t* h);
+int tutor_wordpiece_encode(tutor_wordpiece_t* h, const char* utf8, int64_t nbytes, int max_length, int32_t* ids_out,
+                           int capacity, int* n_out);
+
 #ifdef __cplusplus
 }
 #endif
