@@ -12,6 +12,7 @@
 #include <string>
 #include <vector>
 
+#include "decode_f32_persistent.h"
 #include "decode_mega.h"
 #include "engine_common.h"
 
@@ -101,6 +102,16 @@ struct tutor_gpt2 {
     long long* trace = nullptr;  // tutor_gpt2_decode_trace
     int trace_cta = -1;
   } mega;
+  // cooperative fp32 decode kernel for one or two sequences (decode_f32_persistent.cu); TUTOR_F32_PERSISTENT=0 selects the
+  // launch chain of gemv kernels instead (A/B baseline and cross-check)
+  bool use_persist_f32 = true;
+  struct PersistF32 {
+    uint64_t epoch = 0;
+    int B = 0, nsplit = 1;
+    PersistF32Layer* layers = nullptr;
+    float* att_scratch = nullptr;
+    int* counters = nullptr;  // [2 + B*H] counters, then err[8]
+  } pf;
   // decode graph
   cudaGraphExec_t graph_exec = nullptr;
   uint64_t graph_kernels = 0;
@@ -131,6 +142,65 @@ void drop_graph(tutor_gpt2* e) {
 int gemm(tutor_gpt2* e, const void* A, const Linear& w, int M, const GemmEpilogue& epi) {
   if (e->dt == DT_F32) return k_gemm_f32((const float*)A, (const float*)w.w, M, w.N, w.K, epi, e->stream);
   return k_gemm_bf16((const bf16*)A, (const bf16*)w.w, M, w.N, w.K, epi, e->stream);
+}
+
+void persist_free(tutor_gpt2* e) {
+  dev_free(e->pf.layers); dev_free(e->pf.att_scratch); dev_free(e->pf.counters);
+  e->pf.epoch = 0;
+}
+
+bool persist_applies(const tutor_gpt2* e, int B) {
+  return e->dt == DT_F32 && e->use_persist_f32 && k_decode_f32_persistent_supported(B, e->d, e->num_sms);
+}
+
+// key ranges per (sequence, head) of the cooperative kernel's attention phase: ~64 keys per CTA, as many CTAs as there are
+int persist_nsplit(const tutor_gpt2* e, int B, int total) {
+  const int most = e->num_sms / (B * e->H);
+  int n = ceil_div(total, 64);
+  if (n > most) n = most;
+  return n < 1 ? 1 : n;
+}
+
+// per-layer pointers, scratch and counters of the cooperative fp32 decode kernel (rebuilt when an allocation changed)
+int persist_prepare(tutor_gpt2* e, int B) {
+  tutor_gpt2::PersistF32& f = e->pf;
+  if (f.epoch == e->alloc_epoch && f.B == B) return TUTOR_OK;
+  drop_graph(e);
+  CUDA_TRY(cudaStreamSynchronize(e->stream));
+  persist_free(e);
+  std::vector<PersistF32Layer> lw(e->L);
+  for (int l = 0; l < e->L; ++l) {
+    const Gpt2Layer& w = e->layers[l];
+    lw[l] = PersistF32Layer{w.ln1_g, w.ln1_b, w.ln2_g, w.ln2_b, (const float*)w.qkv.w, w.qkv.b, (const float*)w.proj.w, w.proj.b,
+                            (const float*)w.fc.w, w.fc.b, (const float*)w.proj2.w, w.proj2.b, (float*)e->kcache(l),
+                            (float*)e->vcache(l)};
+  }
+  TRY(dev_alloc(&f.layers, lw.size() * sizeof(PersistF32Layer)));
+  CUDA_TRY(cudaMemcpy(f.layers, lw.data(), lw.size() * sizeof(PersistF32Layer), cudaMemcpyHostToDevice));
+  TRY(dev_alloc(&f.att_scratch, (size_t)e->num_sms * 66 * sizeof(float)));
+  const size_t nc = (size_t)2 + B * e->H + 8;
+  TRY(dev_alloc(&f.counters, nc * sizeof(int)));
+  CUDA_TRY(cudaMemset(f.counters, 0, nc * sizeof(int)));
+  f.B = B;
+  f.epoch = e->alloc_epoch;
+  return TUTOR_OK;
+}
+
+int forward_decode_persist_f32(tutor_gpt2* e, int B) {
+  tutor_gpt2::PersistF32& f = e->pf;
+  PersistF32Params p{};
+  p.L = e->L; p.Smax = e->Smax; p.nsplit = f.nsplit; p.layers = f.layers;
+  p.ids = e->ids; p.ids_ld = e->ids_ld; p.len = e->counters; p.npad = e->padded ? e->npad : nullptr;
+  p.wte = (const float*)e->wte; p.wpe = e->wpe;
+  p.x = e->x; p.q = (float*)e->q; p.att = (float*)e->att; p.h = (float*)e->hbuf;
+  p.att_scratch = f.att_scratch; p.counters = f.counters; p.err = f.counters + 2 + B * e->H;
+  p.eps = e->cfg.layer_norm_epsilon;
+  p.trace = e->mega.trace_cta >= 0 ? e->mega.trace : nullptr;
+  p.trace_cta = e->mega.trace_cta;
+  TRY(k_decode_f32_persistent(p, B, e->d, e->num_sms, e->stream));
+  // ln_f is folded into the LM-head kernel; CTA 0 also leaves ln_f(x) in xn_last for tutor_gpt2_logits
+  return k_lmhead_argmax_ln(e->x, e->dt, e->wte, e->dt, B, e->V, e->d, e->dstate(), e->lm_scratch, e->lnf_g, e->lnf_b,
+                            e->cfg.layer_norm_epsilon, (float*)e->xn_last, e->stream);
 }
 
 // One forward over M = B*T tokens.  decode=true: T == 1 and every position comes from the device counter.
@@ -453,6 +523,12 @@ int forward_decode_mega(tutor_gpt2* e, int B) {
 
 int decode_forward(tutor_gpt2* e, int B) {
   if (!(e->dt == DT_BF16 && e->use_fused && B <= 128)) {
+    if (persist_applies(e, B) && e->pf.epoch == e->alloc_epoch && e->pf.B == B) {
+      tutor_pdl_enabled = e->use_pdl;  // both kernels wait (griddepcontrol.wait) before touching dependent data
+      int rc = forward_decode_persist_f32(e, B);
+      tutor_pdl_enabled = false;
+      return rc;
+    }
     // parity (fp32) path: same kernel chain as prefill, with PDL when every GEMM is the weight-streaming GEMV
     // (M <= 8), all of whose kernels wait before touching dependent data
     tutor_pdl_enabled = e->use_pdl && e->dt == DT_F32 && B <= 8;
@@ -594,6 +670,12 @@ int start_generation(tutor_gpt2* e, int B, int T, int total, float penalty, int 
   e->safe_rows = safe;
   e->cur_B = B; e->cur_T = T; e->cur_total = total; e->cur_penalty = penalty; e->cur_eos = eos; e->cur_pad = pad;
   if (mega_applies(e, B) && nl == 1) TRY(mega_prepare(e, B));
+  if (persist_applies(e, B)) {
+    TRY(persist_prepare(e, B));
+    const int ns = persist_nsplit(e, B, total);
+    if (ns != e->pf.nsplit) drop_graph(e);  // a captured kernel argument
+    e->pf.nsplit = ns;
+  }
   cudaStream_t st = e->stream;
   e->h_counters[0] = T; e->h_counters[1] = 0;
   CUDA_TRY(cudaMemcpyAsync(e->counters, e->h_counters, 2 * sizeof(int), cudaMemcpyHostToDevice, st));
@@ -659,6 +741,16 @@ int read_counters(tutor_gpt2* e, int* len, int* stop_len) {
       return TUTOR_ERR_CUDA;
     }
   }
+  if (e->pf.counters && e->pf.epoch) {  // a grid barrier of the cooperative fp32 kernel gave up
+    int err[5] = {0, 0, 0, 0, 0};
+    int* dev = e->pf.counters + 2 + e->pf.B * e->H;
+    CUDA_TRY(cudaMemcpy(err, dev, sizeof(err), cudaMemcpyDeviceToHost));
+    if (err[0] != 0) {
+      tutor_set_error("fp32 decode kernel: grid barrier %d timed out (target %d) in block %d", err[1], err[2], err[3]);
+      CUDA_TRY(cudaMemset(e->pf.counters, 0, ((size_t)2 + e->pf.B * e->H + 8) * sizeof(int)));
+      return TUTOR_ERR_CUDA;
+    }
+  }
   *len = e->h_counters[0];
   int stop = 0;
   for (int i = 0; i < e->nlanes; ++i) {
@@ -715,6 +807,7 @@ int tutor_gpt2_create(const tutor_gpt2_config* cfg, int device, tutor_gpt2_t** o
   e->use_pdl = getenv("TUTOR_NO_PDL") == nullptr;
   e->use_cluster = getenv("TUTOR_NO_CLUSTER") == nullptr;
   if (const char* mm = getenv("TUTOR_MEGA")) e->mega_mode = atoi(mm);
+  if (const char* pf = getenv("TUTOR_F32_PERSISTENT")) e->use_persist_f32 = atoi(pf) != 0;
   if (!e->use_cluster) e->mega_mode = 0;
   e->use_ln_gemv = tutor_experiment("TUTOR_LN_GEMV") != nullptr;
   e->no_ln_gemv = tutor_experiment("TUTOR_NO_LN_GEMV") != nullptr;
@@ -747,6 +840,7 @@ void tutor_gpt2_destroy(tutor_gpt2_t* e) {
   cudaStreamSynchronize(e->stream);
   drop_graph(e);
   mega_free(e);
+  persist_free(e);
   dev_free(e->mega.trace);
   dev_free(e->wte); dev_free(e->wpe); dev_free(e->lnf_g); dev_free(e->lnf_b);
   for (auto& l : e->layers) {
