@@ -1086,6 +1086,9 @@ int k_attn_prefill(const void* q, int q_dtype, const void* k, const void* v, int
     attn_prefill_kernel<float, float, float, false><<<grid, block, 0, st>>>(
         (const float*)q, (const float*)k, (const float*)v, (float*)out, H, T, Smax, causal, npad);
   else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16) {
+    // tensor cores of the 5th generation by default; TUTOR_ATTN_PREFILL_MMA=1 keeps the mma.sync kernel as a cross-check
+    static const bool legacy = getenv("TUTOR_ATTN_PREFILL_MMA") != nullptr;
+    if (!legacy) return k_attn_prefill_tc((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)out, B, H, T, Smax, causal, npad, st);
     dim3 g2(ceil_div(T, 128), H, B);
 #define PF_LAUNCH(C, P)                                                                                          \
   attn_prefill_mma_kernel<C, P><<<g2, 128, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)out, H, T, \

@@ -49,6 +49,9 @@ int k_gemm_bf16_legacy(const bf16* A, const bf16* W, int M, int N, int K, const 
 // ---- attention.cu : head_dim is 64 for every model on this path
 // q [B*T, H*64] (fp32 or bf16), K/V [B][H][Smax][64] of kv_dtype, out [B*T, H*64]
 // npad (nullable, [B]): leading pad slots of each left-padded sequence - real tokens never attend to them
+// tcgen05 flavour (attention_tc.cu): bf16, head_dim 64, q / out [B*T, H*64], k / v in the cache layout [B][H][Smax][64]
+int k_attn_prefill_tc(const bf16* q, const bf16* k, const bf16* v, bf16* out, int B, int H, int T, int Smax, int causal,
+                      const int* npad, cudaStream_t st);
 int k_attn_prefill(const void* q, int q_dtype, const void* k, const void* v, int kv_dtype, void* out, int out_dtype,
                    int B, int H, int T, int Smax, int causal, const int* npad, cudaStream_t st);
 // one query per (b,h) against cache positions [0, len): len = *len_dev if non-null else len_host

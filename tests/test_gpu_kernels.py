@@ -103,7 +103,8 @@ def _sdpa_ref(q, k, v, causal):
 
 
 @pytest.mark.parametrize("dtype", [F32, BF16])
-@pytest.mark.parametrize("B,H,T,causal", [(1, 2, 32, 1), (2, 12, 100, 1), (3, 2, 40, 0), (2, 4, 129, 1), (1, 12, 512, 0)])
+@pytest.mark.parametrize("B,H,T,causal", [(1, 2, 32, 1), (2, 12, 100, 1), (3, 2, 40, 0), (2, 4, 129, 1), (1, 12, 512, 0),
+                                          (1, 1, 128, 0), (2, 3, 300, 0), (2, 2, 257, 1), (1, 20, 1024, 1), (1, 2, 1, 0)])
 def test_attn_prefill(pkg, lib, dtype, B, H, T, causal):
     g = torch.Generator().manual_seed(T)
     td = torch.float32 if dtype == F32 else torch.bfloat16
