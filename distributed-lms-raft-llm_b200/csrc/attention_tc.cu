@@ -3,21 +3,25 @@
 //   bidirectional: BERT, HF/models/bert/modeling_bert.py:192-205 (through SDPA)
 //
 // A work item is (128 queries, head, sequence), processed flash-style over 64-key blocks:
-//   S = Q K^T        tcgen05.mma 128x64x64, Q and K tiles K-major from TMA (SWIZZLE_128B), S in TMEM (64 columns)
+//   S = Q K^T        tcgen05.mma 128x64x64, Q and K tiles K-major from TMA (SWIZZLE_128B), S in TMEM (two 64-column
+//                    buffers: the MMA of block g + 1 runs while the softmax warps work on block g)
 //   P = softmax tile four warps, one query row per thread, the 64 scores of the row in registers; P written as bf16
-//                    into a swizzled shared-memory tile that is the A operand of
+//                    into a swizzled shared-memory tile (two buffers) that is the A operand of
 //   O += P V         tcgen05.mma 128x64x64, V tile straight from the cache layout [key][dim] as an MN-major B operand,
 //                    O accumulated in TMEM (64 columns).
 // The running maximum is only moved when a block's maximum exceeds it by more than 8 (in log2 units): P then stays
 // below 2^8, and O / l is exact for any reference maximum.  Moving it means rescaling O in TMEM (load, scale, store),
 // which happens for the first few blocks of a row only.
-// Persistent: three CTAs per SM walk the items, longest first; barriers, TMEM and the K/V ring carry over from item to
-// item, so an item's first tiles arrive while the previous one finishes.
-// Warp roles: 0 = TMA producer, 1 = MMA issuer + TMEM allocation, 2..5 = softmax / epilogue.  What bounds a block is the
-// dependent chain MMA -> commit -> TMEM load -> exp2 -> shared memory -> fence -> MMA, not the tensor pipe: small blocks
-// and three CTAs per SM (64 KB of shared memory, 128 TMEM columns each) keep three such chains in flight per SM.
-// Measured on the way here (BERT 32 x 512, 12 heads; mma.sync kernel: 97.7 us): 128-key blocks, one CTA per item, two CTAs
-// per SM 71.7 us; persistent 66.0 us; two threads per row (eight softmax warps) 92.8 us.
+// Persistent: two CTAs per SM walk the items, longest first; barriers, TMEM, the K/V ring (three stages) and a second Q
+// buffer carry over from item to item, so an item's first tiles arrive while the previous one finishes.
+// Warp roles: 0 = TMA producer, 1 = MMA issuer + TMEM allocation, 2..5 = softmax / epilogue.
+//
+// Measured (BERT 32 x 512 x 12 heads, 25.8 GFLOP; mma.sync kernel 97.7 us): 128-key blocks, one CTA per item, two CTAs per
+// SM 71.7 us; persistent 66.0 us; two threads per row (eight softmax warps) 92.8 us; 64-key blocks, three CTAs per SM
+// 68.9 us; this version 70 us, and 97 / 113 us against 135 / 180 us on the causal GPT-2 shapes (64 x 512 x 12, 16 x 1024 x 20).
+// Per block a softmax warp spends ~110 cycles finding S ready, ~130 loading it from TMEM, ~700-900 on maximum + 64 exp2 per
+// thread, ~250 on a barrier test, ~130 packing and storing P (profiles/r2c_attn_prefill_tc.txt); the MUFU pipe is 40 % busy,
+// the tensor pipe 19 %.  Two co-resident CTAs slow each other by ~1.5x, so the SM, not a single chain, is the limit.
 #include <math_constants.h>
 
 #include "kernels.h"
@@ -30,8 +34,9 @@ constexpr int AT_THREADS = 192;               // TMA warp, MMA warp, 4 softmax w
 constexpr int AT_TILE = 128 * 128;             // bytes of a 128-row x 64-column bf16 tile (Q, P)
 constexpr int AT_KV = 64 * 128;                // bytes of a 64-key K or V tile
 constexpr int AT_BN = 64;                      // keys per block
-constexpr int AT_SMEM = 2 * AT_TILE + 4 * AT_KV + 128;  // Q, P, K[2], V[2], barriers
-constexpr uint32_t AT_TMEM_COLS = 128;         // S: columns 0..63, O: 64..127
+constexpr int AT_ST = 3;                       // K / V stages
+constexpr int AT_SMEM = 4 * AT_TILE + 2 * AT_ST * AT_KV + 256;  // Q[2], P[2], K[AT_ST], V[AT_ST], barriers
+constexpr uint32_t AT_TMEM_COLS = 256;         // S[2]: columns 0..63 and 64..127, O: 128..191
 
 // 32 lanes x 8 columns, multiplied in place (the rare rescale of O: narrow on purpose, the score row is live around it)
 __device__ __forceinline__ void tc_scale8(uint32_t taddr, float f) {
@@ -70,26 +75,26 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
 }
 
 template <bool CAUSAL, bool PADDED>
-__global__ void __launch_bounds__(AT_THREADS, 3)
+__global__ void __launch_bounds__(AT_THREADS, 2)
     attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                            const __grid_constant__ CUtensorMap tmV, bf16* __restrict__ out, int B, int H, int T, int Smax,
                            const int* __restrict__ npad) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  uint8_t* sQ = smem;
-  uint8_t* sP = smem + AT_TILE;
-  uint8_t* sK = smem + 2 * AT_TILE;              // [2]
-  uint8_t* sV = smem + 2 * AT_TILE + 2 * AT_KV;  // [2]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * AT_TILE + 4 * AT_KV);
-  uint64_t* q_full = bars;
-  uint64_t* k_full = bars + 1;    // [2]
-  uint64_t* v_full = bars + 3;    // [2]
-  uint64_t* k_empty = bars + 5;   // [2] freed by S = Q K^T (early: the next K tile has a whole block of lead)
-  uint64_t* v_empty = bars + 7;   // [2] freed by O += P V
-  uint64_t* s_full = bars + 9;
-  uint64_t* q_empty = bars + 10;
-  uint64_t* pv_done = bars + 11;
-  uint64_t* p_ready = bars + 12;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  uint8_t* sQ = smem;                                    // [2]: the next item's queries arrive during this item
+  uint8_t* sP = smem + 2 * AT_TILE;                      // [2]
+  uint8_t* sK = smem + 4 * AT_TILE;                      // [AT_ST]
+  uint8_t* sV = smem + 4 * AT_TILE + AT_ST * AT_KV;      // [AT_ST]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 4 * AT_TILE + 2 * AT_ST * AT_KV);
+  uint64_t* k_full = bars;                 // [AT_ST]
+  uint64_t* v_full = bars + AT_ST;         // [AT_ST]
+  uint64_t* k_empty = bars + 2 * AT_ST;    // [AT_ST] freed by S = Q K^T
+  uint64_t* v_empty = bars + 3 * AT_ST;    // [AT_ST] freed by O += P V
+  uint64_t* s_full = bars + 4 * AT_ST;     // [2]
+  uint64_t* q_full = s_full + 2;           // [2]
+  uint64_t* q_empty = s_full + 4;          // [2]
+  uint64_t* pv_done = s_full + 6;          // [2]: block g completes pv_done[g & 1]
+  uint64_t* p_ready = s_full + 8;          // [2], 128 arrivals each
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_full + 10);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nqt = (T + 127) / 128, nitems = nqt * H * B;
@@ -109,8 +114,9 @@ __global__ void __launch_bounds__(AT_THREADS, 3)
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmQ) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmK) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmV) : "memory");
-    for (int i = 0; i < 12; ++i) mbar_init(&bars[i], 1);
-    mbar_init(p_ready, 128);
+    for (int i = 0; i < 4 * AT_ST + 8; ++i) mbar_init(&bars[i], 1);
+    mbar_init(&p_ready[0], 128);
+    mbar_init(&p_ready[1], 128);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -123,7 +129,7 @@ __global__ void __launch_bounds__(AT_THREADS, 3)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tS = tmem_base, tO = tmem_base + 64;
+  const uint32_t tS = tmem_base, tO = tmem_base + 128;  // S buffer i at tS + 64 i
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -132,16 +138,17 @@ __global__ void __launch_bounds__(AT_THREADS, 3)
       for (int w = blockIdx.x; w < nitems; w += gridDim.x, ++it) {
         int qt, h, b;
         item(w, qt, h, b);
-        mbar_wait(q_empty, (it & 1) ^ 1, 0);  // the previous item's last S = Q K^T has read Q
-        mbar_expect_tx(q_full, AT_TILE);
-        tma_load_2d(sQ, &tmQ, q_full, h * 64, b * T + qt * 128);
+        mbar_wait(&q_empty[it & 1], ((it >> 1) & 1) ^ 1, 0);  // the last S = Q K^T of two items ago has read this buffer
+        mbar_expect_tx(&q_full[it & 1], AT_TILE);
+        tma_load_2d(sQ + (it & 1) * AT_TILE, &tmQ, &q_full[it & 1], h * 64, b * T + qt * 128);
         const int kv_row0 = (b * H + h) * Smax, nblk = blocks_of(qt);
         for (int j = 0; j < nblk; ++j, ++g) {
-          const int st = g & 1;
-          mbar_wait(&k_empty[st], ((g >> 1) & 1) ^ 1, 0);
+          const int st = g % AT_ST;
+          const uint32_t use = (uint32_t)(g / AT_ST) & 1;
+          mbar_wait(&k_empty[st], use ^ 1, 0);
           mbar_expect_tx(&k_full[st], AT_KV);
           tma_load_2d(sK + st * AT_KV, &tmK, &k_full[st], 0, kv_row0 + j * AT_BN);
-          mbar_wait(&v_empty[st], ((g >> 1) & 1) ^ 1, 0);
+          mbar_wait(&v_empty[st], use ^ 1, 0);
           mbar_expect_tx(&v_full[st], AT_KV);
           tma_load_2d(sV + st * AT_KV, &tmV, &v_full[st], 0, kv_row0 + j * AT_BN);
         }
@@ -153,14 +160,15 @@ __global__ void __launch_bounds__(AT_THREADS, 3)
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, 64);
       constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64) | (1u << 16);  // B (= V) is MN-major
       auto issue_pv = [&](int g, bool first) {  // O (+)= P V of block g (first: the item's first block starts O afresh)
-        const int st = g & 1;
-        mbar_wait(&v_full[st], (g >> 1) & 1, 1);
+        const int st = g % AT_ST;
+        mbar_wait(&p_ready[g & 1], (g >> 1) & 1, 1);  // P of block g is in shared memory (and S buffer g & 1 has been read)
+        mbar_wait(&v_full[st], (g / AT_ST) & 1, 1);
         tc_fence_after();
-        const uint32_t sp = smem_u32(sP), sv = smem_u32(sV + st * AT_KV);
+        const uint32_t sp = smem_u32(sP + (g & 1) * AT_TILE), sv = smem_u32(sV + st * AT_KV);
 #pragma unroll
         for (int k = 0; k < 4; ++k)  // 16 keys per MMA: 32 bytes along the rows of P; two 8-key groups (2 x 1024 bytes) of V
           tc_mma_bf16(tO, umma_desc_sw128(sp + k * 32), umma_desc_sw128_mn(sv + k * 2048), idesc_o, !first || k != 0);
-        tc_commit(pv_done);
+        tc_commit(&pv_done[g & 1]);
         tc_commit(&v_empty[st]);
       };
       int g = 0, it = 0;
@@ -169,30 +177,28 @@ __global__ void __launch_bounds__(AT_THREADS, 3)
         int qt, h, b;
         item(w, qt, h, b);
         const int nblk = blocks_of(qt);
-        mbar_wait(q_full, it & 1, 1);
+        mbar_wait(&q_full[it & 1], (it >> 1) & 1, 1);
         for (int j = 0; j < nblk; ++j, ++g) {
-          const int st = g & 1;
-          mbar_wait(&k_full[st], (g >> 1) & 1, 1);
-          if (g > 0) mbar_wait(p_ready, (g - 1) & 1, 1);  // S has been read (and the previous P written)
+          // S of block g goes into TMEM buffer g & 1 as soon as the softmax of block g - 2 has read it: one block ahead
+          // of the softmax warps, which therefore find their scores waiting
+          const int st = g % AT_ST;
+          mbar_wait(&k_full[st], (g / AT_ST) & 1, 1);
+          if (g > 1) mbar_wait(&p_ready[g & 1], ((g - 2) >> 1) & 1, 1);
           tc_fence_after();
-          const uint32_t sq = smem_u32(sQ), sk = smem_u32(sK + st * AT_KV);
+          const uint32_t sq = smem_u32(sQ + (it & 1) * AT_TILE), sk = smem_u32(sK + st * AT_KV);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            tc_mma_bf16(tS, umma_desc_sw128(sq + k * 32), umma_desc_sw128(sk + k * 32), idesc_s, k != 0);
-          tc_commit(s_full);
+            tc_mma_bf16(tS + (g & 1) * 64, umma_desc_sw128(sq + k * 32), umma_desc_sw128(sk + k * 32), idesc_s, k != 0);
+          tc_commit(&s_full[g & 1]);
           tc_commit(&k_empty[st]);
-          if (j == nblk - 1) tc_commit(q_empty);
-          // behind S in the tensor pipe: the softmax of this block overlaps the previous block's P V.  When that
-          // block opened a new item it overwrites O: the softmax threads read the old O (their epilogue) before they
-          // signalled p_ready for it, so no further barrier is needed.
+          if (j == nblk - 1) tc_commit(&q_empty[it & 1]);
+          // P V of the previous block, behind S in the tensor pipe.  When that block opened a new item it overwrites O:
+          // the softmax threads read the old O (their epilogue) before they signalled p_ready for it.
           if (g > 0) issue_pv(g - 1, prev_first);
           prev_first = j == 0;
         }
       }
-      if (g > 0) {
-        mbar_wait(p_ready, (g - 1) & 1, 1);
-        issue_pv(g - 1, prev_first);
-      }
+      if (g > 0) issue_pv(g - 1, prev_first);
     }
   } else {
     // ===== softmax + epilogue: thread = query row; a warp reaches the 32 TMEM lanes of its quadrant (warp index mod 4) =====
@@ -200,21 +206,36 @@ __global__ void __launch_bounds__(AT_THREADS, 3)
     const int r = quad * 32 + lane;
     const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
     constexpr float C = 0.125f * 1.4426950408889634f;  // 1/sqrt(64) and log2(e) in one factor
-    uint8_t* prow = sP + r * 128;
     int g = 0;
+#ifdef TUTOR_EXPERIMENTS
+#define AT_STAMP(i) if (tracing && g >= 2 && g < 6) stamp[g - 2][i] = clock64()
+    const bool tracing = blockIdx.x == 0 && threadIdx.x == 64;
+    long long stamp[4][8];
+#else
+#define AT_STAMP(i)
+#endif
     for (int w = blockIdx.x; w < nitems; w += gridDim.x) {
       int qt, h, b;
       item(w, qt, h, b);
       const int nblk = blocks_of(qt), q0 = qt * 128, qrow = q0 + r;
       const int kp = PADDED ? npad[b] : 0;  // left padding: pad keys are invisible to real queries
       float m_run = -CUDART_INF_F, l_run = 0.f;
+#ifdef TUTOR_EXPERIMENTS
+      const long long t_item = clock64();
+      long long t_first = 0;
+#endif
       for (int j = 0; j < nblk; ++j, ++g) {
         const int key0 = j * AT_BN;
         const bool edge = (key0 + AT_BN - 1 >= T) || (CAUSAL && key0 + AT_BN - 1 > q0) || (PADDED && key0 < kp);
-        mbar_wait(s_full, g & 1, 2);
+        AT_STAMP(0);
+        mbar_wait(&s_full[g & 1], (g >> 1) & 1, 2);
         tc_fence_after();
+        AT_STAMP(1);
+#ifdef TUTOR_EXPERIMENTS
+        if (j == 0) t_first = clock64();
+#endif
         float s[64];
-        tc_ld32x2(tS + lane_off, tS + lane_off + 32, s, s + 32);
+        tc_ld32x2(tS + (g & 1) * 64 + lane_off, tS + (g & 1) * 64 + lane_off + 32, s, s + 32);
         if (edge) {
 #pragma unroll
           for (int i = 0; i < 64; ++i) {
@@ -222,6 +243,7 @@ __global__ void __launch_bounds__(AT_THREADS, 3)
             if (key >= T || (CAUSAL && key > qrow) || (PADDED && key < kp && qrow >= kp)) s[i] = -CUDART_INF_F;
           }
         }
+        AT_STAMP(2);
         float mx0 = fmaxf(s[0], s[1]), mx1 = fmaxf(s[2], s[3]);
 #pragma unroll
         for (int i = 4; i < 64; i += 2) { mx0 = fmaxf(mx0, s[i]); mx1 = fmaxf(mx1, s[i + 1]); }
@@ -245,15 +267,20 @@ __global__ void __launch_bounds__(AT_THREADS, 3)
           l1 += s[i + 1];
         }
         l_run += l0 + l1;
-        if (g > 0) {
-          mbar_wait(pv_done, (g - 1) & 1, 3);  // P V of the previous block has read P and finished with O
+        AT_STAMP(3);
+        // P buffer g & 1 was read by the P V of block g - 2 (one barrier per buffer: never more than one phase behind)
+        if (g > 1) mbar_wait(&pv_done[g & 1], ((g - 2) >> 1) & 1, 3);
+        if (j > 0 && __any_sync(0xffffffffu, move)) {
+          mbar_wait(&pv_done[(g - 1) & 1], ((g - 1) >> 1) & 1, 3);  // O is rescaled between two P V
           tc_fence_after();
-          if (j > 0 && __any_sync(0xffffffffu, move)) {
+          {
 #pragma unroll 1
             for (int c = 0; c < 8; ++c) tc_scale8(tO + lane_off + c * 8, alpha);
             tc_wait_st();
           }
         }
+        AT_STAMP(4);
+        uint8_t* prow = sP + (g & 1) * AT_TILE + r * 128;  // P buffer g & 1: block g - 2's P V finished a block ago
 #pragma unroll
         for (int ch = 0; ch < 8; ++ch) {  // 8 keys = one 16-byte chunk of the swizzled A tile
           uint4 v;
@@ -261,12 +288,25 @@ __global__ void __launch_bounds__(AT_THREADS, 3)
           v.z = pack2(s[ch * 8 + 4], s[ch * 8 + 5]); v.w = pack2(s[ch * 8 + 6], s[ch * 8 + 7]);
           *reinterpret_cast<uint4*>(prow + ((ch ^ (r & 7)) << 4)) = v;
         }
+        AT_STAMP(5);
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> the MMA's async proxy
         tc_fence_before();
-        mbar_arrive(p_ready);
+        AT_STAMP(6);
+        mbar_arrive(&p_ready[g & 1]);
+        AT_STAMP(7);
       }
+#ifdef TUTOR_EXPERIMENTS
+      if (tracing && w == (int)blockIdx.x)
+        for (int i = 0; i < 4; ++i)
+          printf("block %d: wait S %lld | TMEM load %lld | max + exp2 %lld | wait PV %lld | pack + store %lld | fence %lld | arrive %lld | to next %lld\n",
+                 i + 2, stamp[i][1] - stamp[i][0], stamp[i][2] - stamp[i][1], stamp[i][3] - stamp[i][2], stamp[i][4] - stamp[i][3],
+                 stamp[i][5] - stamp[i][4], stamp[i][6] - stamp[i][5], stamp[i][7] - stamp[i][6], i < 3 ? stamp[i + 1][0] - stamp[i][7] : 0LL);
+#endif
+#ifdef TUTOR_EXPERIMENTS
+      const long long t_epi = clock64();
+#endif
       // ---- epilogue: O / l -> bf16 [B*T, d]
-      mbar_wait(pv_done, (g - 1) & 1, 4);
+      mbar_wait(&pv_done[(g - 1) & 1], ((g - 1) >> 1) & 1, 4);
       tc_fence_after();
       const float inv = 1.0f / l_run;
       bf16* dst = out + ((size_t)b * T + qrow) * (H * 64) + h * 64;
@@ -285,6 +325,11 @@ __global__ void __launch_bounds__(AT_THREADS, 3)
         }
       }
       tc_fence_before();
+#ifdef TUTOR_EXPERIMENTS
+      if (tracing)
+        printf("item %d (%d blocks): first S after %lld, blocks %lld (%lld each), epilogue %lld\n", w, nblk, t_first - t_item,
+               t_epi - t_first, (t_epi - t_first) / nblk, clock64() - t_epi);
+#endif
     }
   }
   __syncthreads();
@@ -307,9 +352,7 @@ int k_attn_prefill_tc(const bf16* q, const bf16* k, const bf16* v, bf16* out, in
   CUDA_TRY(cudaGetDevice(&dev));
   CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const int nitems = ceil_div(T, 128) * H * B;
-  // as many CTAs as fit (three per SM), fewer when that gives every CTA the same number of items
-  const int per_cta = ceil_div(nitems, 3 * sms);
-  dim3 grid(ceil_div(nitems, per_cta));
+  dim3 grid(nitems < 2 * sms ? nitems : 2 * sms);  // two resident CTAs per SM
 #define AT_LAUNCH(C, P)                                                                                      \
   do {                                                                                                       \
     auto kern = attn_prefill_tc_kernel<C, P>;                                                                \
