@@ -371,6 +371,42 @@ def test_persistent_decode_kernel_matches_launch_chain(pkg, tiny_hf, monkeypatch
     assert torch.equal(outs[1][0], outs[1][1]), "the persistent kernel must be run-to-run deterministic"
 
 
+@pytest.mark.parametrize("B,T,new,pad", [(1, 9, 24, 0), (2, 33, 24, 0), (1, 200, 40, 0), (2, 200, 30, 57), (2, 130, 20, 129)])
+def test_cooperative_fp32_decode_matches_launch_chain_and_oracle(pkg, tiny_hf, monkeypatch, B, T, new, pad):
+    """The cooperative fp32 decode kernel (one or two sequences, csrc/decode_f32_persistent.cu) against the launch chain
+    (TUTOR_F32_PERSISTENT=0) and the oracle: identical ids, including contexts long enough for several key ranges per
+    head (partial softmax states merged by the last CTA to arrive) and a left-padded second row."""
+    ids = rp.gpt2_prompt_ids(B, T, seed=41 + T, vocab=1000)
+    mask = None
+    if pad:
+        mask = torch.ones_like(ids)
+        mask[B - 1, :pad] = 0
+        ids[B - 1, :pad] = 999
+    kw = dict(max_new_tokens=new, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
+    outs = []
+    for flag in ("0", "1"):
+        monkeypatch.setenv("TUTOR_F32_PERSISTENT", flag)
+        eng = pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="fp32")
+        outs.append([eng.generate(ids, attention_mask=mask, **kw) for _ in range(2)])
+    monkeypatch.delenv("TUTOR_F32_PERSISTENT")
+    assert torch.equal(outs[1][0], outs[1][1]), "run-to-run deterministic"
+    assert torch.equal(outs[0][0], outs[1][0]), "cooperative kernel and launch chain disagree"
+    ref = rp.generate(tiny_hf, ids, attention_mask=mask, **kw) if pad else rp.generate(tiny_hf, ids, **kw)
+    assert torch.equal(outs[1][0], ref)
+
+
+def test_cooperative_fp32_decode_on_gpt2_small_two_sequences(pkg, small_hf, monkeypatch):
+    """d = 768, two sequences, a context that needs several key ranges per head: ids identical to the launch chain."""
+    ids = rp.gpt2_prompt_ids(2, 260, seed=5)
+    outs = []
+    for flag in ("0", "1"):
+        monkeypatch.setenv("TUTOR_F32_PERSISTENT", flag)
+        eng = pkg.B200GPT2LMHeadModel.from_hf(small_hf, dtype="fp32")
+        outs.append(eng.generate(ids, max_new_tokens=24, repetition_penalty=1.2))
+    monkeypatch.delenv("TUTOR_F32_PERSISTENT")
+    assert torch.equal(outs[0], outs[1])
+
+
 def test_long_prompt_then_short_prompt_on_one_bf16_engine(pkg, tiny_hf):
     """The captured decode graph bakes in how many prompt rows the attention may stream ahead of its wait.  A long prompt
     followed by a short one on the SAME engine must not replay the long prompt's bound (advisor finding, round 1): the
