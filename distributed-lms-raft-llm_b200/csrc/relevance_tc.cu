@@ -23,6 +23,8 @@
 #include <cuda.h>
 #include <math_constants.h>
 
+#include <cstdlib>
+
 #include "kernels.h"
 #include "tc_ptx.cuh"
 
@@ -63,6 +65,7 @@ __global__ void __launch_bounds__(256) split_queries_kernel(const float* __restr
   __shared__ float red[8];
   const int q = blockIdx.x;
   if (threadIdx.x == 0) counters[q] = 0;  // arrival counters of the re-scoring CTAs (topk_rescore_kernel)
+  if (threadIdx.x == 0 && q == 0) counters[TS_NQ] = 0;  // "the filter pass could not be proven exact"
   float s = 0.f;
   for (int i = threadIdx.x; i < D; i += blockDim.x) {
     const float x = q < Q ? queries[(size_t)q * D + i] : 0.f;
@@ -81,12 +84,18 @@ __global__ void __launch_bounds__(256) split_queries_kernel(const float* __restr
   }
 }
 
-__global__ void __launch_bounds__(TS_THREADS) cosine_scan_tf32x3_kernel(const __grid_constant__ CUtensorMap tmC,
-                                                                      const __grid_constant__ CUtensorMap tmQh,
-                                                                      const __grid_constant__ CUtensorMap tmQl,
-                                                                      const float* __restrict__ inv_norm,
-                                                                      const float* __restrict__ qinv, int Q, int N, int D,
-                                                                      float* __restrict__ scores, float* __restrict__ gmax) {
+// FILTER: one plain TF32 product per k-block (no split, no cross terms): scores good to ~2e-3, used only to pick the
+// candidate groups that are then re-scored in fp32 (see k_cosine_scan_tc).  run_flag != null: a pass that only runs when
+// the flag is set (the exact pass behind a filter pass whose result could not be proven exact).
+template <bool FILTER>
+__global__ void __launch_bounds__(TS_THREADS) cosine_scan_tf32_kernel(const __grid_constant__ CUtensorMap tmC,
+                                                                    const __grid_constant__ CUtensorMap tmQh,
+                                                                    const __grid_constant__ CUtensorMap tmQl,
+                                                                    const float* __restrict__ inv_norm,
+                                                                    const float* __restrict__ qinv, int Q, int N, int D,
+                                                                    float* __restrict__ scores, float* __restrict__ gmax,
+                                                                    const int* __restrict__ run_flag) {
+  if (run_flag && *reinterpret_cast<const volatile int*>(run_flag) == 0) return;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + TS_STAGES * TS_STAGE_BYTES);
@@ -126,11 +135,11 @@ __global__ void __launch_bounds__(TS_THREADS) cosine_scan_tf32x3_kernel(const __
         for (int kb = 0; kb < nk; ++kb, ++it) {
           const int s = it % TS_STAGES;
           mbar_wait(&empty_bar[s], ((it / TS_STAGES) & 1) ^ 1, 0);
-          mbar_expect_tx(&full_bar[s], TS_A_BYTES + 2 * TS_Q_BYTES);
+          mbar_expect_tx(&full_bar[s], TS_A_BYTES + (FILTER ? 1 : 2) * TS_Q_BYTES);
           uint8_t* st = tiles + s * TS_STAGE_BYTES;
           tma_load_2d(st, &tmC, &full_bar[s], kb * TS_BK, t * TS_BM);  // rows past N are zero-filled
           tma_load_2d(st + 2 * TS_A_BYTES, &tmQh, &full_bar[s], kb * TS_BK, 0);
-          tma_load_2d(st + 2 * TS_A_BYTES + TS_Q_BYTES, &tmQl, &full_bar[s], kb * TS_BK, 0);
+          if (!FILTER) tma_load_2d(st + 2 * TS_A_BYTES + TS_Q_BYTES, &tmQl, &full_bar[s], kb * TS_BK, 0);
         }
       }
     }
@@ -150,15 +159,19 @@ __global__ void __launch_bounds__(TS_THREADS) cosine_scan_tf32x3_kernel(const __
           for (int kb = kb0; kb < kb1; ++kb, ++it) {
             const int s = it % TS_STAGES;
             mbar_wait(&full_bar[s], (it / TS_STAGES) & 1, 1);   // the query blocks (TMA) have landed
-            mbar_wait(&split_bar[s], (it / TS_STAGES) & 1, 1);  // c_hi / c_lo have been written
+            if (!FILTER) mbar_wait(&split_bar[s], (it / TS_STAGES) & 1, 1);  // c_hi / c_lo have been written
             tc_fence_after();
             const uint32_t c_hi = smem_u32(tiles + s * TS_STAGE_BYTES);
             const uint32_t c_lo = c_hi + TS_A_BYTES, q_hi = c_hi + 2 * TS_A_BYTES;  // q_lo follows q_hi: one 64-row tile
 #pragma unroll
             for (int k = 0; k < TS_BK / 8; ++k) {  // 8 TF32 = 32 bytes along K per MMA, inside the 128-byte swizzle atom
               const uint32_t first = (kb != kb0 || k != 0);
-              tc_mma_tf32(d_main, umma_desc_sw128(c_hi + k * 32), umma_desc_sw128(q_hi + k * 32), idesc64, first);
-              tc_mma_tf32(d_cross, umma_desc_sw128(c_lo + k * 32), umma_desc_sw128(q_hi + k * 32), idesc32, first);
+              if (FILTER) {  // the raw tile read as TF32 against q_hi only
+                tc_mma_tf32(d_main, umma_desc_sw128(c_hi + k * 32), umma_desc_sw128(q_hi + k * 32), idesc32, first);
+              } else {
+                tc_mma_tf32(d_main, umma_desc_sw128(c_hi + k * 32), umma_desc_sw128(q_hi + k * 32), idesc64, first);
+                tc_mma_tf32(d_cross, umma_desc_sw128(c_lo + k * 32), umma_desc_sw128(q_hi + k * 32), idesc32, first);
+              }
             }
             tc_commit(&empty_bar[s]);
           }
@@ -170,7 +183,7 @@ __global__ void __launch_bounds__(TS_THREADS) cosine_scan_tf32x3_kernel(const __
     // ===== splitters: c -> c_hi (in place) and c_lo; 128 threads, consecutive 16-byte vectors =====
     const int tid = threadIdx.x - 64;
     uint32_t it = 0;
-    for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    for (int t = blockIdx.x; !FILTER && t < ntiles; t += gridDim.x) {
       for (int kb = 0; kb < nk; ++kb, ++it) {
         const int s = it % TS_STAGES;
         mbar_wait(&full_bar[s], (it / TS_STAGES) & 1, 4);
@@ -210,13 +223,17 @@ __global__ void __launch_bounds__(TS_THREADS) cosine_scan_tf32x3_kernel(const __
         tc_fence_after();
         float vm[32], vc[32], vd[32];
         const uint32_t taddr = tmem_base + buf * 128 + ((uint32_t)(quad * 32) << 16);
-        tc_ld32x2(taddr, taddr + TS_NQ, vm, vc);  // c_hi.q_hi, c_hi.q_lo
-        tc_ld32(taddr + 2 * TS_NQ, vd);           // c_lo.q_hi
+        if (FILTER) {
+          tc_ld32(taddr, vm);
+        } else {
+          tc_ld32x2(taddr, taddr + TS_NQ, vm, vc);  // c_hi.q_hi, c_hi.q_lo
+          tc_ld32(taddr + 2 * TS_NQ, vd);           // c_lo.q_hi
+        }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
 #pragma unroll
-        for (int q = 0; q < 32; ++q) sum[q] += vm[q] + (vc[q] + vd[q]);  // round-to-nearest adds of the segment sums
+        for (int q = 0; q < 32; ++q) sum[q] += FILTER ? vm[q] : vm[q] + (vc[q] + vd[q]);  // round-to-nearest adds of the segment sums
       }
       // scores out (32 consecutive rows per query: coalesced), and the maximum of this warp's 32 rows per query:
       // the k best rows of a query lie in at most k such groups, so the top-k only has to look at k x 32 scores
@@ -284,7 +301,9 @@ __device__ __forceinline__ void merge_sorted_lists(const float (*lv)[32], const 
 // the sorted lists (k block-wide arg-max rounds with two barriers each took 10x longer).  k <= 32.
 constexpr int TK_THREADS = 1024;
 __global__ void __launch_bounds__(TK_THREADS) topk_select_groups_kernel(const float* __restrict__ gmax, int N, int G, int k,
-                                                                       int* __restrict__ sel_out) {
+                                                                       int* __restrict__ sel_out, float* __restrict__ last_out,
+                                                                       const int* __restrict__ run_flag) {
+  if (run_flag && *reinterpret_cast<const volatile int*>(run_flag) == 0) return;
   extern __shared__ float sg[];  // [G] group maxima of this query
   __shared__ float lv[32][32];   // per-warp sorted lists
   __shared__ int lk[32][32];
@@ -314,7 +333,11 @@ __global__ void __launch_bounds__(TK_THREADS) topk_select_groups_kernel(const fl
   __syncthreads();
   if (warp == 0)
     merge_sorted_lists(lv, lk, k, lane, [&](int round, float v, int key) {
-      if (lane == 0) sel_out[q * 32 + round] = (key == 0x7fffffff || v == -CUDART_INF_F) ? -1 : key;
+      if (lane == 0) {
+        sel_out[q * 32 + round] = (key == 0x7fffffff || v == -CUDART_INF_F) ? -1 : key;
+        // the smallest selected maximum: every group that was NOT selected has a maximum <= this one
+        if (last_out && round == k - 1) last_out[q] = (key == 0x7fffffff) ? -CUDART_INF_F : v;
+      }
     });
 }
 
@@ -323,9 +346,12 @@ template <int NV>  // float4 per lane and row: d = 128 NV
 __global__ void __launch_bounds__(256) topk_rescore_kernel(const float* __restrict__ queries, const float* __restrict__ qinv,
                                                           const float* __restrict__ corpus,
                                                           const float* __restrict__ inv_norm, const int* __restrict__ sel,
-                                                          int N, int k, float* __restrict__ cand, int* __restrict__ counters,
-                                                          float* __restrict__ out_v, int32_t* __restrict__ out_i,
-                                                          int idx_base) {
+                                                          int N, int ng, int k, float* __restrict__ cand,
+                                                          int* __restrict__ counters, float* __restrict__ out_v,
+                                                          int32_t* __restrict__ out_i, int idx_base,
+                                                          const float* __restrict__ unselected_max, float margin,
+                                                          int* __restrict__ inexact, const int* __restrict__ run_flag) {
+  if (run_flag && *reinterpret_cast<const volatile int*>(run_flag) == 0) return;
   constexpr int D = 128 * NV;
   __shared__ int s_last;
   const int r = blockIdx.x, q = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -355,7 +381,7 @@ __global__ void __launch_bounds__(256) topk_rescore_kernel(const float* __restri
   }
   __threadfence();
   __syncthreads();
-  if (threadIdx.x == 0) s_last = atomicAdd(&counters[q], 1) == k - 1;
+  if (threadIdx.x == 0) s_last = atomicAdd(&counters[q], 1) == ng - 1;
   __syncthreads();
   if (!s_last) return;
   __threadfence();
@@ -368,7 +394,7 @@ __global__ void __launch_bounds__(256) topk_rescore_kernel(const float* __restri
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const int gi = warp * 4 + j;
-    const int gj = gi < k ? sel[q * 32 + gi] : -1;
+    const int gj = gi < ng ? sel[q * 32 + gi] : -1;
     const int row = gj >= 0 ? gj * 32 + lane : N;
     rk[j] = row < N ? row : 0x7fffffff;
     v[j] = row < N ? __ldcg(cand + (size_t)q * 1024 + gi * 32 + lane) : -CUDART_INF_F;
@@ -394,6 +420,11 @@ __global__ void __launch_bounds__(256) topk_rescore_kernel(const float* __restri
       if (lane == 0) {
         out_v[(size_t)q * k + round] = bk != 0x7fffffff ? bv : -CUDART_INF_F;
         out_i[(size_t)q * k + round] = bk != 0x7fffffff ? idx_base + bk : -1;
+        // filter pass: a row outside the candidate groups scored at most unselected_max in the TF32 scan, i.e. at most
+        // unselected_max + margin exactly; unless the k-th exact score is above that, the exact pass has to run
+        if (inexact && round == k - 1 && unselected_max[q] != -CUDART_INF_F &&
+            !(bk != 0x7fffffff && bv > unselected_max[q] + margin))
+          atomicExch(inexact, 1);
       }
     });
   }
@@ -405,8 +436,13 @@ __global__ void __launch_bounds__(256) topk_rescore_kernel(const float* __restri
 size_t k_cosine_scan_tc_scratch_bytes(int d, int N) {
   return round_up((size_t)2 * TS_NQ * d * sizeof(float) + TS_NQ * sizeof(float), 256) +
          round_up((size_t)TS_NQ * ceil_div(N, TS_BM) * 4 * sizeof(float), 256) +  // split queries + group maxima
-         (size_t)TS_NQ * (32 * sizeof(int) + 1024 * sizeof(float) + sizeof(int));  // selected groups, re-scored rows, counters
+         // selected groups, re-scored rows, counters + the "inexact" flag, smallest selected maximum per query
+         (size_t)TS_NQ * (32 * sizeof(int) + 1024 * sizeof(float) + sizeof(int) + sizeof(float)) + 256;
 }
+
+// TF32 reads operands truncated to 10 mantissa bits: each product is off by < 2^-9 relative, so a cosine by < 2^-9
+// (Cauchy-Schwarz on the normalised vectors), plus the truncating accumulation (< 2e-5 over 768 dims)
+constexpr float TS_FILTER_MARGIN = 3e-3f;
 
 int k_cosine_scan_tc(const float* queries, const float* corpus, const float* corpus_inv_norm, int Q, int N, int d,
                      float eps, float* scores, void* scratch, int k, float* out_scores, int32_t* out_idx, int idx_base,
@@ -420,36 +456,55 @@ int k_cosine_scan_tc(const float* queries, const float* corpus, const float* cor
   int* sel = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(gmax) +
                                     round_up((size_t)TS_NQ * ceil_div(N, TS_BM) * 4 * sizeof(float), 256));
   float* cand = reinterpret_cast<float*>(sel + TS_NQ * 32);
-  int* counters = reinterpret_cast<int*>(cand + (size_t)TS_NQ * 1024);
+  int* counters = reinterpret_cast<int*>(cand + (size_t)TS_NQ * 1024);  // [TS_NQ] arrivals, [TS_NQ] = inexact flag
+  int* inexact = counters + TS_NQ;
+  float* sel_min = reinterpret_cast<float*>(counters + TS_NQ + 1);
   split_queries_kernel<<<TS_NQ, 256, 0, st>>>(queries, Q, d, eps, q_hi, q_lo, qinv, counters);
   KERNEL_LAUNCHED();
   CUtensorMap tc, th, tl;
   TRY(k_make_map_2d(&tc, corpus, 4, N, d, TS_BM, TS_BK));
   TRY(k_make_map_2d(&th, q_hi, 4, TS_NQ, d, TS_NQ, TS_BK));
   TRY(k_make_map_2d(&tl, q_lo, 4, TS_NQ, d, TS_NQ, TS_BK));
-  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(cosine_scan_tf32x3_kernel), TS_SMEM));
+  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(cosine_scan_tf32_kernel<false>), TS_SMEM));
+  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(cosine_scan_tf32_kernel<true>), TS_SMEM));
   int dev = 0, sms = 148;
   CUDA_TRY(cudaGetDevice(&dev));
   CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const int ntiles = ceil_div(N, TS_BM);
-  // scores == nullptr: the score matrix is not written (the top-k below re-scores the few rows it looks at)
-  cosine_scan_tf32x3_kernel<<<ntiles < sms ? ntiles : sms, TS_THREADS, TS_SMEM, st>>>(tc, th, tl, corpus_inv_norm, qinv, Q, N, d,
-                                                                                nullptr, gmax);
-  KERNEL_LAUNCHED();
-  // top-k straight from the group maxima (k <= 32, and the maxima of one query must fit in shared memory)
+  const int ntiles = ceil_div(N, TS_BM), nctas = ntiles < sms ? ntiles : sms;
+  // top-k straight from 32-row group maxima (k <= 32, and the maxima of one query must fit in shared memory); the score
+  // matrix itself is never written (the top-k re-scores the few rows it looks at)
   const int G = ntiles * 4;
   ARG_CHECK(k >= 1 && k <= 32 && (d == 128 || d == 768) && (size_t)G * 4 <= 200 * 1024,
             "cosine_scan_tc: k=%d / %d row groups / d=%d unsupported", k, G, d);
   TRY(tutor_set_max_smem(reinterpret_cast<const void*>(topk_select_groups_kernel), 200 * 1024));
-  topk_select_groups_kernel<<<Q, TK_THREADS, (size_t)G * 4, st>>>(gmax, N, G, k, sel);
-  KERNEL_LAUNCHED();
-  if (d == 768)
-    topk_rescore_kernel<6><<<dim3(k, Q), 256, 0, st>>>(queries, qinv, corpus, corpus_inv_norm, sel, N, k, cand, counters,
-                                                       out_scores, out_idx, idx_base);
-  else
-    topk_rescore_kernel<1><<<dim3(k, Q), 256, 0, st>>>(queries, qinv, corpus, corpus_inv_norm, sel, N, k, cand, counters,
-                                                       out_scores, out_idx, idx_base);
   (void)scores;
+  auto topk = [&](int ng, bool filter_pass, const int* run_flag) {
+    topk_select_groups_kernel<<<Q, TK_THREADS, (size_t)G * 4, st>>>(gmax, N, G, ng, sel, filter_pass ? sel_min : nullptr, run_flag);
+    KERNEL_LAUNCHED();
+    if (d == 768)
+      topk_rescore_kernel<6><<<dim3(ng, Q), 256, 0, st>>>(queries, qinv, corpus, corpus_inv_norm, sel, N, ng, k, cand, counters,
+                                                          out_scores, out_idx, idx_base, sel_min, TS_FILTER_MARGIN,
+                                                          filter_pass ? inexact : nullptr, run_flag);
+    else
+      topk_rescore_kernel<1><<<dim3(ng, Q), 256, 0, st>>>(queries, qinv, corpus, corpus_inv_norm, sel, N, ng, k, cand, counters,
+                                                          out_scores, out_idx, idx_base, sel_min, TS_FILTER_MARGIN,
+                                                          filter_pass ? inexact : nullptr, run_flag);
+    KERNEL_LAUNCHED();
+  };
+  // Filter pass: plain TF32 scan (a third of the MMA work, no operand split: the scan is then bound by HBM, not by
+  // shared memory), the 32 best groups re-scored in fp32.  The result is exact when the k-th exact score clears every
+  // unselected group's TF32 maximum by the TF32 error bound; when it does not (near-duplicate rows around rank k), a flag
+  // lets the error-compensated 3xTF32 pass below run and overwrite the result - otherwise its kernels return at once.
+  static const bool filter_off = getenv("TUTOR_SCAN_NO_FILTER") != nullptr;  // cross-check switch for the tests
+  const bool filter = !filter_off && 3 * k <= 32;
+  if (filter) {
+    cosine_scan_tf32_kernel<true><<<nctas, TS_THREADS, TS_SMEM, st>>>(tc, th, tl, corpus_inv_norm, qinv, Q, N, d, nullptr, gmax, nullptr);
+    KERNEL_LAUNCHED();
+    topk(32, true, nullptr);
+  }
+  const int* flag = filter ? inexact : nullptr;
+  cosine_scan_tf32_kernel<false><<<nctas, TS_THREADS, TS_SMEM, st>>>(tc, th, tl, corpus_inv_norm, qinv, Q, N, d, nullptr, gmax, flag);
   KERNEL_LAUNCHED();
+  topk(k, false, flag);
   return TUTOR_OK;
 }

@@ -51,6 +51,29 @@ def test_sharded_equals_unsharded_single_gpu(pkg):
     assert torch.equal(out_i, full_i) and torch.equal(out_s, full_s)
 
 
+def test_near_ties_around_rank_k_fall_back_to_the_exact_scan(pkg):
+    """The plain-TF32 filter scan cannot rank rows whose cosines differ by less than its error (~2e-3): 200 planted rows
+    spaced 1e-4 apart around the top of query 0's ranking, each in a different 32-row group.  The library must notice that
+    its candidate set is not provably complete and run the error-compensated scan: index sets identical to the oracle."""
+    N, Q, k, d = 120_000, 4, 10, 768
+    g = torch.Generator().manual_seed(11)
+    c = corpus(N, d, seed=12)
+    q = torch.randn(Q, d, generator=g)
+    q0 = q[0] / q[0].norm()
+    for j in range(200):
+        u = torch.randn(d, generator=g)
+        u = u - (u @ q0) * q0
+        u = u / u.norm()
+        cos = 0.9 - 1e-4 * j
+        c[j * 577 + 5] = cos * q0 + (1 - cos * cos) ** 0.5 * u
+    s, i = pkg.CorpusShard(c.cuda()).topk(q.cuda(), k)
+    torch.cuda.synchronize()
+    rs, ri = rp.corpus_topk(q, c, k)
+    assert torch.equal(i.cpu().long(), ri)
+    assert (s.cpu() - rs).abs().max().item() < 1e-4
+    assert ri[0].tolist() == [j * 577 + 5 for j in range(k)]
+
+
 def test_full_size_properties(pkg):
     """1M x 768 fp32 corpus (3.07 GB): planted rows must be found, scores sorted, self-similarity 1."""
     N, Q, k = 1_000_000, 32, 10
