@@ -40,12 +40,43 @@ template <> struct Vec16<bf16> {
 // them for its own (b,h) - bias + fixed-order sum - appends the new K/V row to the cache (DynamicLayer.update,
 // HF/cache_utils.py:119-120, without the torch.cat) and attends over positions [0,len) with the fresh row taken
 // from shared memory, so the q/k/v of the current token never make a round trip through HBM.
+// One element of q / k / v of the current token from the c_attn split-K partials (FUSED kernels).  With a folded LayerNorm
+// (gemm_decode_fused.cu) the partial sums are x . W' and the LayerNorm enters here: rstd (sum - mean s[n]) + c[n] + bias[n].
+__device__ __forceinline__ float qkv_from_partials(const float* __restrict__ qkv_partial, int ks, const float* __restrict__ qkv_bias,
+                                                   const QkvFold& fold, int B, int b, int n, int d) {
+  float mean = 0.f, rstd = 1.f, sn = 0.f, add = qkv_bias[n];
+  if (fold.s) {
+    const float2* st2 = reinterpret_cast<const float2*>(fold.stats) + b;
+    float2 tv[16];  // every pair is requested before the first is used
+#pragma unroll
+    for (int i = 0; i < 16; ++i) tv[i] = i < fold.nst ? st2[(size_t)i * B] : make_float2(0.f, 0.f);
+    sn = fold.s[n];
+    add += fold.c[n];
+    float sm = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) sm += tv[i].x;
+    mean = sm / (float)fold.nst;
+    const float n_per = (float)(d / fold.nst);
+    float m2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const float dm = tv[i].x - mean;
+      if (i < fold.nst) m2 += tv[i].y + n_per * dm * dm;
+    }
+    rstd = 1.0f / sqrtf(m2 / (float)d + fold.eps);
+  }
+  float acc = fold.s ? 0.f : add;
+#pragma unroll 8
+  for (int zz = 0; zz < ks; ++zz) acc += qkv_partial[((size_t)zz * B + b) * (3 * d) + n];
+  return fold.s ? fmaf(rstd, acc - mean * sn, add) : acc;
+}
+
 template <typename QT, typename KT, typename OT, bool FAST, bool FUSED>
 __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__ q, KT* kc, KT* vc,
                                                           OT* __restrict__ out, int H, int Smax,
                                                           const int* __restrict__ len_dev, int len_host,
                                                           const float* __restrict__ qkv_partial, int ks,
-                                                          const float* __restrict__ qkv_bias, int B,
+                                                          const float* __restrict__ qkv_bias, int B, const QkvFold fold,
                                                           float* split_scratch, int* split_counters,
                                                           const int* __restrict__ npad) {
   constexpr int EPL = Vec16<KT>::N;  // elements per lane
@@ -75,9 +106,7 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
     for (int e = threadIdx.x; e < 192; e += 128) {
       const int which = e >> 6, i = e & 63;
       const int n = which * d + h * 64 + i;
-      float acc = qkv_bias[n];
-#pragma unroll 8
-      for (int zz = 0; zz < ks; ++zz) acc += qkv_partial[((size_t)zz * B + b) * (3 * d) + n];
+      const float acc = qkv_from_partials(qkv_partial, ks, qkv_bias, fold, B, b, n, d);
       if (which == 0) {
         s_new[0][i] = acc;
       } else {
@@ -250,7 +279,8 @@ __global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf
                                                                     const int* __restrict__ len_dev, int len_host,
                                                                     const float* __restrict__ qkv_partial, int ks,
                                                                     const float* __restrict__ qkv_bias, int B,
-                                                                    const int* __restrict__ npad, int safe_rows) {
+                                                                    const QkvFold fold, const int* __restrict__ npad,
+                                                                    int safe_rows) {
   constexpr int EPL = 8, LPR = 8, KPW = 4, NG = 16, UNR = DK_CHUNK / NG;
   __shared__ __align__(128) bf16 sK[DK_STAGES][DK_CHUNK * 64];
   __shared__ __align__(128) bf16 sV[DK_STAGES][DK_CHUNK * 64];
@@ -319,10 +349,7 @@ __global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf
         accv[r] = 0.f;
         if (e < 192) {
           const int n = (e >> 6) * d + h * 64 + (e & 63);
-          float acc = qkv_bias[n];
-#pragma unroll 8
-          for (int zz = 0; zz < ks; ++zz) acc += qkv_partial[((size_t)zz * B + b) * (3 * d) + n];
-          accv[r] = acc;
+          accv[r] = qkv_from_partials(qkv_partial, ks, qkv_bias, fold, B, b, n, d);
         }
       }
 #pragma unroll
@@ -1008,13 +1035,13 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
   static const bool f32_plain = tutor_experiment("TUTOR_ATTN_PDL") == nullptr;
   if (q_dtype == DT_F32 && kv_dtype == DT_F32 && out_dtype == DT_F32 && f32_plain)
     attn_decode_kernel<float, float, float, false, false><<<grid, block, 0, st>>>(
-        (const float*)q, (float*)k, (float*)v, (float*)out, H, Smax, len_dev, len_host, nullptr, 0, nullptr, B, nullptr,
+        (const float*)q, (float*)k, (float*)v, (float*)out, H, Smax, len_dev, len_host, nullptr, 0, nullptr, B, QkvFold{}, nullptr,
         nullptr, npad);
   else if (q_dtype == DT_F32 && kv_dtype == DT_F32 && out_dtype == DT_F32)
     // (through tutor_launch: part of the fp32 decode chain's programmatic dependent launches; the kernel waits first)
     CUDA_TRY(tutor_launch(attn_decode_kernel<float, float, float, false, false>, grid, block, 0, st, (const float*)q,
                           (float*)k, (float*)v, (float*)out, H, Smax, len_dev, len_host, (const float*)nullptr, 0,
-                          (const float*)nullptr, B, (float*)nullptr, (int*)nullptr, npad));
+                          (const float*)nullptr, B, QkvFold{}, (float*)nullptr, (int*)nullptr, npad));
   else if (q_dtype == DT_BF16 && kv_dtype == DT_BF16 && out_dtype == DT_BF16) {
 #ifdef TUTOR_EXPERIMENTS
     if (use_mma_decode()) {
@@ -1028,7 +1055,7 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
 #endif
     {
       attn_decode_tma_kernel<false, 64, 2, true><<<grid, DK_THREADS, 0, st>>>((const bf16*)q, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax,
-                                                                 len_dev, len_host, nullptr, 0, nullptr, B, npad, 0);
+                                                                 len_dev, len_host, nullptr, 0, nullptr, B, QkvFold{}, npad, 0);
     }
   } else {
     tutor_set_error("attn_decode: unsupported dtype combination q=%d kv=%d out=%d", q_dtype, kv_dtype, out_dtype);
@@ -1038,19 +1065,21 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
   return TUTOR_OK;
 }
 
-int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias, void* k, void* v, int kv_dtype,
-                        void* out, int out_dtype, int B, int H, int Smax, const int* len_dev, int len_host,
+int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias, const QkvFold& fold, void* k, void* v,
+                        int kv_dtype, void* out, int out_dtype, int B, int H, int Smax, const int* len_dev, int len_host,
                         int nsplit, void* split_scratch, const int* npad, int safe_rows, int len_hint,
                         cudaStream_t st) {
   if (B == 0) return TUTOR_OK;
   ARG_CHECK(kv_dtype == DT_BF16 && out_dtype == DT_BF16, "attn_decode_fused: bf16 cache and output only");
   ARG_CHECK(qkv_partial && qkv_bias && ks >= 1, "attn_decode_fused: bad partials");
+  ARG_CHECK(!fold.s || (fold.c && fold.stats && fold.nst >= 1 && fold.nst <= 16), "attn_decode_fused: bad folded-LayerNorm operands");
   ARG_CHECK(len_dev || (len_host >= 1 && len_host <= Smax), "attn_decode_fused: len %d outside [1,%d]", len_host, Smax);
   ARG_CHECK(nsplit >= 1 && nsplit <= 8 && (nsplit == 1 || split_scratch), "attn_decode_fused: bad split setup");
   float* sc = reinterpret_cast<float*>(split_scratch);
   int* counters = reinterpret_cast<int*>(sc + (size_t)B * H * 8 * 66);  // zeroed by the owner; self-resetting
 #ifdef TUTOR_EXPERIMENTS
   if (use_mma_decode()) {
+    ARG_CHECK(!fold.s, "attn_decode_fused: the mma.sync experiment has no folded-LayerNorm path");
     CUtensorMap tk, tv;
     TRY(k_make_map_bf16(&tk, (const bf16*)k, B * H * Smax, 64, DM_CHUNK));
     TRY(k_make_map_bf16(&tv, (const bf16*)v, B * H * Smax, 64, DM_CHUNK));
@@ -1065,14 +1094,14 @@ int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias,
 #endif
   if (nsplit == 1) {
     CUDA_TRY(tutor_launch(attn_decode_tma_kernel<true, 64, 2, true>, dim3(H, B), dim3(DK_THREADS), 0, st, (const bf16*)nullptr,
-                          (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B,
+                          (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B, fold,
                           npad, safe_rows));
     KERNEL_LAUNCHED();
     return TUTOR_OK;
   }
   CUDA_TRY(tutor_launch(attn_decode_kernel<bf16, bf16, bf16, true, true>, dim3(H, B, nsplit), dim3(128), 0, st,
                         (const bf16*)nullptr, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks,
-                        qkv_bias, B, sc, counters, npad));
+                        qkv_bias, B, fold, sc, counters, npad));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }

@@ -187,7 +187,7 @@ int tutor_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_b
   ARG_CHECK(qkv_partial && qkv_bias && k && v && out, "attn_decode_fused: null argument");
   ARG_CHECK(len >= 1 && len <= Smax, "attn_decode_fused: len %d outside [1,%d]", len, Smax);
   const int safe = ((len - 1 < 128 ? len - 1 : 128) / 64) * 64;  // what the engine allows to stream ahead of the wait
-  return k_attn_decode_fused(qkv_partial, ks, qkv_bias, k, v, DT_BF16, out, DT_BF16, B, H, Smax, nullptr, len, 1, nullptr,
+  return k_attn_decode_fused(qkv_partial, ks, qkv_bias, QkvFold{}, k, v, DT_BF16, out, DT_BF16, B, H, Smax, nullptr, len, 1, nullptr,
                              nullptr, safe, len, (cudaStream_t)stream);
 }
 
@@ -216,7 +216,7 @@ int sm_count() {
 
 int tutor_row_tile_stats(const float* x, float* stats, int M, int d, void* stream) {
   ARG_CHECK(x && stats, "row_tile_stats: null argument");
-  return k_row_tile_stats(x, stats, M, d, (cudaStream_t)stream);
+  return k_row_tile_stats(x, stats, M, d, nullptr, (cudaStream_t)stream);
 }
 
 int tutor_decode_ln_linear_partial(const float* x, const float* stats, const float* gamma, const float* beta, float eps,
@@ -242,7 +242,7 @@ int tutor_decode_linear_residual(const void* A, const void* W, const float* bias
   ARG_CHECK(A && W && bias && x && stats, "decode_linear_residual: null argument");
   if (bn <= 0) bn = k_decode_batch_tile(M);
   if (ks <= 0) ks = k_pick_cluster_splitk(N, K, ceil_div(M, bn), sm_count());
-  return k_gemm_resid_stats((const bf16*)A, (const bf16*)W, bias, M, N, K, ks, bn, x, stats, (cudaStream_t)stream);
+  return k_gemm_resid_stats((const bf16*)A, (const bf16*)W, bias, M, N, K, ks, bn, x, stats, nullptr, (cudaStream_t)stream);
 }
 
 int tutor_meanpool(const float* x, float* out, int B, int T, int d, void* stream) {

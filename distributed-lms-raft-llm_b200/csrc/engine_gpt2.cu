@@ -64,6 +64,11 @@ struct tutor_gpt2 {
   bool use_fused = true, use_pdl = true;
   bool use_cluster = true;   // TUTOR_NO_CLUSTER=1: the 8-launch-per-layer chain (separate reduce kernels) for A/B runs
   float* ln_stats = nullptr;  // [d/128][B][2] per-row (mean, M2) of x over each 128-column tile, one slice per lane
+  // TUTOR_FOLD=1: LayerNorm folded into c_attn / c_fc (gemm_decode_fused.cu): their operand is xb = bf16(x), kept next
+  // to x by whoever writes x.  Measured 614 vs 605 us per forward at B = 64 (the TMA operand arrives no earlier than the
+  // hand-normalised one, and the attention prologue and the residual epilogues do more): opt-in, default off.
+  bool use_fold = false;
+  bf16* xb = nullptr;         // [B, d]
   size_t ln_stats_lane_elems = 0;
   bool no_ln_gemv = false;   // TUTOR_NO_LN_GEMV=1: separate LayerNorm kernels even for 1-2 rows (A/B measurements)
   bool use_ln_gemv = false;  // TUTOR_LN_GEMV=1: LayerNorm folded into the fp32 decode GEMVs - measured slower (2213 vs 2560 tok/s)
@@ -288,7 +293,7 @@ int forward_decode_fused(tutor_gpt2* e, int lane, int b0, int B) {
     void* vc = (uint8_t*)e->vcache(l) + kv_off;
     int ks = k_pick_splitk(3 * d, d, e->num_sms);
     TRY(k_gemm_bf16_splitk(xn, (const bf16*)w.qkv.w, B, 3 * d, d, ks, partial, st));
-    TRY(k_attn_decode_fused(partial, ks, w.qkv.b, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
+    TRY(k_attn_decode_fused(partial, ks, w.qkv.b, QkvFold{}, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
                             e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, npad,
                             e->safe_rows, (e->cur_T + e->cur_total) / 2, st));
     ks = k_pick_splitk(d, d, e->num_sms);
@@ -347,28 +352,49 @@ int forward_decode_cluster(tutor_gpt2* e, int lane, int b0, int B) {
   const char* skip = tutor_experiment("TUTOR_SKIP") ? tutor_experiment("TUTOR_SKIP") : "";
   const int bn_qkv = pl.bn_qkv, bn_fc = pl.bn_fc, bn_res = pl.bn_res;
   const int ks_qkv = pl.ks_qkv, ks_proj = pl.ks_proj, ks_fc = pl.ks_fc, ks_proj2 = pl.ks_proj2;
+  // folded LayerNorm when every layer has its folded weights (they are made at load time when the LayerNorm parameters
+  // arrive before the Conv1D weights, as in a state_dict) and the statistic tiles fit the kernels' register arrays
+  bool fold = e->use_fold && nst <= 16;
+  for (int l = 0; l < e->L; ++l) fold = fold && e->layers[l].fold_qkv && e->layers[l].fold_fc;
+  bf16* xb = fold ? e->xb + (size_t)b0 * d : nullptr;
   TRY(k_gpt2_embed(e->ids + (size_t)b0 * e->ids_ld, e->ids_ld, len, 1, e->wte, e->dt, e->wpe, d, x, B, npad, st));
-  TRY(k_row_tile_stats(x, stats, B, d, st));
+  TRY(k_row_tile_stats(x, stats, B, d, xb, st));
   for (int l = 0; l < e->L; ++l) {
     const Gpt2Layer& w = e->layers[l];
     void* kc = (uint8_t*)e->kcache(l) + kv_off;
     void* vc = (uint8_t*)e->vcache(l) + kv_off;
+    if (fold) {
+      const QkvFold qf{w.qkv_s, w.qkv_c, stats, nst, eps};
+      if (!strchr(skip, 'q')) TRY(k_gemm_fold_splitk(xb, (const bf16*)w.qkv_f, B, 3 * d, d, ks_qkv, bn_qkv, partial, st));
+      if (!strchr(skip, 'a'))
+        TRY(k_attn_decode_fused(partial, ks_qkv, w.qkv.b, qf, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
+                                e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, npad,
+                                e->safe_rows, (e->cur_T + e->cur_total) / 2, st));
+      if (!strchr(skip, 'p'))
+        TRY(k_gemm_resid_stats(att, (const bf16*)w.proj.w, w.proj.b, B, d, d, ks_proj, bn_res, x, stats, xb, st));
+      if (!strchr(skip, 'f'))
+        TRY(k_gemm_fold_act(xb, stats, nst, eps, (const bf16*)w.fc_f, w.fc_s, w.fc_c, w.fc.b, ACT_GELU_TANH, B, 4 * d, d, ks_fc,
+                            bn_fc, hb, st));
+      if (!strchr(skip, 'm'))
+        TRY(k_gemm_resid_stats(hb, (const bf16*)w.proj2.w, w.proj2.b, B, d, 4 * d, ks_proj2, bn_res, x, stats, xb, st));
+      continue;
+    }
     // TUTOR_SKIP=<letters> leaves kernels out of the step (q: c_attn, a: attention, p: c_proj, f: c_fc, m: mlp c_proj,
     // h: LM head) - timing ablation only (tools/gpu_ablate.sh): the tokens are meaningless then
     if (!strchr(skip, 'q'))
       TRY(k_gemm_ln_splitk(x, stats, nst, w.ln1_g, w.ln1_b, eps, (const bf16*)w.qkv.w, B, 3 * d, d, ks_qkv, bn_qkv, partial,
                            st));
     if (!strchr(skip, 'a'))
-      TRY(k_attn_decode_fused(partial, ks_qkv, w.qkv.b, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
+      TRY(k_attn_decode_fused(partial, ks_qkv, w.qkv.b, QkvFold{}, kc, vc, DT_BF16, att, DT_BF16, B, e->H, e->Smax, len, 0,
                               e->attn_splits, (uint8_t*)e->attn_scratch + (size_t)lane * e->attn_scratch_lane_bytes, npad,
                               e->safe_rows, (e->cur_T + e->cur_total) / 2, st));
     if (!strchr(skip, 'p'))
-      TRY(k_gemm_resid_stats(att, (const bf16*)w.proj.w, w.proj.b, B, d, d, ks_proj, bn_res, x, stats, st));
+      TRY(k_gemm_resid_stats(att, (const bf16*)w.proj.w, w.proj.b, B, d, d, ks_proj, bn_res, x, stats, nullptr, st));
     if (!strchr(skip, 'f'))
       TRY(k_gemm_ln_act(x, stats, nst, w.ln2_g, w.ln2_b, eps, (const bf16*)w.fc.w, w.fc.b, ACT_GELU_TANH, B, 4 * d, d, ks_fc,
                         bn_fc, hb, st));
     if (!strchr(skip, 'm'))
-      TRY(k_gemm_resid_stats(hb, (const bf16*)w.proj2.w, w.proj2.b, B, d, 4 * d, ks_proj2, bn_res, x, stats, st));
+      TRY(k_gemm_resid_stats(hb, (const bf16*)w.proj2.w, w.proj2.b, B, d, 4 * d, ks_proj2, bn_res, x, stats, nullptr, st));
   }
   TRY(k_layernorm(x, 1, 0, e->lnf_g, e->lnf_b, eps, nullptr, xl, B, d, st));
   if (strchr(skip, 'h')) return TUTOR_OK;
@@ -602,6 +628,8 @@ int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
       dev_free(e->ln_stats);
       e->ln_stats_lane_elems = (size_t)(d / 128) * nb * 2;
       TRY(dev_alloc(&e->ln_stats, tutor_gpt2::MAX_LANES * e->ln_stats_lane_elems * sizeof(float)));
+      dev_free(e->xb);
+      TRY(dev_alloc(&e->xb, (size_t)nb * d * sizeof(bf16)));
     }
     e->ids_ld = ns;
     e->seen_words = ceil_div(e->V, 32);
@@ -806,6 +834,7 @@ int tutor_gpt2_create(const tutor_gpt2_config* cfg, int device, tutor_gpt2_t** o
   e->use_fused = getenv("TUTOR_NO_FUSED") == nullptr;  // debugging aids: unfused decode kernels / no PDL
   e->use_pdl = getenv("TUTOR_NO_PDL") == nullptr;
   e->use_cluster = getenv("TUTOR_NO_CLUSTER") == nullptr;
+  if (const char* f = getenv("TUTOR_FOLD")) e->use_fold = atoi(f) != 0;
   if (const char* mm = getenv("TUTOR_MEGA")) e->mega_mode = atoi(mm);
   if (const char* pf = getenv("TUTOR_F32_PERSISTENT")) e->use_persist_f32 = atoi(pf) != 0;
   if (!e->use_cluster) e->mega_mode = 0;
@@ -851,7 +880,7 @@ void tutor_gpt2_destroy(tutor_gpt2_t* e) {
   }
   dev_free(e->kv); dev_free(e->x); dev_free(e->xn); dev_free(e->q); dev_free(e->att); dev_free(e->hbuf);
   dev_free(e->xn_last); dev_free(e->ids); dev_free(e->counters); dev_free(e->seen); dev_free(e->finished);
-  dev_free(e->lm_scratch); dev_free(e->partial); dev_free(e->attn_scratch); dev_free(e->npad); dev_free(e->ln_stats);
+  dev_free(e->lm_scratch); dev_free(e->partial); dev_free(e->attn_scratch); dev_free(e->npad); dev_free(e->ln_stats); dev_free(e->xb);
   if (e->h_counters) cudaFreeHost(e->h_counters);
   for (int i = 1; i < tutor_gpt2::MAX_LANES; ++i) {
     if (e->lane_stream[i]) cudaStreamDestroy(e->lane_stream[i]);

@@ -35,14 +35,27 @@ int k_make_map_2d(void* tensor_map, const void* ptr, int elem_bytes, int rows, i
 // stats: [d/128][M][2] = per-row (mean, M2) of x over each 128-column tile.
 int k_decode_batch_tile(int M);
 int k_pick_cluster_splitk(int N, int K, int batch_tiles, int max_ctas);
-int k_row_tile_stats(const float* x, float* stats, int M, int d, cudaStream_t st);
+int k_row_tile_stats(const float* x, float* stats, int M, int d, bf16* xb, cudaStream_t st);  // xb: optional bf16 copy of x
 int k_gemm_ln_splitk(const float* x, const float* stats, int nst, const float* gamma, const float* beta, float eps,
                      const bf16* W, int M, int N, int K, int ks, int bn, float* partial, cudaStream_t st);
 int k_gemm_ln_act(const float* x, const float* stats, int nst, const float* gamma, const float* beta, float eps,
                   const bf16* W, const float* bias, int act, int M, int N, int K, int ks, int bn, bf16* out,
                   cudaStream_t st);
 int k_gemm_resid_stats(const bf16* A, const bf16* W, const float* bias, int M, int N, int K, int ks, int bn, float* x,
-                       float* stats, cudaStream_t st);
+                       float* stats, bf16* xb, cudaStream_t st);  // xb: optional bf16 copy of the new x
+// LayerNorm folded into the weights (Wf = bf16(gamma (.) W), s = row sums of Wf, c = beta . W): operand xb = bf16(x)
+int k_gemm_fold_splitk(const bf16* xb, const bf16* Wf, int M, int N, int K, int ks, int bn, float* partial, cudaStream_t st);
+int k_gemm_fold_act(const bf16* xb, const float* stats, int nst, float eps, const bf16* Wf, const float* s, const float* c,
+                    const float* bias, int act, int M, int N, int K, int ks, int bn, bf16* out, cudaStream_t st);
+// c_attn with a folded LayerNorm: q/k/v[n] = rstd (sum of partials - mean s[n]) + c[n] + bias[n], closed by the attention
+// kernel; s == null: plain partial sums + bias
+struct QkvFold {
+  const float* s;      // [3d]
+  const float* c;      // [3d]
+  const float* stats;  // [nst][B][2] per-tile (mean, M2) of the rows of x
+  int nst;
+  float eps;
+};
 // legacy mma.sync kernel kept only as an on-GPU cross-check of the tcgen05 kernel (tests)
 int k_gemm_bf16_legacy(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpilogue& epi, cudaStream_t st);
 
@@ -62,8 +75,8 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
 // safe_rows: cache rows [0, safe_rows) are final before this launch chain began (the prompt) and may be streamed
 // ahead of the programmatic-launch wait; nsplit > 1 cuts the key range over gridDim.z CTAs per (b,h) (better SM balance); split_scratch holds
 // k_attn_decode_scratch_bytes(B,H) bytes laid out for B rows, zero-initialised once by the owner
-int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias, void* k, void* v, int kv_dtype,
-                        void* out, int out_dtype, int B, int H, int Smax, const int* len_dev, int len_host,
+int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias, const QkvFold& fold, void* k, void* v,
+                        int kv_dtype, void* out, int out_dtype, int B, int H, int Smax, const int* len_dev, int len_host,
                         int nsplit, void* split_scratch, const int* npad, int safe_rows, int len_hint,
                         cudaStream_t st);
 int k_attn_decode_splits(int B, int H, int len_hint, int num_sms);

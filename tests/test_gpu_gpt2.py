@@ -407,6 +407,27 @@ def test_cooperative_fp32_decode_on_gpt2_small_two_sequences(pkg, small_hf, monk
     assert torch.equal(outs[0], outs[1])
 
 
+@pytest.mark.parametrize("B,T", [(3, 17), (40, 60), (100, 20)])
+def test_folded_layernorm_decode_chain_matches_default(pkg, tiny_hf, monkeypatch, B, T):
+    """TUTOR_FOLD=1 (LayerNorm folded into the c_attn / c_fc weights, bf16 copy of x as the TMA operand, rstd and mean
+    applied where the split-K sum is closed) against the default chain: one decode step from the same prompt, logits
+    within the bf16 tolerance; deterministic."""
+    ids = rp.gpt2_prompt_ids(B, T, seed=61 + B, vocab=1000)
+    logits, outs = [], []
+    for mode in ("0", "1"):
+        monkeypatch.setenv("TUTOR_FOLD", mode)
+        eng = pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="bf16")
+        eng.prefill(ids, max_new_tokens=12, eos_token_id=999, pad_token_id=999)
+        eng.step(1)
+        logits.append(eng.last_logits().float().cpu())
+        outs.append([eng.generate(ids, max_new_tokens=12, eos_token_id=999, pad_token_id=999) for _ in range(2)])
+    monkeypatch.delenv("TUTOR_FOLD")
+    err = ((logits[0] - logits[1]).abs().max() / logits[0].abs().max()).item()
+    print(f"folded LayerNorm vs operand-load LayerNorm, B={B}: relative logit difference {err:.3e}")
+    assert err < 2e-2
+    assert torch.equal(outs[1][0], outs[1][1])
+
+
 def test_long_prompt_then_short_prompt_on_one_bf16_engine(pkg, tiny_hf):
     """The captured decode graph bakes in how many prompt rows the attention may stream ahead of its wait.  A long prompt
     followed by a short one on the SAME engine must not replay the long prompt's bound (advisor finding, round 1): the
