@@ -496,7 +496,8 @@ int k_cosine_scan_tc(const float* queries, const float* corpus, const float* cor
   // unselected group's TF32 maximum by the TF32 error bound; when it does not (near-duplicate rows around rank k), a flag
   // lets the error-compensated 3xTF32 pass below run and overwrite the result - otherwise its kernels return at once.
   static const bool filter_off = getenv("TUTOR_SCAN_NO_FILTER") != nullptr;  // cross-check switch for the tests
-  const bool filter = !filter_off && 3 * k <= 32;
+  // (selecting and re-scoring 32 groups instead of k costs ~35 us more; below ~200 k rows the shorter scan does not pay for it)
+  const bool filter = !filter_off && 3 * k <= 32 && N >= 200000;
   if (filter) {
     cosine_scan_tf32_kernel<true><<<nctas, TS_THREADS, TS_SMEM, st>>>(tc, th, tl, corpus_inv_norm, qinv, Q, N, d, nullptr, gmax, nullptr);
     KERNEL_LAUNCHED();

@@ -16,7 +16,7 @@ def corpus(n, d=768, seed=3):
 
 # the last two leave the tensor-core path: more than 32 queries (SIMT scan, register-row kernel) and k > 32 (SIMT scan,
 # block-wide chunk selection)
-@pytest.mark.parametrize("N,Q,k,d", [(50_000, 32, 10, 768), (4097, 3, 5, 768), (7, 2, 10, 128), (20_000, 1, 1, 128),
+@pytest.mark.parametrize("N,Q,k,d", [(50_000, 32, 10, 768), (250_000, 32, 10, 768), (4097, 3, 5, 768), (7, 2, 10, 128), (20_000, 1, 1, 128),
                                      (3000, 40, 5, 768), (5000, 4, 40, 128), (9000, 32, 32, 768)])
 def test_topk_matches_oracle(pkg, N, Q, k, d):
     c = corpus(N, d)
@@ -55,7 +55,7 @@ def test_near_ties_around_rank_k_fall_back_to_the_exact_scan(pkg):
     """The plain-TF32 filter scan cannot rank rows whose cosines differ by less than its error (~2e-3): 200 planted rows
     spaced 1e-4 apart around the top of query 0's ranking, each in a different 32-row group.  The library must notice that
     its candidate set is not provably complete and run the error-compensated scan: index sets identical to the oracle."""
-    N, Q, k, d = 120_000, 4, 10, 768
+    N, Q, k, d = 220_000, 4, 10, 768  # the filter scan is used from 200 k rows on
     g = torch.Generator().manual_seed(11)
     c = corpus(N, d, seed=12)
     q = torch.randn(Q, d, generator=g)
