@@ -311,23 +311,36 @@ __global__ void __launch_bounds__(TK_THREADS) topk_select_groups_kernel(const fl
   const int ngroups = (N + 31) / 32;  // groups past this are padding of the last tile
   for (int g = tid; g < G; g += TK_THREADS) sg[g] = g < ngroups ? gmax[(size_t)q * G + g] : -CUDART_INF_F;
   __syncthreads();
-  // thread t owns the groups t, t + 1024, ...; its warp extracts the k best of the warp's 32 slices
-  auto rescan = [&](float& bv, int& bk) {
-    bv = -CUDART_INF_F; bk = 0x7fffffff;
+  // thread t owns the groups t, t + 1024, ...; its warp extracts the k best of the warp's 32 slices.  A thread keeps its
+  // three best in registers, so that dropping a winner costs a register shift and only every third win of the same thread
+  // a walk over its slice (with one cached value the owner re-walked up to 31 elements in every round it won, and its
+  // warp waited: 0.85 us per round)
+  float cv[3];
+  int ck[3];
+  auto rescan = [&]() {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { cv[i] = -CUDART_INF_F; ck[i] = 0x7fffffff; }
     for (int g = tid; g < G; g += TK_THREADS) {
       const float v = sg[g];
-      if (v > bv) { bv = v; bk = g; }  // ascending g: strict > keeps the lowest group
+      if (v == -CUDART_INF_F) continue;
+      if (v > cv[2]) {  // ascending g: strict > keeps the lower group ahead among equals
+        if (v > cv[1]) {
+          cv[2] = cv[1]; ck[2] = ck[1];
+          if (v > cv[0]) { cv[1] = cv[0]; ck[1] = ck[0]; cv[0] = v; ck[0] = g; }
+          else { cv[1] = v; ck[1] = g; }
+        } else { cv[2] = v; ck[2] = g; }
+      }
     }
   };
-  float bv; int bk;
-  rescan(bv, bk);
+  rescan();
   for (int round = 0; round < k; ++round) {
-    float v = bv; int key = bk;
+    float v = cv[0]; int key = ck[0];
     warp_argmax(v, key);
     if (lane == 0) { lv[warp][round] = v; lk[warp][round] = (v == -CUDART_INF_F) ? 0x7fffffff : key; }
-    if (key != 0x7fffffff && key == bk) {  // the owner drops the winner and refreshes its cached best
+    if (key != 0x7fffffff && key == ck[0]) {  // the owner drops the winner
       sg[key] = -CUDART_INF_F;
-      rescan(bv, bk);
+      cv[0] = cv[1]; ck[0] = ck[1]; cv[1] = cv[2]; ck[1] = ck[2]; cv[2] = -CUDART_INF_F; ck[2] = 0x7fffffff;
+      if (ck[0] == 0x7fffffff) rescan();  // cache empty: whatever is left of the slice
     }
   }
   __syncthreads();
