@@ -42,8 +42,17 @@ template <> struct Vec16<bf16> {
 // from shared memory, so the q/k/v of the current token never make a round trip through HBM.
 // One element of q / k / v of the current token from the c_attn split-K partials (FUSED kernels).  With a folded LayerNorm
 // (gemm_decode_fused.cu) the partial sums are x . W' and the LayerNorm enters here: rstd (sum - mean s[n]) + c[n] + bias[n].
+// FOLD is a template parameter so that the default kernels stay exactly the code they were before the folded path existed
+// (as a run-time branch it cost the split-attention kernel of GPT-2 large 20 %: registers, a spill).
+template <bool FOLD>
 __device__ __forceinline__ float qkv_from_partials(const float* __restrict__ qkv_partial, int ks, const float* __restrict__ qkv_bias,
                                                    const QkvFold& fold, int B, int b, int n, int d) {
+  if (!FOLD) {
+    float acc = qkv_bias[n];
+#pragma unroll 8
+    for (int zz = 0; zz < ks; ++zz) acc += qkv_partial[((size_t)zz * B + b) * (3 * d) + n];
+    return acc;
+  }
   float mean = 0.f, rstd = 1.f, sn = 0.f, add = qkv_bias[n];
   if (fold.s) {
     const float2* st2 = reinterpret_cast<const float2*>(fold.stats) + b;
@@ -71,7 +80,7 @@ __device__ __forceinline__ float qkv_from_partials(const float* __restrict__ qkv
   return fold.s ? fmaf(rstd, acc - mean * sn, add) : acc;
 }
 
-template <typename QT, typename KT, typename OT, bool FAST, bool FUSED>
+template <typename QT, typename KT, typename OT, bool FAST, bool FUSED, bool FOLD = false>
 __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__ q, KT* kc, KT* vc,
                                                           OT* __restrict__ out, int H, int Smax,
                                                           const int* __restrict__ len_dev, int len_host,
@@ -106,7 +115,7 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const QT* __restrict__
     for (int e = threadIdx.x; e < 192; e += 128) {
       const int which = e >> 6, i = e & 63;
       const int n = which * d + h * 64 + i;
-      const float acc = qkv_from_partials(qkv_partial, ks, qkv_bias, fold, B, b, n, d);
+      const float acc = qkv_from_partials<FOLD>(qkv_partial, ks, qkv_bias, fold, B, b, n, d);
       if (which == 0) {
         s_new[0][i] = acc;
       } else {
@@ -273,7 +282,7 @@ __device__ __forceinline__ void dk_wait(uint64_t* bar, uint32_t parity) {
 }
 
 // DK_CHUNK keys per stage, DK_STAGES stages; MATH=false (microbench only) drains the ring without the arithmetic
-template <bool FUSED, int DK_CHUNK, int DK_STAGES, bool MATH>
+template <bool FUSED, int DK_CHUNK, int DK_STAGES, bool MATH, bool FOLD = false>
 __global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf16* __restrict__ q, bf16* kc, bf16* vc,
                                                                     bf16* __restrict__ out, int H, int Smax,
                                                                     const int* __restrict__ len_dev, int len_host,
@@ -349,7 +358,7 @@ __global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf
         accv[r] = 0.f;
         if (e < 192) {
           const int n = (e >> 6) * d + h * 64 + (e & 63);
-          accv[r] = qkv_from_partials(qkv_partial, ks, qkv_bias, fold, B, b, n, d);
+          accv[r] = qkv_from_partials<FOLD>(qkv_partial, ks, qkv_bias, fold, B, b, n, d);
         }
       }
 #pragma unroll
@@ -1093,15 +1102,15 @@ int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias,
   }
 #endif
   if (nsplit == 1) {
-    CUDA_TRY(tutor_launch(attn_decode_tma_kernel<true, 64, 2, true>, dim3(H, B), dim3(DK_THREADS), 0, st, (const bf16*)nullptr,
-                          (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B, fold,
-                          npad, safe_rows));
+    auto kern = fold.s ? attn_decode_tma_kernel<true, 64, 2, true, true> : attn_decode_tma_kernel<true, 64, 2, true, false>;
+    CUDA_TRY(tutor_launch(kern, dim3(H, B), dim3(DK_THREADS), 0, st, (const bf16*)nullptr, (bf16*)k, (bf16*)v, (bf16*)out, H,
+                          Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B, fold, npad, safe_rows));
     KERNEL_LAUNCHED();
     return TUTOR_OK;
   }
-  CUDA_TRY(tutor_launch(attn_decode_kernel<bf16, bf16, bf16, true, true>, dim3(H, B, nsplit), dim3(128), 0, st,
-                        (const bf16*)nullptr, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks,
-                        qkv_bias, B, fold, sc, counters, npad));
+  auto kern = fold.s ? attn_decode_kernel<bf16, bf16, bf16, true, true, true> : attn_decode_kernel<bf16, bf16, bf16, true, true, false>;
+  CUDA_TRY(tutor_launch(kern, dim3(H, B, nsplit), dim3(128), 0, st, (const bf16*)nullptr, (bf16*)k, (bf16*)v, (bf16*)out, H,
+                        Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B, fold, sc, counters, npad));
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }
