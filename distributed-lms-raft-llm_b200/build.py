@@ -15,6 +15,7 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std
          "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 if os.environ.get("TUTOR_EXPERIMENTS"):  # A/B knobs for tools/ (csrc/common.cuh); never set for the shipped library
     FLAGS.append("-DTUTOR_EXPERIMENTS")
+FLAGS += os.environ.get("TUTOR_EXTRA_NVCC_FLAGS", "").split()  # one-off timing experiments (tools/)
 
 
 def sources():

@@ -34,9 +34,9 @@ constexpr int AT_THREADS = 192;               // TMA warp, MMA warp, 4 softmax w
 constexpr int AT_TILE = 128 * 128;             // bytes of a 128-row x 64-column bf16 tile (Q, P)
 constexpr int AT_KV = 64 * 128;                // bytes of a 64-key K or V tile
 constexpr int AT_BN = 64;                      // keys per block
-constexpr int AT_ST = 3;                       // K / V stages
-constexpr int AT_SMEM = 4 * AT_TILE + 2 * AT_ST * AT_KV + 256;  // Q[2], P[2], K[AT_ST], V[AT_ST], barriers
-constexpr uint32_t AT_TMEM_COLS = 256;         // S[2]: columns 0..63 and 64..127, O: 128..191
+constexpr int AT_ST = 4;                       // K / V stages
+constexpr int AT_SMEM = 2 * AT_ST * AT_KV + 256;  // K[AT_ST], V[AT_ST], barriers
+constexpr uint32_t AT_TMEM_COLS = 256;         // S[2]: columns 0..127, O: 128..191, Q[2] (packed bf16): 192..255
 
 // 32 lanes x 8 columns, multiplied in place (the rare rescale of O: narrow on purpose, the score row is live around it)
 __device__ __forceinline__ void tc_scale8(uint32_t taddr, float f) {
@@ -65,36 +65,56 @@ __device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t smem_addr) {
   return d;
 }
 __device__ __forceinline__ float ex2(float x) {
+#ifdef TUTOR_EXPERIMENTS_NOMUFU
+  return fmaf(x, 1e-9f, 1.0f);  // timing experiment only: no MUFU
+#else
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+#endif
 }
 __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
   __nv_bfloat162 p = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&p);
 }
 
+// tcgen05.mma with the A operand in tensor memory (bf16 pairs packed into 32-bit columns, lane = row)
+__device__ __forceinline__ void tc_mma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 lanes x 32 columns of 32-bit words into tensor memory
+__device__ __forceinline__ void tc_st32(uint32_t taddr, const uint32_t* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
+      "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]),
+      "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]),
+      "r"(v[31])
+      : "memory");
+}
+
 template <bool CAUSAL, bool PADDED>
 __global__ void __launch_bounds__(AT_THREADS, 2)
-    attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+    attn_prefill_tc_kernel(const bf16* __restrict__ q, const __grid_constant__ CUtensorMap tmK,
                            const __grid_constant__ CUtensorMap tmV, bf16* __restrict__ out, int B, int H, int T, int Smax,
                            const int* __restrict__ npad) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  uint8_t* sQ = smem;                                    // [2]: the next item's queries arrive during this item
-  uint8_t* sP = smem + 2 * AT_TILE;                      // [2]
-  uint8_t* sK = smem + 4 * AT_TILE;                      // [AT_ST]
-  uint8_t* sV = smem + 4 * AT_TILE + AT_ST * AT_KV;      // [AT_ST]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 4 * AT_TILE + 2 * AT_ST * AT_KV);
-  uint64_t* k_full = bars;                 // [AT_ST]
-  uint64_t* v_full = bars + AT_ST;         // [AT_ST]
-  uint64_t* k_empty = bars + 2 * AT_ST;    // [AT_ST] freed by S = Q K^T
-  uint64_t* v_empty = bars + 3 * AT_ST;    // [AT_ST] freed by O += P V
-  uint64_t* s_full = bars + 4 * AT_ST;     // [2]
-  uint64_t* q_full = s_full + 2;           // [2]
-  uint64_t* q_empty = s_full + 4;          // [2]
-  uint64_t* pv_done = s_full + 6;          // [2]: block g completes pv_done[g & 1]
-  uint64_t* p_ready = s_full + 8;          // [2], 128 arrivals each
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_full + 10);
+  uint8_t* sK = smem;                      // [AT_ST]
+  uint8_t* sV = smem + AT_ST * AT_KV;      // [AT_ST]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * AT_ST * AT_KV);
+  uint64_t* kv_full = bars;                // [AT_ST] K and V tile of a block have landed
+  uint64_t* kv_empty = bars + AT_ST;       // [AT_ST] ... and O += P V of that block has completed (it read V last)
+  uint64_t* s_full = bars + 2 * AT_ST;     // [2]
+  uint64_t* p_ready = s_full + 2;          // [2], 128 arrivals each
+  uint64_t* q_full = s_full + 4;           // [2], 128 arrivals each
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_full + 6);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nqt = (T + 127) / 128, nitems = nqt * H * B;
@@ -110,13 +130,11 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
   auto blocks_of = [&](int qt) { return CAUSAL ? min(2 * (qt + 1), nkb) : nkb; };
 
   if (threadIdx.x == 0) {
-    if (smem_u32(smem) & 1023) __trap();  // the swizzled tiles need 1 KB alignment and there is no room for slack
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmQ) : "memory");
+    if (smem_u32(smem) & 1023) __trap();  // the swizzled tiles need 1 KB alignment
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmK) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmV) : "memory");
-    for (int i = 0; i < 4 * AT_ST + 8; ++i) mbar_init(&bars[i], 1);
-    mbar_init(&p_ready[0], 128);
-    mbar_init(&p_ready[1], 128);
+    for (int i = 0; i < 2 * AT_ST + 2; ++i) mbar_init(&bars[i], 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&p_ready[i], 128); mbar_init(&q_full[i], 128); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -129,47 +147,61 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tS = tmem_base, tO = tmem_base + 128;  // S buffer i at tS + 64 i
+  // S buffer i at tS + 64 i (P of the block overwrites its first 32 columns), Q buffer i at tQ + 32 i
+  const uint32_t tS = tmem_base, tO = tmem_base + 128, tQ = tmem_base + 192;
 
   if (warp == 0) {
-    // ===== TMA producer =====
+    // ===== TMA producer: K and V tiles =====
     if (lane == 0) {
-      int g = 0, it = 0;  // K/V blocks and items this CTA has started
-      for (int w = blockIdx.x; w < nitems; w += gridDim.x, ++it) {
+      int g = 0;
+      for (int w = blockIdx.x; w < nitems; w += gridDim.x) {
         int qt, h, b;
         item(w, qt, h, b);
-        mbar_wait(&q_empty[it & 1], ((it >> 1) & 1) ^ 1, 0);  // the last S = Q K^T of two items ago has read this buffer
-        mbar_expect_tx(&q_full[it & 1], AT_TILE);
-        tma_load_2d(sQ + (it & 1) * AT_TILE, &tmQ, &q_full[it & 1], h * 64, b * T + qt * 128);
         const int kv_row0 = (b * H + h) * Smax, nblk = blocks_of(qt);
         for (int j = 0; j < nblk; ++j, ++g) {
           const int st = g % AT_ST;
           const uint32_t use = (uint32_t)(g / AT_ST) & 1;
-          mbar_wait(&k_empty[st], use ^ 1, 0);
-          mbar_expect_tx(&k_full[st], AT_KV);
-          tma_load_2d(sK + st * AT_KV, &tmK, &k_full[st], 0, kv_row0 + j * AT_BN);
-          mbar_wait(&v_empty[st], use ^ 1, 0);
-          mbar_expect_tx(&v_full[st], AT_KV);
-          tma_load_2d(sV + st * AT_KV, &tmV, &v_full[st], 0, kv_row0 + j * AT_BN);
+          mbar_wait(&kv_empty[st], use ^ 1, 0);
+          mbar_expect_tx(&kv_full[st], 2 * AT_KV);
+          tma_load_2d(sK + st * AT_KV, &tmK, &kv_full[st], 0, kv_row0 + j * AT_BN);
+          tma_load_2d(sV + st * AT_KV, &tmV, &kv_full[st], 0, kv_row0 + j * AT_BN);
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread) =====
+    // ===== MMA issuer (one thread).  Both A operands live in tensor memory: Q (stored there once per item by the softmax
+    // threads) and P (stored over the S buffer they have just read).  Only K and V are read from shared memory - with A in
+    // shared memory too the kernel was bound by shared-memory bandwidth (Q and P re-read for every 64 keys: 32 of the 48 KB
+    // a block moved through the MMA's operand path, plus 16 KB of P stores). =====
     if (lane == 0) {
+      // The issuing thread is the pacemaker of the whole CTA: with three barrier tests (~130 cycles each even when the
+      // barrier is long complete), four commits (~65 each) and descriptors rebuilt for every MMA it spent ~1600 cycles per
+      // 64-key block - as long as the softmax warps need for the block.  Hence one barrier per K/V stage, two commits per
+      // block, and descriptors made once per stage.
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, 64);
       constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64) | (1u << 16);  // B (= V) is MN-major
+      uint64_t kdesc[AT_ST], vdesc[AT_ST];
+#pragma unroll
+      for (int st = 0; st < AT_ST; ++st) {
+        kdesc[st] = umma_desc_sw128(smem_u32(sK + st * AT_KV));
+        vdesc[st] = umma_desc_sw128_mn(smem_u32(sV + st * AT_KV));
+      }
+      auto stage_desc = [&](const uint64_t* d, int st) {  // register array indexed by a run-time stage without local memory
+        uint64_t r = d[0];
+#pragma unroll
+        for (int i = 1; i < AT_ST; ++i) r = st == i ? d[i] : r;
+        return r;
+      };
       auto issue_pv = [&](int g, bool first) {  // O (+)= P V of block g (first: the item's first block starts O afresh)
         const int st = g % AT_ST;
-        mbar_wait(&p_ready[g & 1], (g >> 1) & 1, 1);  // P of block g is in shared memory (and S buffer g & 1 has been read)
-        mbar_wait(&v_full[st], (g / AT_ST) & 1, 1);
+        mbar_wait(&p_ready[g & 1], (g >> 1) & 1, 1);  // P of block g is in tensor memory
         tc_fence_after();
-        const uint32_t sp = smem_u32(sP + (g & 1) * AT_TILE), sv = smem_u32(sV + st * AT_KV);
+        const uint32_t tp = tS + (g & 1) * 64;
+        const uint64_t vd = stage_desc(vdesc, st);
 #pragma unroll
-        for (int k = 0; k < 4; ++k)  // 16 keys per MMA: 32 bytes along the rows of P; two 8-key groups (2 x 1024 bytes) of V
-          tc_mma_bf16(tO, umma_desc_sw128(sp + k * 32), umma_desc_sw128_mn(sv + k * 2048), idesc_o, !first || k != 0);
-        tc_commit(&pv_done[g & 1]);
-        tc_commit(&v_empty[st]);
+        for (int k = 0; k < 4; ++k)  // 16 keys per MMA: 8 columns of packed P; two 8-key groups (2 x 1024 bytes) of V
+          tc_mma_bf16_ts(tO, tp + k * 8, vd + (uint64_t)(k * (2048 >> 4)), idesc_o, !first || k != 0);
+        tc_commit(&kv_empty[st]);  // also tells the softmax warps that O is complete up to this block
       };
       int g = 0, it = 0;
       bool prev_first = false;
@@ -179,22 +211,18 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
         const int nblk = blocks_of(qt);
         mbar_wait(&q_full[it & 1], (it >> 1) & 1, 1);
         for (int j = 0; j < nblk; ++j, ++g) {
-          // S of block g goes into TMEM buffer g & 1 as soon as the softmax of block g - 2 has read it: one block ahead
-          // of the softmax warps, which therefore find their scores waiting
+          // S of block g goes into TMEM buffer g & 1 once the P V of block g - 2 (which read its P from there) has been
+          // issued: the tensor pipe runs in order.  One block ahead of the softmax warps.
           const int st = g % AT_ST;
-          mbar_wait(&k_full[st], (g / AT_ST) & 1, 1);
-          if (g > 1) mbar_wait(&p_ready[g & 1], ((g - 2) >> 1) & 1, 1);
+          mbar_wait(&kv_full[st], (g / AT_ST) & 1, 1);
           tc_fence_after();
-          const uint32_t sq = smem_u32(sQ + (it & 1) * AT_TILE), sk = smem_u32(sK + st * AT_KV);
+          const uint32_t tq = tQ + (it & 1) * 32;
+          const uint64_t kd = stage_desc(kdesc, st);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            tc_mma_bf16(tS + (g & 1) * 64, umma_desc_sw128(sq + k * 32), umma_desc_sw128(sk + k * 32), idesc_s, k != 0);
+            tc_mma_bf16_ts(tS + (g & 1) * 64, tq + k * 8, kd + (uint64_t)(k * (32 >> 4)), idesc_s, k != 0);
           tc_commit(&s_full[g & 1]);
-          tc_commit(&k_empty[st]);
-          if (j == nblk - 1) tc_commit(&q_empty[it & 1]);
-          // P V of the previous block, behind S in the tensor pipe.  When that block opened a new item it overwrites O:
-          // the softmax threads read the old O (their epilogue) before they signalled p_ready for it.
-          if (g > 0) issue_pv(g - 1, prev_first);
+          if (g > 0) issue_pv(g - 1, prev_first);  // behind S in the tensor pipe: the softmax of this block overlaps it
           prev_first = j == 0;
         }
       }
@@ -206,36 +234,47 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
     const int r = quad * 32 + lane;
     const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
     constexpr float C = 0.125f * 1.4426950408889634f;  // 1/sqrt(64) and log2(e) in one factor
-    int g = 0;
-#ifdef TUTOR_EXPERIMENTS
-#define AT_STAMP(i) if (tracing && g >= 2 && g < 6) stamp[g - 2][i] = clock64()
-    const bool tracing = blockIdx.x == 0 && threadIdx.x == 64;
-    long long stamp[4][8];
-#else
-#define AT_STAMP(i)
-#endif
-    for (int w = blockIdx.x; w < nitems; w += gridDim.x) {
+    // this thread's query row of item w -> Q buffer `buf` (64 bf16 = 32 packed columns); rows past the tensor are clamped
+    auto store_q = [&](int w, int buf) {
       int qt, h, b;
       item(w, qt, h, b);
+      const size_t row = min((size_t)b * T + qt * 128 + r, (size_t)B * T - 1);
+      const uint4* src = reinterpret_cast<const uint4*>(q + row * (H * 64) + h * 64);
+      uint32_t v[32];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const uint4 x = src[i];
+        v[4 * i] = x.x; v[4 * i + 1] = x.y; v[4 * i + 2] = x.z; v[4 * i + 3] = x.w;
+      }
+      tc_st32(tQ + buf * 32 + lane_off, v);
+      tc_wait_st();
+      tc_fence_before();
+      mbar_arrive(&q_full[buf]);
+    };
+    int g = 0, it = 0;
+    store_q(blockIdx.x, 0);
+    for (int w = blockIdx.x; w < nitems; w += gridDim.x, ++it) {
+      int qt, h, b;
+      item(w, qt, h, b);
+      // the next item's queries, an item ahead: that buffer was last read by the S MMAs of the previous item, all of
+      // which this thread has seen completed (it consumed their results)
+      if (w + (int)gridDim.x < nitems) store_q(w + (int)gridDim.x, (it + 1) & 1);
       const int nblk = blocks_of(qt), q0 = qt * 128, qrow = q0 + r;
       const int kp = PADDED ? npad[b] : 0;  // left padding: pad keys are invisible to real queries
       float m_run = -CUDART_INF_F, l_run = 0.f;
-#ifdef TUTOR_EXPERIMENTS
-      const long long t_item = clock64();
-      long long t_first = 0;
-#endif
       for (int j = 0; j < nblk; ++j, ++g) {
         const int key0 = j * AT_BN;
         const bool edge = (key0 + AT_BN - 1 >= T) || (CAUSAL && key0 + AT_BN - 1 > q0) || (PADDED && key0 < kp);
-        AT_STAMP(0);
+        const uint32_t tSb = tS + (g & 1) * 64 + lane_off;
         mbar_wait(&s_full[g & 1], (g >> 1) & 1, 2);
         tc_fence_after();
-        AT_STAMP(1);
-#ifdef TUTOR_EXPERIMENTS
-        if (j == 0) t_first = clock64();
-#endif
         float s[64];
-        tc_ld32x2(tS + (g & 1) * 64 + lane_off, tS + (g & 1) * 64 + lane_off + 32, s, s + 32);
+#ifdef TUTOR_EXPERIMENTS_NOLDTM
+#pragma unroll
+        for (int i = 0; i < 64; ++i) s[i] = (float)(i + r) * 0.01f;  // timing experiment only: the scores are not read
+#else
+        tc_ld32x2(tSb, tSb + 32, s, s + 32);
+#endif
         if (edge) {
 #pragma unroll
           for (int i = 0; i < 64; ++i) {
@@ -243,7 +282,6 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
             if (key >= T || (CAUSAL && key > qrow) || (PADDED && key < kp && qrow >= kp)) s[i] = -CUDART_INF_F;
           }
         }
-        AT_STAMP(2);
         float mx0 = fmaxf(s[0], s[1]), mx1 = fmaxf(s[2], s[3]);
 #pragma unroll
         for (int i = 4; i < 64; i += 2) { mx0 = fmaxf(mx0, s[i]); mx1 = fmaxf(mx1, s[i + 1]); }
@@ -257,56 +295,30 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
           l_run *= alpha;
         }
         const float mref = (m_run == -CUDART_INF_F) ? 0.f : m_run;  // a fully masked row stays at zero weight
-        // ---- P = exp2(S C - m) and the row sum; independent of the previous block's P V, so it runs before the wait
+        // ---- P = exp2(S C - m) as packed bf16 pairs, and the row sum
         float l0 = 0.f, l1 = 0.f;
+        uint32_t pk[32];
 #pragma unroll
-        for (int i = 0; i < 64; i += 2) {
-          s[i] = ex2(fmaf(s[i], C, -mref));
-          s[i + 1] = ex2(fmaf(s[i + 1], C, -mref));
-          l0 += s[i];
-          l1 += s[i + 1];
+        for (int i = 0; i < 32; ++i) {
+          const float p0 = ex2(fmaf(s[2 * i], C, -mref)), p1 = ex2(fmaf(s[2 * i + 1], C, -mref));
+          l0 += p0;
+          l1 += p1;
+          pk[i] = pack2(p0, p1);
         }
         l_run += l0 + l1;
-        AT_STAMP(3);
-        // P buffer g & 1 was read by the P V of block g - 2 (one barrier per buffer: never more than one phase behind)
-        if (g > 1) mbar_wait(&pv_done[g & 1], ((g - 2) >> 1) & 1, 3);
         if (j > 0 && __any_sync(0xffffffffu, move)) {
-          mbar_wait(&pv_done[(g - 1) & 1], ((g - 1) >> 1) & 1, 3);  // O is rescaled between two P V
+          mbar_wait(&kv_empty[(g - 1) % AT_ST], ((g - 1) / AT_ST) & 1, 3);  // O is rescaled between two P V
           tc_fence_after();
-          {
 #pragma unroll 1
-            for (int c = 0; c < 8; ++c) tc_scale8(tO + lane_off + c * 8, alpha);
-            tc_wait_st();
-          }
+          for (int c = 0; c < 8; ++c) tc_scale8(tO + lane_off + c * 8, alpha);
         }
-        AT_STAMP(4);
-        uint8_t* prow = sP + (g & 1) * AT_TILE + r * 128;  // P buffer g & 1: block g - 2's P V finished a block ago
-#pragma unroll
-        for (int ch = 0; ch < 8; ++ch) {  // 8 keys = one 16-byte chunk of the swizzled A tile
-          uint4 v;
-          v.x = pack2(s[ch * 8 + 0], s[ch * 8 + 1]); v.y = pack2(s[ch * 8 + 2], s[ch * 8 + 3]);
-          v.z = pack2(s[ch * 8 + 4], s[ch * 8 + 5]); v.w = pack2(s[ch * 8 + 6], s[ch * 8 + 7]);
-          *reinterpret_cast<uint4*>(prow + ((ch ^ (r & 7)) << 4)) = v;
-        }
-        AT_STAMP(5);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> the MMA's async proxy
+        tc_st32(tSb, pk);  // over the scores this thread has just read: the A operand of this block's P V
+        tc_wait_st();
         tc_fence_before();
-        AT_STAMP(6);
         mbar_arrive(&p_ready[g & 1]);
-        AT_STAMP(7);
       }
-#ifdef TUTOR_EXPERIMENTS
-      if (tracing && w == (int)blockIdx.x)
-        for (int i = 0; i < 4; ++i)
-          printf("block %d: wait S %lld | TMEM load %lld | max + exp2 %lld | wait PV %lld | pack + store %lld | fence %lld | arrive %lld | to next %lld\n",
-                 i + 2, stamp[i][1] - stamp[i][0], stamp[i][2] - stamp[i][1], stamp[i][3] - stamp[i][2], stamp[i][4] - stamp[i][3],
-                 stamp[i][5] - stamp[i][4], stamp[i][6] - stamp[i][5], stamp[i][7] - stamp[i][6], i < 3 ? stamp[i + 1][0] - stamp[i][7] : 0LL);
-#endif
-#ifdef TUTOR_EXPERIMENTS
-      const long long t_epi = clock64();
-#endif
       // ---- epilogue: O / l -> bf16 [B*T, d]
-      mbar_wait(&pv_done[(g - 1) & 1], ((g - 1) >> 1) & 1, 4);
+      mbar_wait(&kv_empty[(g - 1) % AT_ST], ((g - 1) / AT_ST) & 1, 4);  // the item's last P V has completed
       tc_fence_after();
       const float inv = 1.0f / l_run;
       bf16* dst = out + ((size_t)b * T + qrow) * (H * 64) + h * 64;
@@ -316,20 +328,15 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
         tc_ld32(tO + lane_off + c * 32, o);
         if (qrow < T) {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
+          for (int qq = 0; qq < 4; ++qq) {
             uint4 v;
-            v.x = pack2(o[q * 8 + 0] * inv, o[q * 8 + 1] * inv); v.y = pack2(o[q * 8 + 2] * inv, o[q * 8 + 3] * inv);
-            v.z = pack2(o[q * 8 + 4] * inv, o[q * 8 + 5] * inv); v.w = pack2(o[q * 8 + 6] * inv, o[q * 8 + 7] * inv);
-            *reinterpret_cast<uint4*>(dst + c * 32 + q * 8) = v;
+            v.x = pack2(o[qq * 8 + 0] * inv, o[qq * 8 + 1] * inv); v.y = pack2(o[qq * 8 + 2] * inv, o[qq * 8 + 3] * inv);
+            v.z = pack2(o[qq * 8 + 4] * inv, o[qq * 8 + 5] * inv); v.w = pack2(o[qq * 8 + 6] * inv, o[qq * 8 + 7] * inv);
+            *reinterpret_cast<uint4*>(dst + c * 32 + qq * 8) = v;
           }
         }
       }
       tc_fence_before();
-#ifdef TUTOR_EXPERIMENTS
-      if (tracing)
-        printf("item %d (%d blocks): first S after %lld, blocks %lld (%lld each), epilogue %lld\n", w, nblk, t_first - t_item,
-               t_epi - t_first, (t_epi - t_first) / nblk, clock64() - t_epi);
-#endif
     }
   }
   __syncthreads();
@@ -344,8 +351,7 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
 // q [B*T, H*64] bf16, k / v [B][H][Smax][64] bf16 (cache layout), out [B*T, H*64] bf16
 int k_attn_prefill_tc(const bf16* q, const bf16* k, const bf16* v, bf16* out, int B, int H, int T, int Smax, int causal,
                       const int* npad, cudaStream_t st) {
-  CUtensorMap tq, tk, tv;
-  TRY(k_make_map_bf16(&tq, q, B * T, H * 64, 128));
+  CUtensorMap tk, tv;
   TRY(k_make_map_bf16(&tk, k, B * H * Smax, 64, AT_BN));
   TRY(k_make_map_bf16(&tv, v, B * H * Smax, 64, AT_BN));
   int dev = 0, sms = 0;
@@ -358,7 +364,7 @@ int k_attn_prefill_tc(const bf16* q, const bf16* k, const bf16* v, bf16* out, in
     auto kern = attn_prefill_tc_kernel<C, P>;                                                                \
     TRY(tutor_set_max_smem(reinterpret_cast<const void*>(kern), AT_SMEM));                                   \
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
-    kern<<<grid, AT_THREADS, AT_SMEM, st>>>(tq, tk, tv, out, B, H, T, Smax, npad);                              \
+    kern<<<grid, AT_THREADS, AT_SMEM, st>>>(q, tk, tv, out, B, H, T, Smax, npad);                              \
   } while (0)
   if (causal && npad) AT_LAUNCH(true, true);
   else if (causal) AT_LAUNCH(true, false);
