@@ -3,25 +3,29 @@
 //   bidirectional: BERT, HF/models/bert/modeling_bert.py:192-205 (through SDPA)
 //
 // A work item is (128 queries, head, sequence), processed flash-style over 64-key blocks:
-//   S = Q K^T        tcgen05.mma 128x64x64, Q and K tiles K-major from TMA (SWIZZLE_128B), S in TMEM (two 64-column
-//                    buffers: the MMA of block g + 1 runs while the softmax warps work on block g)
-//   P = softmax tile four warps, one query row per thread, the 64 scores of the row in registers; P written as bf16
-//                    into a swizzled shared-memory tile (two buffers) that is the A operand of
+//   S = Q K^T        tcgen05.mma 128x64x64 with Q as a tensor-memory A operand (the softmax threads store their query row
+//                    there once per item, bf16 pairs packed into 32 columns) and the K tile K-major from TMA (SWIZZLE_128B);
+//                    S in TMEM, two 64-column buffers: the MMA of block g + 1 runs while the softmax warps work on block g
+//   P = softmax tile four warps, one query row per thread, the 64 scores of the row in registers; P is stored as packed
+//                    bf16 over the first 32 columns of the score buffer it came from and is the A operand of
 //   O += P V         tcgen05.mma 128x64x64, V tile straight from the cache layout [key][dim] as an MN-major B operand,
 //                    O accumulated in TMEM (64 columns).
-// The running maximum is only moved when a block's maximum exceeds it by more than 8 (in log2 units): P then stays
-// below 2^8, and O / l is exact for any reference maximum.  Moving it means rescaling O in TMEM (load, scale, store),
-// which happens for the first few blocks of a row only.
-// Persistent: two CTAs per SM walk the items, longest first; barriers, TMEM, the K/V ring (three stages) and a second Q
-// buffer carry over from item to item, so an item's first tiles arrive while the previous one finishes.
-// Warp roles: 0 = TMA producer, 1 = MMA issuer + TMEM allocation, 2..5 = softmax / epilogue.
+// Only K and V tiles live in shared memory (four stages of 16 KB).  The running maximum is only moved when a block's
+// maximum exceeds it by more than 8 (in log2 units): P then stays below 2^8, and O / l is exact for any reference maximum.
+// Moving it means rescaling O in TMEM (load, scale, store), which happens for the first few blocks of a row only.
+// Persistent: two CTAs per SM (256 TMEM columns each) walk the items, longest first; barriers, TMEM and the K/V ring carry
+// over from item to item, and the next item's queries are stored an item ahead.
+// Warp roles: 0 = TMA producer, 1 = issues S = Q K^T, 6 = issues O += P V, 2..5 = softmax / epilogue.
 //
-// Measured (BERT 32 x 512 x 12 heads, 25.8 GFLOP; mma.sync kernel 97.7 us): 128-key blocks, one CTA per item, two CTAs per
-// SM 71.7 us; persistent 66.0 us; two threads per row (eight softmax warps) 92.8 us; 64-key blocks, three CTAs per SM
-// 68.9 us; this version 70 us, and 97 / 113 us against 135 / 180 us on the causal GPT-2 shapes (64 x 512 x 12, 16 x 1024 x 20).
-// Per block a softmax warp spends ~110 cycles finding S ready, ~130 loading it from TMEM, ~700-900 on maximum + 64 exp2 per
-// thread, ~250 on a barrier test, ~130 packing and storing P (profiles/r2c_attn_prefill_tc.txt); the MUFU pipe is 40 % busy,
-// the tensor pipe 19 %.  Two co-resident CTAs slow each other by ~1.5x, so the SM, not a single chain, is the limit.
+// Measured (BERT 32 x 512 x 12 heads, 25.8 GFLOP; mma.sync kernel 97.7 us): 128-key blocks with Q, K, V, P in shared memory,
+// one CTA per item 71.7 us; persistent 66.0 us; two threads per row (eight softmax warps) 92.8 us; 64-key blocks, three CTAs
+// per SM 68.9 us; S / P / Q double-buffered 64.3 us; two softmax warpgroups on alternating blocks with separate O
+// accumulators 77.9 us; Q and P in TMEM 64.3 us; + one barrier per K/V stage, two commits per block, descriptors built once
+// per stage 59.4 us; + separate issuing threads for S and P V 58.6 us (93 / 104 us on the causal GPT-2 shapes 64 x 512 x 12
+// and 16 x 1024 x 20, against 135 / 180 us).  Timing experiments on the last version: exp2 replaced by an FMA 56.7 us, score
+// loads from TMEM removed as well 60.5 us, six K/V stages 60.9 us - neither the softmax arithmetic nor TMEM reads nor the
+// tile supply bound it; what remains is the per-block hand-off chain (commit -> barrier -> TMEM load ... TMEM store ->
+// barrier -> MMA) of two co-resident CTAs and the 5-or-6 items per CTA quantisation (profiles/r2c_attn_prefill_tc.txt).
 #include <math_constants.h>
 
 #include "kernels.h"
@@ -30,7 +34,7 @@
 namespace {
 using namespace tcptx;
 
-constexpr int AT_THREADS = 192;               // TMA warp, MMA warp, 4 softmax warps
+constexpr int AT_THREADS = 224;               // TMA warp, S-MMA warp, 4 softmax warps, PV-MMA warp
 constexpr int AT_TILE = 128 * 128;             // bytes of a 128-row x 64-column bf16 tile (Q, P)
 constexpr int AT_KV = 64 * 128;                // bytes of a 64-key K or V tile
 constexpr int AT_BN = 64;                      // keys per block
@@ -112,8 +116,8 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
   uint64_t* kv_full = bars;                // [AT_ST] K and V tile of a block have landed
   uint64_t* kv_empty = bars + AT_ST;       // [AT_ST] ... and O += P V of that block has completed (it read V last)
   uint64_t* s_full = bars + 2 * AT_ST;     // [2]
-  uint64_t* p_ready = s_full + 2;          // [2], 128 arrivals each
-  uint64_t* q_full = s_full + 4;           // [2], 128 arrivals each
+  uint64_t* p_ready = s_full + 2;          // [2], one arrival per softmax warp
+  uint64_t* q_full = s_full + 4;           // [2], one arrival per softmax warp
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_full + 6);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -134,7 +138,7 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmK) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmV) : "memory");
     for (int i = 0; i < 2 * AT_ST + 2; ++i) mbar_init(&bars[i], 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(&p_ready[i], 128); mbar_init(&q_full[i], 128); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&p_ready[i], 4); mbar_init(&q_full[i], 4); }  // one arrival per softmax warp
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -179,42 +183,28 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
       // 64-key block - as long as the softmax warps need for the block.  Hence one barrier per K/V stage, two commits per
       // block, and descriptors made once per stage.
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, 64);
-      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64) | (1u << 16);  // B (= V) is MN-major
-      uint64_t kdesc[AT_ST], vdesc[AT_ST];
+      uint64_t kdesc[AT_ST];
 #pragma unroll
-      for (int st = 0; st < AT_ST; ++st) {
-        kdesc[st] = umma_desc_sw128(smem_u32(sK + st * AT_KV));
-        vdesc[st] = umma_desc_sw128_mn(smem_u32(sV + st * AT_KV));
-      }
+      for (int st = 0; st < AT_ST; ++st) kdesc[st] = umma_desc_sw128(smem_u32(sK + st * AT_KV));
       auto stage_desc = [&](const uint64_t* d, int st) {  // register array indexed by a run-time stage without local memory
         uint64_t r = d[0];
 #pragma unroll
         for (int i = 1; i < AT_ST; ++i) r = st == i ? d[i] : r;
         return r;
       };
-      auto issue_pv = [&](int g, bool first) {  // O (+)= P V of block g (first: the item's first block starts O afresh)
-        const int st = g % AT_ST;
-        mbar_wait(&p_ready[g & 1], (g >> 1) & 1, 1);  // P of block g is in tensor memory
-        tc_fence_after();
-        const uint32_t tp = tS + (g & 1) * 64;
-        const uint64_t vd = stage_desc(vdesc, st);
-#pragma unroll
-        for (int k = 0; k < 4; ++k)  // 16 keys per MMA: 8 columns of packed P; two 8-key groups (2 x 1024 bytes) of V
-          tc_mma_bf16_ts(tO, tp + k * 8, vd + (uint64_t)(k * (2048 >> 4)), idesc_o, !first || k != 0);
-        tc_commit(&kv_empty[st]);  // also tells the softmax warps that O is complete up to this block
-      };
+      // This thread issues S = Q K^T only; O += P V is issued by warp 6, so that neither waits behind the other's barriers.
+      // Without a common issue order the reuse of a score buffer needs its own edge: S of block g overwrites the buffer whose
+      // P the P V of block g - 2 reads, so it waits for that P V to complete (kv_empty of its stage).
       int g = 0, it = 0;
-      bool prev_first = false;
       for (int w = blockIdx.x; w < nitems; w += gridDim.x, ++it) {
         int qt, h, b;
         item(w, qt, h, b);
         const int nblk = blocks_of(qt);
         mbar_wait(&q_full[it & 1], (it >> 1) & 1, 1);
         for (int j = 0; j < nblk; ++j, ++g) {
-          // S of block g goes into TMEM buffer g & 1 once the P V of block g - 2 (which read its P from there) has been
-          // issued: the tensor pipe runs in order.  One block ahead of the softmax warps.
           const int st = g % AT_ST;
           mbar_wait(&kv_full[st], (g / AT_ST) & 1, 1);
+          if (g >= 2) mbar_wait(&kv_empty[(g - 2) % AT_ST], ((g - 2) / AT_ST) & 1, 1);
           tc_fence_after();
           const uint32_t tq = tQ + (it & 1) * 32;
           const uint64_t kd = stage_desc(kdesc, st);
@@ -222,11 +212,35 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
           for (int k = 0; k < 4; ++k)
             tc_mma_bf16_ts(tS + (g & 1) * 64, tq + k * 8, kd + (uint64_t)(k * (32 >> 4)), idesc_s, k != 0);
           tc_commit(&s_full[g & 1]);
-          if (g > 0) issue_pv(g - 1, prev_first);  // behind S in the tensor pipe: the softmax of this block overlaps it
-          prev_first = j == 0;
         }
       }
-      if (g > 0) issue_pv(g - 1, prev_first);
+    }
+  } else if (warp == 6) {
+    // ===== second MMA issuer: O += P V =====
+    if (lane == 0) {
+      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64) | (1u << 16);  // B (= V) is MN-major
+      uint64_t vdesc[AT_ST];
+#pragma unroll
+      for (int st = 0; st < AT_ST; ++st) vdesc[st] = umma_desc_sw128_mn(smem_u32(sV + st * AT_KV));
+      int g = 0;
+      for (int w = blockIdx.x; w < nitems; w += gridDim.x) {
+        int qt, h, b;
+        item(w, qt, h, b);
+        const int nblk = blocks_of(qt);
+        for (int j = 0; j < nblk; ++j, ++g) {
+          const int st = g % AT_ST;
+          mbar_wait(&p_ready[g & 1], (g >> 1) & 1, 1);  // P of block g is in tensor memory (its K/V stage landed long ago)
+          tc_fence_after();
+          const uint32_t tp = tS + (g & 1) * 64;
+          uint64_t vd = vdesc[0];
+#pragma unroll
+          for (int i = 1; i < AT_ST; ++i) vd = st == i ? vdesc[i] : vd;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)  // 16 keys per MMA: 8 columns of packed P; two 8-key groups (2 x 1024 bytes) of V
+            tc_mma_bf16_ts(tO, tp + k * 8, vd + (uint64_t)(k * (2048 >> 4)), idesc_o, j != 0 || k != 0);
+          tc_commit(&kv_empty[st]);  // frees the stage, and tells the softmax warps that O is complete up to this block
+        }
+      }
     }
   } else {
     // ===== softmax + epilogue: thread = query row; a warp reaches the 32 TMEM lanes of its quadrant (warp index mod 4) =====
@@ -249,7 +263,8 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
       tc_st32(tQ + buf * 32 + lane_off, v);
       tc_wait_st();
       tc_fence_before();
-      mbar_arrive(&q_full[buf]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&q_full[buf]);
     };
     int g = 0, it = 0;
     store_q(blockIdx.x, 0);
@@ -315,7 +330,8 @@ __global__ void __launch_bounds__(AT_THREADS, 2)
         tc_st32(tSb, pk);  // over the scores this thread has just read: the A operand of this block's P V
         tc_wait_st();
         tc_fence_before();
-        mbar_arrive(&p_ready[g & 1]);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_ready[g & 1]);  // one arrival per warp (128 arrivals on one barrier serialise)
       }
       // ---- epilogue: O / l -> bf16 [B*T, d]
       mbar_wait(&kv_empty[(g - 1) % AT_ST], ((g - 1) / AT_ST) & 1, 4);  // the item's last P V has completed
