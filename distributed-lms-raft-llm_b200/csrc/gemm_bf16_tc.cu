@@ -212,13 +212,13 @@ __global__ void __launch_bounds__(EPI == EPI_ROWMAJOR ? NTHREADS_WIDE : NTHREADS
         tc_fence_after();
         if (kb == 0) TRACE(3);
         const uint32_t sa = smem_u32(tiles + s * L::STAGE_BYTES);
-        const uint32_t sb = sa + L::A_BYTES;
+        // one descriptor pair per stage; advancing 16 bf16 = 32 bytes along K inside the 128-byte swizzle atom moves the
+        // 16-byte-granular address field by 2
+        const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + L::A_BYTES);
 #pragma unroll
-        for (int k = 0; k < BK / UMMA_K; ++k) {
-          // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle atom
-          tc_mma_bf16(tmem_base, umma_desc_sw128(sa + k * UMMA_K * 2), umma_desc_sw128(sb + k * UMMA_K * 2), idesc,
+        for (int k = 0; k < BK / UMMA_K; ++k)
+          tc_mma_bf16(tmem_base, da + (uint64_t)(k * (UMMA_K * 2 >> 4)), db + (uint64_t)(k * (UMMA_K * 2 >> 4)), idesc,
                       (kb | k) != 0);
-        }
         tc_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
       }
       tc_commit(tmem_full_bar);    // accumulator complete
@@ -408,10 +408,10 @@ __global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_kernel(
           mbar_wait(&full_bar[s], (it / L::STAGES) & 1, 1);
           tc_fence_after();
           const uint32_t sa = smem_u32(tiles + s * L::STAGE_BYTES);
-          const uint32_t sb = sa + L::A_BYTES;
+          const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + L::A_BYTES);  // k-step: address field + 2
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k)
-            tc_mma_bf16(d_tmem, umma_desc_sw128(sa + k * UMMA_K * 2), umma_desc_sw128(sb + k * UMMA_K * 2), idesc,
+            tc_mma_bf16(d_tmem, da + (uint64_t)(k * (UMMA_K * 2 >> 4)), db + (uint64_t)(k * (UMMA_K * 2 >> 4)), idesc,
                         (kb | k) != 0);
           tc_commit(&empty_bar[s]);
         }
@@ -586,10 +586,10 @@ __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
           mbar_wait(&full_bar[s], (it / L::STAGES) & 1, 1);
           tc_fence_after();
           const uint32_t sa = smem_u32(tiles + s * L::STAGE_BYTES);
-          const uint32_t sb = sa + L::A_BYTES;
+          const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + L::A_BYTES);  // k-step: address field + 2
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k)
-            tc_mma_bf16(d_tmem, umma_desc_sw128(sa + k * UMMA_K * 2), umma_desc_sw128(sb + k * UMMA_K * 2), idesc,
+            tc_mma_bf16(d_tmem, da + (uint64_t)(k * (UMMA_K * 2 >> 4)), db + (uint64_t)(k * (UMMA_K * 2 >> 4)), idesc,
                         (kb | k) != 0);
           tc_commit(&empty_bar[s]);
         }

@@ -188,10 +188,11 @@ __global__ void __launch_bounds__(NTHREADS) gemm_decode_fused_kernel(const __gri
         mbar_wait(&full_bar[s], (kb / L::STAGES) & 1, 1);
         tc_fence_after();
         const uint32_t sa = smem_u32(tiles + s * L::STAGE_BYTES);
-        const uint32_t sb = sa + L::A_BYTES;
+        // one descriptor pair per stage; a k-step of 16 bf16 = 32 bytes moves the 16-byte-granular address field by 2
+        const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + L::A_BYTES);
 #pragma unroll
         for (int k = 0; k < BK / UMMA_K; ++k)
-          tc_mma_bf16(tmem_base, umma_desc_sw128(sa + k * UMMA_K * 2), umma_desc_sw128(sb + k * UMMA_K * 2), idesc,
+          tc_mma_bf16(tmem_base, da + (uint64_t)(k * (UMMA_K * 2 >> 4)), db + (uint64_t)(k * (UMMA_K * 2 >> 4)), idesc,
                       (kb | k) != 0);
         tc_commit(&empty_bar[s]);
       }
