@@ -497,25 +497,64 @@ struct TmaEpilogue {
 // EW epilogue warps.  16: every warp owns one 64-column slice of a tile, bias in shared memory, 3 mainloop stages.
 // 8: two slices per warp and the bias in registers (fetched by shuffle), which frees the room for a 4th stage - for
 // long-K GEMMs (K >= 2048) whose mainloop hides the longer epilogue and pays for a short ring instead.
-template <int BN, int EW> struct PersistTmaLayout {
+// CG = 2: CTA pair (cta_group::2) - a 256 x BN tile per pair, each CTA stages its own 128 rows of A and HALF of the B tile
+template <int BN, int EW, int CG = 1> struct PersistTmaLayout {
   static constexpr int A_BYTES = BM * BK * 2;
-  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int B_BYTES = (BN / CG) * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int EPI_BYTES = EW * 4096;                      // one swizzled 32 x 128 B buffer per epilogue warp
   static constexpr int BIAS_BYTES = EW == 16 ? EW * 256 : 0;       // 64 floats per epilogue warp
   static constexpr int BAR_BYTES = 256;
-  static constexpr int STAGES = (227 * 1024 - EPI_BYTES - BIAS_BYTES - BAR_BYTES - 1024) / STAGE_BYTES;  // 3 / 4 at BN=256
+  static constexpr int STAGES_FIT = (227 * 1024 - EPI_BYTES - BIAS_BYTES - BAR_BYTES - 1024) / STAGE_BYTES;  // 3 / 4 at BN=256
+  static constexpr int STAGES = STAGES_FIT > 6 ? 6 : STAGES_FIT;
   static constexpr int TILE_BYTES = STAGES * STAGE_BYTES;
   static constexpr int TOTAL = TILE_BYTES + EPI_BYTES + BIAS_BYTES + BAR_BYTES + 1024;
 };
 
-template <int BN, int EW>
+// ---- CTA pair (cta_group::2) plumbing: the leader CTA (cluster rank 0) issues the MMAs for both SMs; operands are staged
+// by both CTAs, whose TMA loads complete on the LEADER's barrier; commits are multicast to both CTAs' barriers.
+__device__ __forceinline__ uint32_t leader_addr(uint32_t local_smem_addr) {  // same offset in the cluster's CTA 0
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(r) : "r"(local_smem_addr));
+  return r;
+}
+__device__ __forceinline__ void mbar_expect_tx_cluster(uint32_t cluster_addr, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_addr), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA tile load of a CTA pair: data into this CTA's shared memory, completion on the leader's barrier `leader_bar`
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint32_t leader_bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(leader_bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16_pair(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(uint64_t* bar) {  // arrives on `bar` in both CTAs of the pair
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                   smem_u32(bar)),
+               "h"((uint16_t)3)
+               : "memory");
+}
+
+template <int BN, int EW, int CG>
 __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
     const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
     const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes,
     const __grid_constant__ CUtensorMap tmV, int M, int N, int K, TmaEpilogue epi) {
-  using L = PersistTmaLayout<BN, EW>;
+  using L = PersistTmaLayout<BN, EW, CG>;
   static_assert(BN == 256 && (EW == 16 || EW == 8), "four 64-column slices per tile row block, 1 or 2 per warp");
+  static_assert(CG == 1 || CG == 2, "one CTA or a CTA pair");
   constexpr int SPW = 16 / EW;  // 64-column slices per epilogue warp
   constexpr int TMEM_COLS = 2 * BN;
   extern __shared__ uint8_t smem_raw[];
@@ -531,52 +570,69 @@ __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nk = K / BK;
-  const int m_tiles = (M + BM - 1) / BM, n_tiles = (N + BN - 1) / BN;
+  // a tile is (BM * CG) x BN; CTA `rank` of a pair owns rows [rank * BM, +BM) of it and stages B rows [rank * BN/2, +BN/2)
+  const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
+  const int m_tiles = (M + BM * CG - 1) / (BM * CG), n_tiles = (N + BN - 1) / BN;
   const int ntiles = m_tiles * n_tiles;
+  const int tile0 = (int)blockIdx.x / CG, tile_step = (int)gridDim.x / CG;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmOut) : "memory");
-    for (int s = 0; s < L::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], EW); }
+    // pair: both CTAs' producers announce their bytes on the leader's full barrier; both CTAs' epilogue warps free the accumulator
+    for (int s = 0; s < L::STAGES; ++s) { mbar_init(&full_bar[s], CG); mbar_init(&empty_bar[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], EW * CG); }
     for (int w = 0; w < EW; ++w) mbar_init(&res_bar[w], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "r"(TMEM_COLS)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (CG == 2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TMEM_COLS)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TMEM_COLS)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   tc_fence_before();
   __syncthreads();
+  if (CG == 2) cluster_sync_all();  // the peer's barriers are initialised before anybody arrives on them remotely
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===== TMA producer =====
+    // ===== TMA producer (in both CTAs of a pair) =====
     if (lane == 0) {
       uint32_t it = 0;
-      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        const int a_row0 = (t % m_tiles) * BM, b_row0 = (t / m_tiles) * BN;
+      for (int t = tile0; t < ntiles; t += tile_step) {
+        const int a_row0 = (t % m_tiles) * BM * CG + rank * BM, b_row0 = (t / m_tiles) * BN + rank * (BN / CG);
         for (int kb = 0; kb < nk; ++kb, ++it) {
           const int s = it % L::STAGES;
           mbar_wait(&empty_bar[s], ((it / L::STAGES) & 1) ^ 1, 0);
-          mbar_expect_tx(&full_bar[s], L::STAGE_BYTES);
           uint8_t* sa = tiles + s * L::STAGE_BYTES;
-          tma_load_2d(sa, &tmA, &full_bar[s], kb * BK, a_row0);
-          tma_load_2d(sa + L::A_BYTES, &tmB, &full_bar[s], kb * BK, b_row0);
+          if (CG == 2) {
+            const uint32_t lbar = leader_addr(smem_u32(&full_bar[s]));
+            mbar_expect_tx_cluster(lbar, L::STAGE_BYTES);
+            tma_load_2d_pair(sa, &tmA, lbar, kb * BK, a_row0);
+            tma_load_2d_pair(sa + L::A_BYTES, &tmB, lbar, kb * BK, b_row0);
+          } else {
+            mbar_expect_tx(&full_bar[s], L::STAGE_BYTES);
+            tma_load_2d(sa, &tmA, &full_bar[s], kb * BK, a_row0);
+            tma_load_2d(sa + L::A_BYTES, &tmB, &full_bar[s], kb * BK, b_row0);
+          }
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+    // ===== MMA issuer (pair: the leader CTA only; its MMAs run on both SMs and read both CTAs' shared memory) =====
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM * CG, BN);
       uint32_t it = 0, ti = 0;
-      for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++ti) {
+      for (int t = tile0; t < ntiles; t += tile_step, ++ti) {
         const uint32_t acc = ti & 1;
         mbar_wait(&tmem_empty_bar[acc], ((ti >> 1) & 1) ^ 1, 3);
         tc_fence_after();
@@ -588,12 +644,17 @@ __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
           const uint32_t sa = smem_u32(tiles + s * L::STAGE_BYTES);
           const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + L::A_BYTES);  // k-step: address field + 2
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k)
-            tc_mma_bf16(d_tmem, da + (uint64_t)(k * (UMMA_K * 2 >> 4)), db + (uint64_t)(k * (UMMA_K * 2 >> 4)), idesc,
-                        (kb | k) != 0);
-          tc_commit(&empty_bar[s]);
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            if (CG == 2)
+              tc_mma_bf16_pair(d_tmem, da + (uint64_t)(k * (UMMA_K * 2 >> 4)), db + (uint64_t)(k * (UMMA_K * 2 >> 4)), idesc,
+                               (kb | k) != 0);
+            else
+              tc_mma_bf16(d_tmem, da + (uint64_t)(k * (UMMA_K * 2 >> 4)), db + (uint64_t)(k * (UMMA_K * 2 >> 4)), idesc,
+                          (kb | k) != 0);
+          }
+          if (CG == 2) tc_commit_pair(&empty_bar[s]); else tc_commit(&empty_bar[s]);
         }
-        tc_commit(&tmem_full_bar[acc]);
+        if (CG == 2) tc_commit_pair(&tmem_full_bar[acc]); else tc_commit(&tmem_full_bar[acc]);
       }
     }
   } else {
@@ -606,8 +667,13 @@ __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
     uint32_t ti = 0, res_uses = 0;
     const uint32_t swz = (uint32_t)(lane & 7);
     const uint32_t my_row = stage + lane * 128;
-    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++ti) {
-      const int a_row0 = (t % m_tiles) * BM, b_row0 = (t / m_tiles) * BN;
+    // the accumulator is handed back to the MMA issuer, i.e. (pair) to the leader CTA's barrier
+    auto free_acc = [&](uint32_t acc) {
+      if (CG == 2) mbar_arrive_cluster(leader_addr(smem_u32(&tmem_empty_bar[acc])));
+      else mbar_arrive(&tmem_empty_bar[acc]);
+    };
+    for (int t = tile0; t < ntiles; t += tile_step, ++ti) {
+      const int a_row0 = (t % m_tiles) * BM * CG + rank * BM, b_row0 = (t / m_tiles) * BN;
       const uint32_t acc = ti & 1;
       const int row0 = a_row0 + quad * 32;
 #pragma unroll 1
@@ -645,14 +711,14 @@ __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
         if (epi.has_res && live) { mbar_wait(rbar, res_uses & 1, 5); ++res_uses; }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0 && last_slice) mbar_arrive(&tmem_empty_bar[acc]);
+        if (lane == 0 && last_slice) free_acc(acc);
         continue;
       }
 #endif
       if (!live) {
         tc_fence_before();
         __syncwarp();
-        if (lane == 0 && last_slice) mbar_arrive(&tmem_empty_bar[acc]);
+        if (lane == 0 && last_slice) free_acc(acc);
         continue;
       }
       // bias of element i (0..63) of this slice
@@ -669,7 +735,7 @@ __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
           if (sub == 1 && last_slice) {  // last read of this accumulator by this warp
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+            if (lane == 0) free_acc(acc);
           }
           const int c0 = col0 + sub * 32;
           if (c0 >= N) continue;  // (the TMA store would clip it anyway)
@@ -718,7 +784,7 @@ __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
-          if (last_slice) mbar_arrive(&tmem_empty_bar[acc]);
+          if (last_slice) free_acc(acc);
           tma_store_wait_read();  // the buffer's previous contents have left
         }
         __syncwarp();
@@ -757,8 +823,10 @@ __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
 
   tc_fence_before();
   __syncthreads();
+  if (CG == 2) cluster_sync_all();  // neither CTA of a pair leaves (or frees TMEM) while the other may still use it
   if (warp == 1) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    if (CG == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
   }
 }
 
@@ -891,14 +959,14 @@ bool tma_epilogue_ok(const GemmEpilogue& e, int M, int N) {
   return N % 8 == 0;
 }
 
-template <int EW>
+template <int EW, int CG>
 int launch_persistent_tma(const bf16* A, int M, const bf16* W, int N, int K, const GemmEpilogue& e, cudaStream_t st) {
-  using L = PersistTmaLayout<256, EW>;
+  using L = PersistTmaLayout<256, EW, CG>;
   static_assert(L::TOTAL <= 227 * 1024, "shared-memory budget");
-  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(gemm_bf16_persistent_tma_kernel<256, EW>), L::TOTAL));
+  TRY(tutor_set_max_smem(reinterpret_cast<const void*>(gemm_bf16_persistent_tma_kernel<256, EW, CG>), L::TOTAL));
   CUtensorMap ta, tb, to, tr, tv;
   TRY(make_map(&ta, A, M, K, BM));
-  TRY(make_map(&tb, W, N, K, 256));
+  TRY(make_map(&tb, W, N, K, 256 / CG));
   const bool f32 = e.out_f32 != nullptr;
   TmaEpilogue te{e.bias, e.act, e.residual != nullptr, f32 ? 1 : 0, 0, 0, 0, 0, 0, 0};
   if (e.qkv_mode) {
@@ -916,9 +984,24 @@ int launch_persistent_tma(const bf16* A, int M, const bf16* W, int N, int K, con
   int dev = 0, sms = 148;
   CUDA_TRY(cudaGetDevice(&dev));
   CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const int ntiles = ceil_div(M, BM) * ceil_div(N, 256);
-  CUDA_TRY(tutor_launch(gemm_bf16_persistent_tma_kernel<256, EW>, dim3(ntiles < sms ? ntiles : sms), dim3(64 + 32 * EW),
-                        (size_t)L::TOTAL, st, ta, tb, to, tr, tv, M, N, K, te));
+  const int ntiles = ceil_div(M, BM * CG) * ceil_div(N, 256);
+  if (CG == 2) {
+    // CTA pairs: a cluster of two along x; as many pairs as there are tiles, at most one CTA per SM
+    const int pairs = ntiles < sms / 2 ? ntiles : sms / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * pairs); cfg.blockDim = dim3(64 + 32 * EW); cfg.dynamicSmemBytes = (size_t)L::TOTAL; cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = tutor_pdl_enabled ? 2 : 1;
+    CUDA_TRY(cudaLaunchKernelEx(&cfg, gemm_bf16_persistent_tma_kernel<256, EW, CG>, ta, tb, to, tr, tv, M, N, K, te));
+  } else {
+    CUDA_TRY(tutor_launch(gemm_bf16_persistent_tma_kernel<256, EW, CG>, dim3(ntiles < sms ? ntiles : sms), dim3(64 + 32 * EW),
+                          (size_t)L::TOTAL, st, ta, tb, to, tr, tv, M, N, K, te));
+  }
   KERNEL_LAUNCHED();
   return TUTOR_OK;
 }
@@ -982,8 +1065,14 @@ int k_gemm_bf16(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpi
   if (persistent && tma_epi && N >= 128 && tma_epilogue_ok(epi, M, N)) {
     // long K: the mainloop hides an 8-warp epilogue and gains a 4th pipeline stage (TUTOR_GEMM_EW16=1 forces 16 warps)
     static const bool ew16 = tutor_experiment("TUTOR_GEMM_EW16") != nullptr;
-    if (K >= 2048 && !ew16) return launch_persistent_tma<8>(A, M, W, N, K, epi, st);
-    return launch_persistent_tma<16>(A, M, W, N, K, epi, st);
+    // TUTOR_GEMM_PAIR=1: CTA pairs (cta_group::2, 256 x 256 tiles, each CTA stages half of B)
+    static const bool pair = getenv("TUTOR_GEMM_PAIR") != nullptr && atoi(getenv("TUTOR_GEMM_PAIR")) != 0;
+    if (pair && M >= 256) {
+      if (K >= 2048 && !ew16) return launch_persistent_tma<8, 2>(A, M, W, N, K, epi, st);
+      return launch_persistent_tma<16, 2>(A, M, W, N, K, epi, st);
+    }
+    if (K >= 2048 && !ew16) return launch_persistent_tma<8, 1>(A, M, W, N, K, epi, st);
+    return launch_persistent_tma<16, 1>(A, M, W, N, K, epi, st);
   }
   if (persistent) {
     if (wide && N >= 256) return launch_persistent<256>(A, M, W, N, K, epi, st);
