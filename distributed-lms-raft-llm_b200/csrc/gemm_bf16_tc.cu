@@ -780,9 +780,22 @@ __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
       } else {
         // one piece of 64 bf16 columns (128-byte rows)
         float v[64];
-        tc_ld32x2(taddr, taddr + 32, v, v + 32);
+#ifdef TUTOR_TRACE
+        if (g_epi_skip == 3) {  // tools/microbench_gemm.cu: no TMEM read
+#pragma unroll
+          for (int i = 0; i < 64; ++i) v[i] = 0.f;
+        } else
+#endif
+        tc_ld64(taddr, v);
         tc_fence_before();
         __syncwarp();
+#ifdef TUTOR_TRACE
+        if (g_epi_skip == 4) {  // TMEM read only: no epilogue math, no shared-memory or global traffic
+          if (lane == 0 && last_slice) free_acc(acc);
+          if (v[lane] == 12345.f) sbias[0] = v[0];  // keep the load
+          continue;
+        }
+#endif
         if (lane == 0) {
           if (last_slice) free_acc(acc);
           tma_store_wait_read();  // the buffer's previous contents have left
@@ -1065,8 +1078,9 @@ int k_gemm_bf16(const bf16* A, const bf16* W, int M, int N, int K, const GemmEpi
   if (persistent && tma_epi && N >= 128 && tma_epilogue_ok(epi, M, N)) {
     // long K: the mainloop hides an 8-warp epilogue and gains a 4th pipeline stage (TUTOR_GEMM_EW16=1 forces 16 warps)
     static const bool ew16 = tutor_experiment("TUTOR_GEMM_EW16") != nullptr;
-    // TUTOR_GEMM_PAIR=1: CTA pairs (cta_group::2, 256 x 256 tiles, each CTA stages half of B)
-    static const bool pair = getenv("TUTOR_GEMM_PAIR") != nullptr && atoi(getenv("TUTOR_GEMM_PAIR")) != 0;
+    // CTA pairs (cta_group::2, 256 x 256 tiles, each CTA stages half of B: a third less shared-memory traffic per FLOP,
+    // 5-9 % faster at the BERT / GPT-2 large shapes); TUTOR_GEMM_PAIR=0 keeps one CTA per tile (cross-check)
+    static const bool pair = getenv("TUTOR_GEMM_PAIR") == nullptr || atoi(getenv("TUTOR_GEMM_PAIR")) != 0;
     if (pair && M >= 256) {
       if (K >= 2048 && !ew16) return launch_persistent_tma<8, 2>(A, M, W, N, K, epi, st);
       return launch_persistent_tma<16, 2>(A, M, W, N, K, epi, st);
