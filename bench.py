@@ -253,7 +253,7 @@ def attn_kernel_roofline(lib, check, torch, pk):
     """Dominant kernel of the step (86 % of its bytes): the KV-streaming decode attention AS THE STEP LAUNCHES IT (c_attn
     split-K partials summed + bias, K/V row appended, attention over the cache), timed alone with CUDA events on the
     launching stream at the workload's mid-point cache length, rotating over 12 layers of cache (1.5 GB > L2)."""
-    B, H, L, ks = B_PER_GPU, 12, 12, 6
+    B, H, L, ks = B_PER_GPU, 12, 12, 2  # ks: the K splits of c_attn at this batch size (decode_plan: 18 x 4 tiles x 2)
     S = T_PROMPT + NEW // 2  # tokens including the one being decoded: 639 cached rows + the new one
     Smax, d = 768, H * 64
     g = torch.Generator(device="cuda").manual_seed(0)
