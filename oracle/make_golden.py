@@ -209,6 +209,19 @@ def make_cfg2_logits(tut, lms, seq=None):
     print("cfg2 teacher-forced logits for", CFG2_TF)
 
 
+def make_cfg2_hf_bf16(tut, lms):
+    """What transformers' OWN bf16 run does on configs[2]: the same model cast with .bfloat16(), same
+    stock generate call on the host, rows 0..15, 128 new tokens.  The GPU test compares the engine's bf16 agreement with the
+    fp32 oracle to this run's agreement with the fp32 oracle over the same rows and steps."""
+    import copy
+    model = copy.deepcopy(tut.model).bfloat16()
+    ids = rp.gpt2_prompt_ids(64, 512, seed=1)[:16]
+    t0 = time.time()
+    seq = rp.generate(model, ids, max_new_tokens=128, repetition_penalty=1.0)
+    print("cfg2 HF bf16 (16 rows, 128 tokens)", time.time() - t0, "s")
+    np.savez_compressed(os.path.join(OUT, "gpt2_cfg2_hf_bf16.npz"), ids_p10=seq[:, 512:].numpy().astype(np.int32))
+
+
 def make_cfg3(tut, lms):
     """configs[3] parity target: GPT-2 large, B=16, 896-token prompts, +128 tokens (1024 total)."""
     model = rp.build_gpt2("large", seed=0)
@@ -244,10 +257,10 @@ def make_padded(tut, lms):
 
 
 MAKERS = dict(padded=make_padded, cfg0=make_cfg0, as_written=make_as_written, tiny=make_tiny, bert=make_bert, bert_tiny=make_bert_tiny,
-              cfg2=make_cfg2, cfg2_logits=make_cfg2_logits, cfg3=make_cfg3)
+              cfg2=make_cfg2, cfg2_logits=make_cfg2_logits, cfg2_hf_bf16=make_cfg2_hf_bf16, cfg3=make_cfg3)
 # every fixture under tests/golden/, in the order they are cheapest to make (cfg2 and cfg3 take many CPU-minutes each;
 # cfg2 writes gpt2_cfg2_logits.npz too, `cfg2_logits` alone rebuilds it from the committed ids)
-ALL = ["cfg0", "as_written", "tiny", "padded", "bert", "bert_tiny", "cfg2", "cfg3"]
+ALL = ["cfg0", "as_written", "tiny", "padded", "bert", "bert_tiny", "cfg2", "cfg2_hf_bf16", "cfg3"]
 
 
 def main():
