@@ -600,6 +600,7 @@ def main():
             # the metric's "% HBM roofline": the WHOLE decode forward (weights + KV read + KV write) over its measured time
             "roofline_step": {"what": "configs[2] decode forward, averaged over cache lengths 512..766", "bound": "hbm",
                               "achieved": step_gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": step_gbs / pk["hbm"],
+                              "frac_of_nominal_8tbs": step_gbs / 8000.0,
                               "algorithmic_gb": step_bytes / 1e9, "ms": ms_decode, "peak_source": pk["source"]},
         }
         try:
