@@ -76,9 +76,14 @@ def test_linear_bf16(pkg, lib, M, N, K, impl):
     W = (torch.randn(N, K, generator=g) * 0.05).to(DEV).bfloat16()
     bias = torch.randn(N, generator=g).to(DEV)
     res = torch.randn(M, N, generator=g).to(DEV)
-    out = torch.full((M, N), float("nan"), device=DEV)
+    guard = 8192  # guard zones around the output: the CTA-pair kernel's 256-row tiles overhang ragged M by up to 255 rows
+    slab = torch.full((M * N + 2 * guard,), float("nan"), device=DEV)
+    slab[:guard] = 7.0
+    slab[guard + M * N:] = 7.0
+    out = slab[guard:guard + M * N].view(M, N)
     pkg._lib.check(lib.tutor_linear(BF16, ptr(A), ptr(W), ptr(bias), ptr(res), ptr(out), 1, M, N, K, 1, impl, None))
     sync()
+    assert (slab[:guard] == 7.0).all() and (slab[guard + M * N:] == 7.0).all(), "stores outside the output tensor"
     ref = _linear_ref(A.double(), W.double(), bias.double(), res.double(), 1).float()
     # bf16 inputs are exact in fp32, so only the accumulation order differs - except that the tcgen05 kernel's
     # row-major (M > 128) epilogue uses the one-instruction tanh (|err| ~ 5e-4), stated tolerance 2e-3
@@ -112,12 +117,19 @@ def test_attn_prefill(pkg, lib, dtype, B, H, T, causal):
     q = torch.randn(B, T, H, 64, generator=g).to(DEV).to(td)
     k = torch.randn(B, H, Smax, 64, generator=g).to(DEV).to(td)
     v = torch.randn(B, H, Smax, 64, generator=g).to(DEV).to(td)
-    out = torch.empty(B, T, H, 64, device=DEV, dtype=td)
+    # the output sits between two guard zones: a kernel that stores past either end of it (query tiles are 128 rows, the
+    # last one is ragged) would change them
+    n, guard = B * T * H * 64, 4096
+    slab = torch.full((n + 2 * guard,), 7.0, device=DEV, dtype=td)
+    out = slab[guard:guard + n].view(B, T, H, 64)
+    kv_before = (k.clone(), v.clone())
     pkg._lib.check(lib.tutor_attn_prefill(dtype, ptr(q), ptr(k), ptr(v), ptr(out), B, H, T, Smax, causal, None))
     sync()
     ref = _sdpa_ref(q, k[:, :, :T], v[:, :, :T], causal)
     tol = 2e-5 if dtype == F32 else 2e-2
     assert (out.float() - ref).abs().max().item() < tol
+    assert (slab[:guard] == 7.0).all() and (slab[guard + n:] == 7.0).all(), "stores outside the output tensor"
+    assert torch.equal(k, kv_before[0]) and torch.equal(v, kv_before[1]), "the cache must not be written"
 
 
 @pytest.mark.parametrize("dtype", [F32, BF16])
