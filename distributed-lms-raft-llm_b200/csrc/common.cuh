@@ -202,6 +202,7 @@ struct GemmEpilogue {
   int d, H, Smax, T;   // T = tokens per sequence in this GEMM (row m -> b = m / T, t = m % T)
   int pos0;            // first cache position of this GEMM's tokens (prefill: 0)
   const int* pos_dev;  // if non-null: position = *pos_dev - 1 (decode step; T must be 1)
+  const bf16* residual_bf16;  // [M, ldo] bf16 or null: the residual of a bf16 activation stream (out_bf16 only, not with residual)
 };
 
 // everything after bias + activation: residual add and the store (plain or QKV scatter)
@@ -214,6 +215,7 @@ __device__ __forceinline__ void epilogue_finish(const GemmEpilogue& e, int m, in
   if (!e.qkv_mode) {
     size_t o = (size_t)m * e.ldo + n;
     if (e.residual) v += e.residual[o];
+    if (e.residual_bf16) v += __bfloat162float(e.residual_bf16[o]);
     if (e.out_f32) e.out_f32[o] = v;
     if (e.out_bf16) e.out_bf16[o] = __float2bfloat16_rn(v);
     return;

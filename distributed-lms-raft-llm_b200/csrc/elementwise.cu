@@ -89,6 +89,77 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int in_stride, int
   }
 }
 
+// The same LayerNorm over rows held in bf16 (BERT in bf16 mode keeps its activation stream in bf16 between the linear
+// layers, like the reference's bf16 modules do): NV8 16-byte vectors of 8 elements per lane, statistics in fp32.
+template <int NV8>
+__global__ void layernorm_bf16in_kernel(const bf16* __restrict__ x, const float* __restrict__ gamma,
+                                        const float* __restrict__ beta, float eps, float* __restrict__ out_f32,
+                                        bf16* __restrict__ out_bf16, int M, int d) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= M) return;
+  const int lane = threadIdx.x & 31;
+  const bf16* xr = x + (size_t)r * d;
+  float v[NV8][8];
+  float4 g[NV8][2], b[NV8][2];
+  uint4 raw[NV8];
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int j = 0; j < NV8; ++j) {  // every load first: one memory round trip
+    const int i = lane * 8 + j * 256;
+    const bool ok = i < d;
+    raw[j] = ok ? *reinterpret_cast<const uint4*>(xr + i) : make_uint4(0, 0, 0, 0);
+    g[j][0] = ok ? load4(gamma + i) : zero;
+    g[j][1] = ok ? load4(gamma + i + 4) : zero;
+    b[j][0] = ok ? load4(beta + i) : zero;
+    b[j][1] = ok ? load4(beta + i + 4) : zero;
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < NV8; ++j) {
+    unpack_bf16x8(raw[j], v[j]);
+    s += ((v[j][0] + v[j][1]) + (v[j][2] + v[j][3])) + ((v[j][4] + v[j][5]) + (v[j][6] + v[j][7]));
+  }
+  const float mean = warp_sum(s) / d;
+  float q = 0.f;
+#pragma unroll
+  for (int j = 0; j < NV8; ++j) {
+    if (lane * 8 + j * 256 < d) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float a = v[j][k] - mean;
+        q = fmaf(a, a, q);
+      }
+    }
+  }
+  const float rstd = 1.0f / sqrtf(warp_sum(q) / d + eps);
+#pragma unroll
+  for (int j = 0; j < NV8; ++j) {
+    const int i = lane * 8 + j * 256;
+    if (i < d) {
+      const float gg[8] = {g[j][0].x, g[j][0].y, g[j][0].z, g[j][0].w, g[j][1].x, g[j][1].y, g[j][1].z, g[j][1].w};
+      const float bb[8] = {b[j][0].x, b[j][0].y, b[j][0].z, b[j][0].w, b[j][1].x, b[j][1].y, b[j][1].z, b[j][1].w};
+      float o[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = (v[j][k] - mean) * rstd * gg[k] + bb[k];
+      if (out_f32) {
+        *reinterpret_cast<float4*>(out_f32 + (size_t)r * d + i) = make_float4(o[0], o[1], o[2], o[3]);
+        *reinterpret_cast<float4*>(out_f32 + (size_t)r * d + i + 4) = make_float4(o[4], o[5], o[6], o[7]);
+      }
+      if (out_bf16) {
+        uint32_t w[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          __nv_bfloat162 h2 = __floats2bfloat162_rn(o[2 * k], o[2 * k + 1]);
+          w[k] = *reinterpret_cast<uint32_t*>(&h2);
+        }
+        *reinterpret_cast<uint4*>(out_bf16 + (size_t)r * d + i) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+  }
+}
+
 // ---- BERT embeddings: word + token_type(0) + position, then LayerNorm eps 1e-12
 // (HF/models/bert/modeling_bert.py:102-111).
 template <typename WT>
@@ -214,6 +285,22 @@ int k_layernorm(const float* x, int in_stride, int in_offset, const float* gamma
   else if (d <= 768) LN_LAUNCH(6);
   else if (d <= 1280) LN_LAUNCH(10);
   else LN_LAUNCH(16);
+#undef LN_LAUNCH
+  KERNEL_LAUNCHED();
+  return TUTOR_OK;
+}
+
+int k_layernorm_bf16in(const bf16* x, const float* gamma, const float* beta, float eps, float* out_f32, bf16* out_bf16,
+                       int M, int d, cudaStream_t st) {
+  ARG_CHECK(d % 8 == 0 && d <= 2048 && (reinterpret_cast<uintptr_t>(x) & 15) == 0, "layernorm (bf16 rows): unsupported d=%d", d);
+  if (M == 0) return TUTOR_OK;
+  const dim3 grid(ceil_div(M, 4)), block(128);
+#define LN_LAUNCH(NV8) \
+  CUDA_TRY(tutor_launch(layernorm_bf16in_kernel<NV8>, grid, block, 0, st, x, gamma, beta, eps, out_f32, out_bf16, M, d))
+  if (d <= 256) LN_LAUNCH(1);
+  else if (d <= 768) LN_LAUNCH(3);
+  else if (d <= 1280) LN_LAUNCH(5);
+  else LN_LAUNCH(8);
 #undef LN_LAUNCH
   KERNEL_LAUNCHED();
   return TUTOR_OK;

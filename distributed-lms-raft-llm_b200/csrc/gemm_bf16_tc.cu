@@ -108,6 +108,15 @@ __device__ __forceinline__ void store_run32(const GemmEpilogue& e, int m, int n0
         for (int j = 0; j < 8; ++j) v[i + j] += r[j];
       }
     }
+    if (!e.qkv_mode && e.residual_bf16) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+        float r[8];
+        unpack_bf16x8(*reinterpret_cast<const uint4*>(e.residual_bf16 + o + i), r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[i + j] += r[j];
+      }
+    }
     if (e.out_f32) of = e.out_f32 + o;
     if (e.out_bf16) ob = e.out_bf16 + o;
   } else {  // 32 columns sit inside one head's 64-wide row of the K or V cache
@@ -486,7 +495,7 @@ __global__ void __launch_bounds__(NTHREADS_PERSIST) gemm_bf16_persistent_kernel(
 struct TmaEpilogue {
   const float* bias;  // [N] or null
   int act;
-  int has_res;        // residual tile (fp32) is read through tmRes
+  int has_res;        // residual tile (fp32 with an fp32 output, bf16 with a bf16 output) is read through tmRes
   int out_f32;        // 1: fp32 output in 32-column pieces, 0: bf16 output in 64-column pieces
   // QKV scatter (qkv != 0, bf16): columns [0,d) -> q [M,d] through tmOut; [d,2d) / [2d,3d) -> the K / V cache,
   // addressed as a [(B*H*Smax), 64] matrix through tmRes / tmV: a piece is one head's 64 dims of 32 consecutive tokens
@@ -777,6 +786,43 @@ __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
           }
           __syncwarp();
         }
+      } else if (epi.has_res) {
+        // one piece of 64 bf16 columns added to the bf16 residual piece that sits where the output will go; the
+        // accumulator is read in two halves, which keeps this path inside the register budget of the 64-column one
+        mbar_wait(rbar, res_uses & 1, 5);
+        ++res_uses;
+#pragma unroll 1
+        for (int sub = 0; sub < 2; ++sub) {
+          float v[32];
+          tc_ld32(taddr + sub * 32, v);
+          if (sub == 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0 && last_slice) free_acc(acc);
+          }
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const uint32_t addr = my_row + (((uint32_t)(sub * 4 + c) ^ swz) << 4);
+            uint4 rv;
+            asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(rv.x), "=r"(rv.y), "=r"(rv.z), "=r"(rv.w) : "r"(addr));
+            float r[8];
+            unpack_bf16x8(rv, r);
+            uint32_t w[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int i = 8 * c + 2 * j;
+              __nv_bfloat162 h2 =
+                  __floats2bfloat162_rn(apply_act_fast(v[i] + bias_at(sub * 32 + i), epi.act) + r[2 * j],
+                                        apply_act_fast(v[i + 1] + bias_at(sub * 32 + i + 1), epi.act) + r[2 * j + 1]);
+              w[j] = *reinterpret_cast<uint32_t*>(&h2);
+            }
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+          }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) tma_store_2d(&tmOut, stage, col0, row0);
+        __syncwarp();
       } else {
         // one piece of 64 bf16 columns (128-byte rows)
         float v[64];
@@ -955,7 +1001,8 @@ int launch_persistent(const bf16* A, int M, const bf16* W, int N, int K, const G
   return TUTOR_OK;
 }
 
-// the TMA-staged epilogue covers plain row-major outputs: bias -> activation -> (+ fp32 residual) -> fp32 or bf16
+// the TMA-staged epilogue covers plain row-major outputs: bias -> activation -> (+ fp32 residual) -> fp32, or
+// bias -> activation -> (+ bf16 residual) -> bf16
 bool tma_epilogue_ok(const GemmEpilogue& e, int M, int N) {
   if (e.qkv_mode) {  // q [M,d] + scatter into the K / V cache: whole 32-token pieces of one sequence, bf16 everywhere
     return e.out_bf16 && !e.out_f32 && !e.residual && !e.pos_dev && e.kv_dtype == DT_BF16 && e.T % 32 == 0 &&
@@ -966,8 +1013,11 @@ bool tma_epilogue_ok(const GemmEpilogue& e, int M, int N) {
   if (e.ldo != N) return false;
   if ((e.out_f32 != nullptr) == (e.out_bf16 != nullptr)) return false;  // exactly one output
   if (e.residual && !e.out_f32) return false;
+  if (e.residual_bf16 && (!e.out_bf16 || e.residual)) return false;
   const void* out = e.out_f32 ? (const void*)e.out_f32 : (const void*)e.out_bf16;
-  if ((reinterpret_cast<uintptr_t>(out) & 15) || (e.residual && (reinterpret_cast<uintptr_t>(e.residual) & 15))) return false;
+  if ((reinterpret_cast<uintptr_t>(out) & 15) || (e.residual && (reinterpret_cast<uintptr_t>(e.residual) & 15)) ||
+      (e.residual_bf16 && (reinterpret_cast<uintptr_t>(e.residual_bf16) & 15)))
+    return false;
   if (e.bias && (reinterpret_cast<uintptr_t>(e.bias) & 15)) return false;
   return N % 8 == 0;
 }
@@ -981,7 +1031,7 @@ int launch_persistent_tma(const bf16* A, int M, const bf16* W, int N, int K, con
   TRY(make_map(&ta, A, M, K, BM));
   TRY(make_map(&tb, W, N, K, 256 / CG));
   const bool f32 = e.out_f32 != nullptr;
-  TmaEpilogue te{e.bias, e.act, e.residual != nullptr, f32 ? 1 : 0, 0, 0, 0, 0, 0, 0};
+  TmaEpilogue te{e.bias, e.act, e.residual != nullptr || e.residual_bf16 != nullptr, f32 ? 1 : 0, 0, 0, 0, 0, 0, 0};
   if (e.qkv_mode) {
     const int cache_rows = (M / e.T) * e.H * e.Smax;
     TRY(make_map_epi(&to, e.out_bf16, false, M, e.d));
@@ -991,6 +1041,7 @@ int launch_persistent_tma(const bf16* A, int M, const bf16* W, int N, int K, con
   } else {
     TRY(make_map_epi(&to, f32 ? (const void*)e.out_f32 : (const void*)e.out_bf16, f32, M, N));
     if (e.residual) TRY(make_map_epi(&tr, e.residual, true, M, N));
+    else if (e.residual_bf16) TRY(make_map_epi(&tr, e.residual_bf16, false, M, N));
     else tr = to;  // unused
     tv = to;       // unused
   }

@@ -8,6 +8,9 @@ int k_gpt2_embed(const int32_t* ids, int ids_ld, const int* len_dev, int T, cons
                  const float* wpe, int d, float* x, int M, const int* npad, cudaStream_t st);
 int k_layernorm(const float* x, int in_stride, int in_offset, const float* gamma, const float* beta, float eps,
                 float* out_f32, bf16* out_bf16, int M, int d, cudaStream_t st);
+// the same over bf16 rows [M, d] (d % 8 == 0, d <= 2048)
+int k_layernorm_bf16in(const bf16* x, const float* gamma, const float* beta, float eps, float* out_f32, bf16* out_bf16,
+                       int M, int d, cudaStream_t st);
 int k_bert_embed_ln(const int32_t* ids, int T, const void* word, int wdtype, const float* pos, const float* type0,
                     const float* gamma, const float* beta, float eps, float* out_f32, bf16* out_bf16, int M, int d,
                     cudaStream_t st);
