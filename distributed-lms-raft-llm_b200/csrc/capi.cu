@@ -170,6 +170,20 @@ int tutor_linear(int dtype, const void* A, const void* W, const float* bias, con
   return k_gemm_bf16((const bf16*)A, (const bf16*)W, M, N, K, e, (cudaStream_t)stream);
 }
 
+int tutor_linear_bf16_residual(const void* A, const void* W, const float* bias, const void* residual_bf16, void* out_bf16,
+                               int M, int N, int K, int act, void* stream) {
+  ARG_CHECK(A && W && out_bf16, "linear_bf16_residual: null argument");
+  GemmEpilogue e{};
+  e.bias = bias; e.residual_bf16 = (const bf16*)residual_bf16; e.out_bf16 = (bf16*)out_bf16; e.act = act; e.ldo = N;
+  return k_gemm_bf16((const bf16*)A, (const bf16*)W, M, N, K, e, (cudaStream_t)stream);
+}
+
+int tutor_layernorm_bf16(const void* x, const float* gamma, const float* beta, float eps, float* out_f32, void* out_bf16,
+                         int M, int d, void* stream) {
+  ARG_CHECK(x && gamma && beta && (out_f32 || out_bf16), "layernorm_bf16: null argument");
+  return k_layernorm_bf16in((const bf16*)x, gamma, beta, eps, out_f32, (bf16*)out_bf16, M, d, (cudaStream_t)stream);
+}
+
 int tutor_attn_prefill(int dtype, const void* q, const void* k, const void* v, void* out, int B, int H, int T, int Smax,
                        int causal, void* stream) {
   ARG_CHECK(q && k && v && out, "attn_prefill: null argument");

@@ -172,6 +172,14 @@ int tutor_layernorm(const float* x_dev, const float* gamma_dev, const float* bet
  * impl 0 = product kernel; impl 1 (bf16 only) = the mma.sync cross-check kernel used by the tests.            */
 int tutor_linear(int dtype, const void* A_dev, const void* W_dev, const float* bias_dev, const float* residual_dev,
                  void* out_dev, int out_is_f32, int M, int N, int K, int act, int impl, void* stream);
+/* The two kernels of the bf16 activation stream BERT runs in bf16 mode (BertSelfOutput / BertOutput,
+ * modeling_bert.py:294-298, 352-356, with every tensor between the linear layers held in bf16 as the reference's bf16
+ * modules hold it): out_bf16[M,N] = bf16(act(A · W^T + bias) + residual_bf16), fp32 accumulation and sum; and
+ * nn.LayerNorm over bf16 rows (d % 8 == 0, d <= 2048), fp32 statistics.                                        */
+int tutor_linear_bf16_residual(const void* A_dev, const void* W_dev, const float* bias_dev, const void* residual_bf16_dev,
+                               void* out_bf16_dev, int M, int N, int K, int act, void* stream);
+int tutor_layernorm_bf16(const void* x_bf16_dev, const float* gamma_dev, const float* beta_dev, float eps,
+                         float* out_f32_dev, void* out_bf16_dev, int M, int d, void* stream);
 /* SDPA (sdpa_attention.py:42-104), head_dim 64, scale 1/8. q/out [B*T, H*64]; k/v [B][H][Smax][64]. */
 int tutor_attn_prefill(int dtype, const void* q_dev, const void* k_dev, const void* v_dev, void* out_dev, int B, int H,
                        int T, int Smax, int causal, void* stream);

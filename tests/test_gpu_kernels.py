@@ -95,6 +95,45 @@ def test_linear_bf16(pkg, lib, M, N, K, impl):
     assert rel_err(outb, refb) < 1e-2
 
 
+@pytest.mark.parametrize("M,N,K", BF16_SHAPES)
+def test_linear_bf16_stream_residual(pkg, lib, M, N, K):
+    """The bf16 activation stream's linear layer: bf16(A W^T + bias + bf16 residual), every kernel flavour (swap-AB,
+    single-CTA and CTA-pair TMA-staged epilogues, ragged edges), guard zones around the output."""
+    g = torch.Generator().manual_seed(M + 3 * N + K)
+    A = torch.randn(M, K, generator=g).to(DEV).bfloat16()
+    W = (torch.randn(N, K, generator=g) * 0.05).to(DEV).bfloat16()
+    bias = torch.randn(N, generator=g).to(DEV)
+    res = (torch.randn(M, N, generator=g) * 2).to(DEV).bfloat16()
+    guard = 8192
+    slab = torch.full((M * N + 2 * guard,), float("nan"), device=DEV).bfloat16()
+    slab[:guard] = 7.0
+    slab[guard + M * N:] = 7.0
+    out = slab[guard:guard + M * N].view(M, N)
+    pkg._lib.check(lib.tutor_linear_bf16_residual(ptr(A), ptr(W), ptr(bias), ptr(res), ptr(out), M, N, K, 0, None))
+    sync()
+    assert (slab[:guard] == 7.0).all() and (slab[guard + M * N:] == 7.0).all(), "stores outside the output tensor"
+    ref = _linear_ref(A.double(), W.double(), bias.double(), res.double(), 0)
+    # one bf16 rounding of the fp32 sum: half an ulp = 2^-9 relative, plus the accumulation-order difference
+    assert ((out.double() - ref).abs() <= ref.abs() * 2.0 ** -8 + 1e-4).all()
+
+
+@pytest.mark.parametrize("M,d,eps", [(5, 128, 1e-12), (64, 768, 1e-12), (1025, 768, 1e-12), (33, 1280, 1e-5), (7, 2048, 1e-5)])
+def test_layernorm_bf16_rows(pkg, lib, M, d, eps):
+    g = torch.Generator(device="cpu").manual_seed(1)
+    x = (torch.randn(M, d, generator=g) * 3 + 0.5).to(DEV).bfloat16()
+    w, b = torch.randn(d, generator=g).to(DEV), torch.randn(d, generator=g).to(DEV)
+    of, ob = torch.empty(M, d, device=DEV), torch.empty(M, d, dtype=torch.bfloat16, device=DEV)
+    pkg._lib.check(lib.tutor_layernorm_bf16(ptr(x), ptr(w), ptr(b), eps, ptr(of), ptr(ob), M, d, None))
+    sync()
+    ref = torch.nn.functional.layer_norm(x.float(), (d,), w, b, eps)
+    assert (of - ref).abs().max().item() < 2e-5
+    assert (ob.float() - ref).abs().max().item() < 0.05
+    ob2 = torch.empty_like(ob)
+    pkg._lib.check(lib.tutor_layernorm_bf16(ptr(x), ptr(w), ptr(b), eps, None, ptr(ob2), M, d, None))
+    sync()
+    assert torch.equal(ob, ob2)
+
+
 def _sdpa_ref(q, k, v, causal):
     # q [B,T,H,64], k/v [B,H,S,64]
     qh = q.permute(0, 2, 1, 3).double()

@@ -1,4 +1,4 @@
-"""Decode attention at configs[2] shape: the fused instance (c_attn partials reduced in the prologue, K/V row appended) at
+"""Decode attention at configs[2] shape (or B H S Smax from the command line, e.g. 16 20 960 1024 for configs[3]): the fused instance (c_attn partials reduced in the prologue, K/V row appended) at
 ks = 2 and 6 against the plain instance (q given), each as 12 launches over 12 layers of cache in one CUDA graph."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -6,6 +6,8 @@ import torch
 import lms_b200
 lib, check = lms_b200._lib.load(), lms_b200._lib.check
 B, H, L, S, Smax = 64, 12, 12, 640, 768
+if len(sys.argv) == 5:
+    B, H, S, Smax = (int(a) for a in sys.argv[1:])
 d = H * 64
 g = torch.Generator(device="cuda").manual_seed(0)
 k = torch.randn(L, B, H, Smax, 64, device="cuda", generator=g).bfloat16()
