@@ -102,18 +102,11 @@ __global__ void layernorm_bf16in_kernel(const bf16* __restrict__ x, const float*
   const int lane = threadIdx.x & 31;
   const bf16* xr = x + (size_t)r * d;
   float v[NV8][8];
-  float4 g[NV8][2], b[NV8][2];
   uint4 raw[NV8];
-  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-  for (int j = 0; j < NV8; ++j) {  // every load first: one memory round trip
+  for (int j = 0; j < NV8; ++j) {  // the whole row first: one memory round trip
     const int i = lane * 8 + j * 256;
-    const bool ok = i < d;
-    raw[j] = ok ? *reinterpret_cast<const uint4*>(xr + i) : make_uint4(0, 0, 0, 0);
-    g[j][0] = ok ? load4(gamma + i) : zero;
-    g[j][1] = ok ? load4(gamma + i + 4) : zero;
-    b[j][0] = ok ? load4(beta + i) : zero;
-    b[j][1] = ok ? load4(beta + i + 4) : zero;
+    raw[j] = i < d ? *reinterpret_cast<const uint4*>(xr + i) : make_uint4(0, 0, 0, 0);
   }
   float s = 0.f;
 #pragma unroll
@@ -138,8 +131,11 @@ __global__ void layernorm_bf16in_kernel(const bf16* __restrict__ x, const float*
   for (int j = 0; j < NV8; ++j) {
     const int i = lane * 8 + j * 256;
     if (i < d) {
-      const float gg[8] = {g[j][0].x, g[j][0].y, g[j][0].z, g[j][0].w, g[j][1].x, g[j][1].y, g[j][1].z, g[j][1].w};
-      const float bb[8] = {b[j][0].x, b[j][0].y, b[j][0].z, b[j][0].w, b[j][1].x, b[j][1].y, b[j][1].z, b[j][1].w};
+      // gamma / beta only now (L1 hits after the first rows): held from the start they cost 48 registers per thread and
+      // two thirds of the resident warps, and the kernel is there to stream rows
+      const float4 g0 = load4(gamma + i), g1 = load4(gamma + i + 4), b0 = load4(beta + i), b1 = load4(beta + i + 4);
+      const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+      const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
       float o[8];
 #pragma unroll
       for (int k = 0; k < 8; ++k) o[k] = (v[j][k] - mean) * rstd * gg[k] + bb[k];

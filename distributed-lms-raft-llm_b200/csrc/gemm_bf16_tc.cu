@@ -501,6 +501,10 @@ struct TmaEpilogue {
   // addressed as a [(B*H*Smax), 64] matrix through tmRes / tmV: a piece is one head's 64 dims of 32 consecutive tokens
   // of one sequence (T % 32 == 0), i.e. 32 consecutive cache rows
   int qkv, d, H, T, Smax, pos0;
+  // tile order of the persistent schedule.  1: the column tiles of one row block are neighbours (CTAs of one round read
+  // a row block of A together, so A crosses HBM once: at K = 3072-5120 the 100-170 MB of A do not survive in L2 between
+  // passes, and one pass per column tile measured 292 MB of DRAM reads for a 130 MB GEMM); 0: row blocks first
+  int raster_n;
 };
 
 // EW epilogue warps.  16: every warp owns one 64-column slice of a tile, bias in shared memory, 3 mainloop stages.
@@ -618,7 +622,8 @@ __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
     if (lane == 0) {
       uint32_t it = 0;
       for (int t = tile0; t < ntiles; t += tile_step) {
-        const int a_row0 = (t % m_tiles) * BM * CG + rank * BM, b_row0 = (t / m_tiles) * BN + rank * (BN / CG);
+        const int tm = epi.raster_n ? t / n_tiles : t % m_tiles, tn = epi.raster_n ? t % n_tiles : t / m_tiles;
+        const int a_row0 = tm * BM * CG + rank * BM, b_row0 = tn * BN + rank * (BN / CG);
         for (int kb = 0; kb < nk; ++kb, ++it) {
           const int s = it % L::STAGES;
           mbar_wait(&empty_bar[s], ((it / L::STAGES) & 1) ^ 1, 0);
@@ -682,7 +687,8 @@ __global__ void __launch_bounds__(64 + 32 * EW) gemm_bf16_persistent_tma_kernel(
       else mbar_arrive(&tmem_empty_bar[acc]);
     };
     for (int t = tile0; t < ntiles; t += tile_step, ++ti) {
-      const int a_row0 = (t % m_tiles) * BM * CG + rank * BM, b_row0 = (t / m_tiles) * BN;
+      const int tm = epi.raster_n ? t / n_tiles : t % m_tiles, tn = epi.raster_n ? t % n_tiles : t / m_tiles;
+      const int a_row0 = tm * BM * CG + rank * BM, b_row0 = tn * BN;
       const uint32_t acc = ti & 1;
       const int row0 = a_row0 + quad * 32;
 #pragma unroll 1
@@ -1031,7 +1037,9 @@ int launch_persistent_tma(const bf16* A, int M, const bf16* W, int N, int K, con
   TRY(make_map(&ta, A, M, K, BM));
   TRY(make_map(&tb, W, N, K, 256 / CG));
   const bool f32 = e.out_f32 != nullptr;
-  TmaEpilogue te{e.bias, e.act, e.residual != nullptr || e.residual_bf16 != nullptr, f32 ? 1 : 0, 0, 0, 0, 0, 0, 0};
+  TmaEpilogue te{e.bias, e.act, e.residual != nullptr || e.residual_bf16 != nullptr, f32 ? 1 : 0, 0, 0, 0, 0, 0, 0, 0};
+  static const int raster = getenv("TUTOR_GEMM_RASTER_M") ? 0 : 1;  // TUTOR_GEMM_RASTER_M=1: row blocks first (A/B measurements)
+  te.raster_n = raster;
   if (e.qkv_mode) {
     const int cache_rows = (M / e.T) * e.H * e.Smax;
     TRY(make_map_epi(&to, e.out_bf16, false, M, e.d));
