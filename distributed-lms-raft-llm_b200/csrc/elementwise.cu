@@ -37,7 +37,10 @@ __global__ void gpt2_embed_kernel(const int32_t* __restrict__ ids, int ids_ld, c
 // NV4 = float4 slots per lane (d <= 128*NV4); every load (row, gamma, beta) is issued up front so the kernel
 // pays one memory round trip, not one per slot (the first version loaded gamma/beta inside the output loop:
 // 3.0 us for 64 rows; see profiles/README.md).
-template <int NV4>
+// STREAM (thousands of rows, prefill): gamma / beta are loaded after the statistics instead (L1 hits by then) - held from
+// the start they cost 2 * 4 * NV4 registers per thread and most of the resident warps, and there the kernel is bound by
+// the rows it streams (GPT-2 large, 16384 rows: 27 us for 126 MB).
+template <int NV4, bool STREAM>
 __global__ void layernorm_kernel(const float* __restrict__ x, int in_stride, int in_offset,
                                  const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                                  float* __restrict__ out_f32, bf16* __restrict__ out_bf16, int M, int d) {
@@ -54,8 +57,10 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int in_stride, int
     const int i = lane * 4 + j * 128;
     const bool ok = i < d;
     v[j] = ok ? load4(xr + i) : zero;
-    g[j] = ok ? load4(gamma + i) : zero;
-    b[j] = ok ? load4(beta + i) : zero;
+    if (!STREAM) {
+      g[j] = ok ? load4(gamma + i) : zero;
+      b[j] = ok ? load4(beta + i) : zero;
+    }
   }
   float s = 0.f;
 #pragma unroll
@@ -74,6 +79,7 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int in_stride, int
   for (int j = 0; j < NV4; ++j) {
     const int i = lane * 4 + j * 128;
     if (i < d) {
+      if (STREAM) { g[j] = load4(gamma + i); b[j] = load4(beta + i); }
       float4 o;
       o.x = (v[j].x - mean) * rstd * g[j].x + b[j].x;
       o.y = (v[j].y - mean) * rstd * g[j].y + b[j].y;
@@ -274,9 +280,15 @@ int k_layernorm(const float* x, int in_stride, int in_offset, const float* gamma
   ARG_CHECK(d % 4 == 0 && d <= 32 * LN_MAX_PER_LANE, "layernorm: unsupported d=%d", d);
   if (M == 0) return TUTOR_OK;
   const dim3 grid(ceil_div(M, 4)), block(128);
-#define LN_LAUNCH(NV4)                                                                                              \
-  CUDA_TRY(tutor_launch(layernorm_kernel<NV4>, grid, block, 0, st, x, in_stride, in_offset, gamma, beta, eps, out_f32, \
-                        out_bf16, M, d))
+#define LN_LAUNCH(NV4)                                                                                                  \
+  do {                                                                                                                  \
+    if (M >= 1024)                                                                                                      \
+      CUDA_TRY(tutor_launch(layernorm_kernel<NV4, true>, grid, block, 0, st, x, in_stride, in_offset, gamma, beta, eps,  \
+                            out_f32, out_bf16, M, d));                                                                  \
+    else                                                                                                                \
+      CUDA_TRY(tutor_launch(layernorm_kernel<NV4, false>, grid, block, 0, st, x, in_stride, in_offset, gamma, beta, eps, \
+                            out_f32, out_bf16, M, d));                                                                  \
+  } while (0)
   if (d <= 128) LN_LAUNCH(1);
   else if (d <= 768) LN_LAUNCH(6);
   else if (d <= 1280) LN_LAUNCH(10);

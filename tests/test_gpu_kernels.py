@@ -22,7 +22,8 @@ def rel_err(a, b):
     return ((a.float() - b.float()).abs().max() / b.float().abs().max().clamp_min(1e-12)).item()
 
 
-@pytest.mark.parametrize("M,d,eps", [(5, 128, 1e-5), (64, 768, 1e-5), (33, 1280, 1e-5), (16, 768, 1e-12)])
+@pytest.mark.parametrize("M,d,eps", [(5, 128, 1e-5), (64, 768, 1e-5), (33, 1280, 1e-5), (16, 768, 1e-12),
+                                     (2048, 768, 1e-12), (1501, 1280, 1e-5)])  # >= 1024 rows: the streaming flavour
 def test_layernorm(pkg, lib, M, d, eps):
     g = torch.Generator(device="cpu").manual_seed(0)
     x = (torch.randn(M, d, generator=g) * 3 + 0.5).to(DEV)
