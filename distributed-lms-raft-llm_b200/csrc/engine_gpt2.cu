@@ -121,6 +121,7 @@ struct tutor_gpt2 {
   cudaGraphExec_t graph_exec = nullptr;
   uint64_t graph_kernels = 0;
   bool use_graph = true;
+  bool prefill_pad = true;  // TUTOR_NO_PREFILL_PAD=1: ragged prompts keep their row count (cross-check)
 
   size_t esz() const { return dt == DT_F32 ? 4 : 2; }
   void* kcache(int l) const {
@@ -208,10 +209,24 @@ int forward_decode_persist_f32(tutor_gpt2* e, int B) {
                             e->cfg.layer_norm_epsilon, (float*)e->xn_last, e->stream);
 }
 
+// Rows per sequence of a prefill forward.  bf16 prompts whose length is not a multiple of 32 run as if right-padded to
+// the next one (pad slots hold token 0): causal attention keeps the real positions' results what they were, the pad
+// positions' cache rows sit past the current length (masked, and overwritten by the decode steps that reach them), and the
+// c_attn GEMM keeps its TMA-staged cache scatter, which needs whole 32-token pieces of one sequence (GPT-2 large,
+// 16 x 1023: 182 us per layer through the per-lane-store epilogue against 105 us).  TUTOR_NO_PREFILL_PAD=1 turns it off.
+int prefill_rows(const tutor_gpt2* e, int B, int T) {
+  const int Tp = (T + 31) / 32 * 32;
+  if (!e->prefill_pad || e->dt != DT_BF16 || Tp == T || T < 64 || B * T <= 128 || Tp > e->P || Tp > e->Smax || Tp > e->ids_ld) return T;
+  return Tp;
+}
+
 // One forward over M = B*T tokens.  decode=true: T == 1 and every position comes from the device counter.
-int forward(tutor_gpt2* e, int B, int T, bool decode) {
+int forward(tutor_gpt2* e, int B, int T_real, bool decode) {
+  const int T = decode ? T_real : prefill_rows(e, B, T_real);
   const int M = B * T, d = e->d, dt = e->dt;
   cudaStream_t st = e->stream;
+  if (T != T_real)  // pad slots of the id rows: any valid token
+    CUDA_TRY(cudaMemset2DAsync(e->ids + T_real, (size_t)e->ids_ld * 4, 0, (size_t)(T - T_real) * 4, B, st));
   const int* len_dev = decode ? e->counters : nullptr;
   float* xn_f = dt == DT_F32 ? (float*)e->xn : nullptr;
   bf16* xn_b = dt == DT_BF16 ? (bf16*)e->xn : nullptr;
@@ -262,7 +277,7 @@ int forward(tutor_gpt2* e, int B, int T, bool decode) {
   if (ln_in_gemv)  // folded into the LM-head kernel; CTA 0 also leaves ln_f(x) in xn_last for tutor_gpt2_logits
     return k_lmhead_argmax_ln(e->x, dt, e->wte, dt, B, e->V, d, e->dstate(), e->lm_scratch, e->lnf_g, e->lnf_b,
                               e->cfg.layer_norm_epsilon, (float*)e->xn_last, st);
-  TRY(k_layernorm(e->x, T, T - 1, e->lnf_g, e->lnf_b, e->cfg.layer_norm_epsilon,
+  TRY(k_layernorm(e->x, T, T_real - 1, e->lnf_g, e->lnf_b, e->cfg.layer_norm_epsilon,
                   dt == DT_F32 ? (float*)e->xn_last : nullptr, dt == DT_BF16 ? (bf16*)e->xn_last : nullptr, B, d, st));
   TRY(k_lmhead_argmax(e->xn_last, dt, e->wte, dt, B, e->V, d, e->dstate(), e->lm_scratch, st));
   return TUTOR_OK;
@@ -641,7 +656,7 @@ int ensure_capacity(tutor_gpt2* e, int B, int T, int total) {
     TRY(dev_alloc(&e->xn_last, (size_t)nb * e->d * 4));
     e->Bcap = nb; e->Smax = ns;
   }
-  const int M = B * T;
+  const int M = B * ((T + 31) / 32 * 32);  // room for a prefill that rounds its rows up (prefill_rows)
   if (M > e->Mcap) {
     drop_graph(e);
     ++e->alloc_epoch;
@@ -831,6 +846,7 @@ int tutor_gpt2_create(const tutor_gpt2_config* cfg, int device, tutor_gpt2_t** o
   e->d = cfg->n_embd; e->H = cfg->n_head; e->L = cfg->n_layer; e->V = cfg->vocab_size; e->P = cfg->n_positions;
   e->layers.resize(e->L);
   e->use_graph = getenv("TUTOR_NO_GRAPH") == nullptr;
+  e->prefill_pad = getenv("TUTOR_NO_PREFILL_PAD") == nullptr;
   e->use_fused = getenv("TUTOR_NO_FUSED") == nullptr;  // debugging aids: unfused decode kernels / no PDL
   e->use_pdl = getenv("TUTOR_NO_PDL") == nullptr;
   e->use_cluster = getenv("TUTOR_NO_CLUSTER") == nullptr;

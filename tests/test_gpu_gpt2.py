@@ -357,6 +357,28 @@ def test_bf16_ragged_shapes_against_oracle_logits(pkg, tiny_hf, B, T):
     assert int(a.min()) >= 0 and int(a.max()) < 1000
 
 
+@pytest.mark.parametrize("B,T,new", [(3, 65, 20), (16, 70, 30), (4, 199, 40), (2, 225, 30)])
+def test_prefill_rows_rounded_up_to_32_change_nothing(pkg, tiny_hf, monkeypatch, B, T, new):
+    """bf16 prompts whose length is not a multiple of 32 are prefilled as if right-padded to the next one (the c_attn
+    GEMM keeps its TMA cache scatter): prefill logits and every generated id equal those of the unpadded prefill, also
+    when the cache rows the pad positions wrote are reached and overwritten by the decode steps."""
+    ids = rp.gpt2_prompt_ids(B, T, seed=B + T, vocab=1000)
+    res = {}
+    for name, env in (("padded", None), ("plain", "1")):
+        monkeypatch.delenv("TUTOR_NO_PREFILL_PAD", raising=False)
+        if env:
+            monkeypatch.setenv("TUTOR_NO_PREFILL_PAD", env)
+        eng = pkg.B200GPT2LMHeadModel.from_hf(tiny_hf, dtype="bf16")
+        eng.prefill(ids, max_new_tokens=new, eos_token_id=999, pad_token_id=999)
+        logits = eng.last_logits().float().cpu()
+        out = eng.generate(ids, max_new_tokens=new, repetition_penalty=1.2, eos_token_id=999, pad_token_id=999)
+        res[name] = (logits, out)
+        del eng
+    # same arithmetic per row in both runs except the c_attn epilogue flavour (same accumulation order): tight tolerance
+    assert (res["padded"][0] - res["plain"][0]).abs().max().item() <= 1e-3 * res["plain"][0].abs().max().item()
+    assert torch.equal(res["padded"][1], res["plain"][1])
+
+
 @pytest.mark.parametrize("B,T", [(1, 9), (5, 40), (16, 70), (33, 20), (64, 130), (100, 20)])
 def test_persistent_decode_kernel_matches_launch_chain(pkg, tiny_hf, monkeypatch, B, T):
     """The opt-in persistent decode kernel (TUTOR_MEGA=1: LayerNorm folded into the weights, TMA operands, split-K
