@@ -94,7 +94,9 @@ int forward(tutor_bert* e, int B, int T) {
   cudaStream_t st = e->stream;
   const float eps = e->cfg.layer_norm_eps;
   bf16* xb = dt == DT_BF16 ? e->xb : nullptr;
-  TRY(k_bert_embed_ln(e->ids, T, e->word, dt, e->pos, e->type0, e->emb_g, e->emb_b, eps, e->x, xb, M, d, st));
+  // (the bf16 activation stream has no use for the fp32 copy of the embeddings unless they are the output)
+  TRY(k_bert_embed_ln(e->ids, T, e->word, dt, e->pos, e->type0, e->emb_g, e->emb_b, eps,
+                      e->bf16_stream && e->L > 0 ? nullptr : e->x, xb, M, d, st));
   for (int l = 0; l < e->L; ++l) {
     const BertLayer& w = e->layers[l];
     GemmEpilogue qe{};  // fused query/key/value (modeling_bert.py:158-160, 179-181)
