@@ -291,8 +291,10 @@ __global__ void __launch_bounds__(DK_THREADS, 6) attn_decode_tma_kernel(const bf
                                                                     const QkvFold fold, const int* __restrict__ npad,
                                                                     int safe_rows) {
   constexpr int EPL = 8, LPR = 8, KPW = 4, NG = 16, UNR = DK_CHUNK / NG;
-  __shared__ __align__(128) bf16 sK[DK_STAGES][DK_CHUNK * 64];
-  __shared__ __align__(128) bf16 sV[DK_STAGES][DK_CHUNK * 64];
+  // the ring is dynamic shared memory (2 * DK_STAGES * DK_CHUNK * 128 bytes: four stages exceed the static limit)
+  extern __shared__ __align__(128) uint8_t dk_ring[];
+  bf16(*sK)[DK_CHUNK * 64] = reinterpret_cast<bf16(*)[DK_CHUNK * 64]>(dk_ring);
+  bf16(*sV)[DK_CHUNK * 64] = sK + DK_STAGES;
   __shared__ __align__(8) uint64_t full_bar[DK_STAGES], empty_bar[DK_STAGES];
   __shared__ float s_new[3][64];
   __shared__ float sm_m[NG], sm_l[NG], sm_o[NG][64];
@@ -1015,22 +1017,25 @@ bool use_mma_decode() {
 }  // namespace
 
 // number of key-range splits: enough CTAs for ~8 per SM, at least 64 keys per split
+static int num_sms_cached() {
+  static const int n = [] {
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return sms;
+  }();
+  return n;
+}
+
 int k_attn_decode_splits(int B, int H, int len_hint, int num_sms) {
   // fewer (b,h) streams than SMs: split until every SM has work
   int n = 1;
   while (n < 8 && B * H * n < num_sms && len_hint / (2 * n) >= 64) n *= 2;
-  // more streams than SMs: aim at one full wave of the ring kernels' 6 CTAs per SM.  B*H = 768 (GPT-2 small, B = 64):
-  // one CTA per (b,h) is already 5.2 per SM and every split measured slower (see use_mma_decode).  B*H = 320 (GPT-2
-  // large, B = 16) leaves the SMs a third empty: 3 key-range splits of the register kernel (960 CTAs, last-arriver merge)
-  // took the decode forward from 1.91 to 1.74 ms, while 2 / 4 / 5 / 6 / 8 splits gave 1.88 / 1.94 / 1.90 / 1.92 / 1.99 ms
-  // and the tensor-core ring kernel with 3 splits 1.97 ms.
-  int best = 1;
-  long best_gap = labs((long)B * H - 6L * num_sms);
-  for (int c = 2; c <= 4 && len_hint / c >= 128; ++c) {
-    const long gap = labs((long)B * H * c - 6L * num_sms);
-    if (gap < best_gap) { best_gap = gap; best = c; }
-  }
-  return best;
+  // more streams than SMs: one ring CTA per (sequence, head), whose ring is four stages deep while at most three of them
+  // share an SM (k_attn_decode_fused).  GPT-2 large, cache ~960, decode forward with that against the best key-range split
+  // of the register kernel (3 splits at B = 16): B = 8: 1440 vs 1465 us, 12: 1499 vs 1552, 16: 1580 vs 1722, 20: 1733 vs
+  // 2005, 24 (two stages): 1963 vs 2089.  B*H = 768 (GPT-2 small, B = 64) is 5.2 two-stage CTAs per SM and HBM-bound.
+  if ((long)B * H > num_sms) return 1;
+  return n;
 }
 size_t k_attn_decode_scratch_bytes(int B, int H) { return (size_t)B * H * (8 * 66 * sizeof(float) + sizeof(int)); }
 
@@ -1063,7 +1068,7 @@ int k_attn_decode(const void* q, int q_dtype, const void* k, const void* v, int 
     } else
 #endif
     {
-      attn_decode_tma_kernel<false, 64, 2, true><<<grid, DK_THREADS, 0, st>>>((const bf16*)q, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax,
+      attn_decode_tma_kernel<false, 64, 2, true><<<grid, DK_THREADS, 2 * 2 * 64 * 128, st>>>((const bf16*)q, (bf16*)k, (bf16*)v, (bf16*)out, H, Smax,
                                                                  len_dev, len_host, nullptr, 0, nullptr, B, QkvFold{}, npad, 0);
     }
   } else {
@@ -1102,9 +1107,17 @@ int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias,
   }
 #endif
   if (nsplit == 1) {
+    // few (sequence, head) streams per SM (GPT-2 large at B = 16: 320 CTAs, 2.2 per SM): each CTA is bound by the latency
+    // of its own ring, not by HBM, so it gets four stages instead of two (three such CTAs still share an SM)
+    const bool deep = (long)B * H <= 3L * num_sms_cached();
     auto kern = fold.s ? attn_decode_tma_kernel<true, 64, 2, true, true> : attn_decode_tma_kernel<true, 64, 2, true, false>;
-    CUDA_TRY(tutor_launch(kern, dim3(H, B), dim3(DK_THREADS), 0, st, (const bf16*)nullptr, (bf16*)k, (bf16*)v, (bf16*)out, H,
-                          Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B, fold, npad, safe_rows));
+    if (deep) {
+      kern = fold.s ? attn_decode_tma_kernel<true, 64, 4, true, true> : attn_decode_tma_kernel<true, 64, 4, true, false>;
+      TRY(tutor_set_max_smem(reinterpret_cast<const void*>(kern), 2 * 4 * 64 * 128));
+    }
+    CUDA_TRY(tutor_launch(kern, dim3(H, B), dim3(DK_THREADS), (size_t)(2 * (deep ? 4 : 2) * 64 * 128), st, (const bf16*)nullptr,
+                          (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B, fold, npad,
+                          safe_rows));
     KERNEL_LAUNCHED();
     return TUTOR_OK;
   }

@@ -5,7 +5,8 @@ import torch
 import lms_b200
 from oracle import reference_path as rp
 hf = rp.build_gpt2("large", seed=0)
-ids = rp.gpt2_prompt_ids(16, 896, seed=1)
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 16
+ids = rp.gpt2_prompt_ids(B, 896, seed=1)
 VARIANTS = [{}, {"TUTOR_ATTN_SPLITS": "1"}]
 for env in VARIANTS:
     for k in ("TUTOR_ATTN_SPLITS", "TUTOR_ATTN_MMA"):
@@ -21,6 +22,6 @@ for env in VARIANTS:
     eng.step(100)
     e1.record(stream)
     torch.cuda.synchronize()
-    print(f"{env or 'default'}: {e0.elapsed_time(e1) * 10:.1f} us per decode forward", flush=True)
+    print(f"B={B} {env or 'default'}: {e0.elapsed_time(e1) * 10:.1f} us per decode forward", flush=True)
     del eng
     torch.cuda.empty_cache()
