@@ -6,8 +6,10 @@ import torch
 import lms_b200
 lib, check = lms_b200._lib.load(), lms_b200._lib.check
 B, H, L, S, Smax = 64, 12, 12, 640, 768
-if len(sys.argv) == 5:
-    B, H, S, Smax = (int(a) for a in sys.argv[1:])
+if len(sys.argv) >= 5:
+    B, H, S, Smax = (int(a) for a in sys.argv[1:5])
+if len(sys.argv) == 6:
+    L = int(sys.argv[5])  # 1: every launch streams the same layer (L2-resident when it fits)
 d = H * 64
 g = torch.Generator(device="cuda").manual_seed(0)
 k = torch.randn(L, B, H, Smax, 64, device="cuda", generator=g).bfloat16()
