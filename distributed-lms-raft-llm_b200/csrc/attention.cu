@@ -1108,16 +1108,17 @@ int k_attn_decode_fused(const float* qkv_partial, int ks, const float* qkv_bias,
 #endif
   if (nsplit == 1) {
     // few (sequence, head) streams per SM (GPT-2 large at B = 16: 320 CTAs, 2.2 per SM): each CTA is bound by the latency
-    // of its own ring, not by HBM, so it gets four stages instead of two (three such CTAs still share an SM)
-    const bool deep = (long)B * H <= 3L * num_sms_cached();
+    // of its own ring, not by HBM, so the ring is as deep as the number of CTAs that must share an SM allows: four stages
+    // up to 3 CTAs per SM, three up to 4, else two (6 per SM)
+    const long bh = (long)B * H, sms = num_sms_cached();
+    const int stages = bh <= 3 * sms ? 4 : bh <= 4 * sms ? 3 : 2;
     auto kern = fold.s ? attn_decode_tma_kernel<true, 64, 2, true, true> : attn_decode_tma_kernel<true, 64, 2, true, false>;
-    if (deep) {
-      kern = fold.s ? attn_decode_tma_kernel<true, 64, 4, true, true> : attn_decode_tma_kernel<true, 64, 4, true, false>;
-      TRY(tutor_set_max_smem(reinterpret_cast<const void*>(kern), 2 * 4 * 64 * 128));
-    }
-    CUDA_TRY(tutor_launch(kern, dim3(H, B), dim3(DK_THREADS), (size_t)(2 * (deep ? 4 : 2) * 64 * 128), st, (const bf16*)nullptr,
-                          (bf16*)k, (bf16*)v, (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B, fold, npad,
-                          safe_rows));
+    if (stages == 4) kern = fold.s ? attn_decode_tma_kernel<true, 64, 4, true, true> : attn_decode_tma_kernel<true, 64, 4, true, false>;
+    if (stages == 3) kern = fold.s ? attn_decode_tma_kernel<true, 64, 3, true, true> : attn_decode_tma_kernel<true, 64, 3, true, false>;
+    const int ring_bytes = 2 * stages * 64 * 128;
+    if (stages > 2) TRY(tutor_set_max_smem(reinterpret_cast<const void*>(kern), ring_bytes));
+    CUDA_TRY(tutor_launch(kern, dim3(H, B), dim3(DK_THREADS), (size_t)ring_bytes, st, (const bf16*)nullptr, (bf16*)k, (bf16*)v,
+                          (bf16*)out, H, Smax, len_dev, len_host, qkv_partial, ks, qkv_bias, B, fold, npad, safe_rows));
     KERNEL_LAUNCHED();
     return TUTOR_OK;
   }

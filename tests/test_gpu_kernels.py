@@ -189,7 +189,9 @@ def test_attn_decode(pkg, lib, dtype, B, H, S):
     assert (out.float() - ref).abs().max().item() < tol
 
 
-@pytest.mark.parametrize("B,H,S,ks", [(1, 2, 5, 1), (5, 12, 130, 3), (64, 12, 640, 6), (16, 20, 961, 4)])
+# B*H = 768 / 320 / 520: the two-, four- and three-stage rings of the TMA kernel
+@pytest.mark.parametrize("B,H,S,ks", [(1, 2, 5, 1), (5, 12, 130, 3), (64, 12, 640, 6), (16, 20, 961, 4), (26, 20, 417, 2),
+                                      (20, 12, 64, 2)])
 def test_attn_decode_fused(pkg, lib, B, H, S, ks):
     """The decode step's own attention instance: split-K partials of c_attn summed in order + bias, K/V row appended at
     position S-1, attention over S rows - against fp64 SDPA on the same (bf16-rounded) q, k, v."""
