@@ -53,33 +53,52 @@ __global__ void __launch_bounds__(256) gemv_f32_kernel(const float* __restrict__
   }
 }
 
-// Short prompts (9..64 rows, e.g. the 32-token prompt of the reference's own configuration): the same weight-streaming
-// scheme with the rows cut into chunks of 8 along gridDim.y.  A 64x64-tiled SGEMM has only N/64 = 12..48 CTAs here and
-// spends ~100 us per layer GEMM in its k-loop; this form puts N/8 x M/8 CTAs on the weights (read once per row chunk,
-// from L2 after the first) - 5.7 ms -> about 1 ms for the 32-token fp32 prefill of GPT-2 small.
+// Short prompts (9..64 rows, e.g. the 32-token prompt of the reference's own configuration).  A 64x64-tiled SGEMM has only
+// N/64 = 12..48 CTAs here and spends ~100 us per layer GEMM in its k-loop.  Weight-streaming form with register blocking:
+// a warp owns 4 weight rows x 8 input rows; per k-step a lane loads 4 + 8 float4 and issues 128 FMAs (the first version
+// of this kernel - one weight row per warp, 9 loads per 32 FMAs - was bound by its loads: 1.97 ms for the 32-token fp32
+// prefill of GPT-2 small).  The 32 lane-partial sums are combined by a butterfly that halves the values a lane holds at
+// every step (31 shuffles, fixed order: deterministic), after which lane l owns (weight row l / 8, input row l % 8).
+// Weights cross HBM once and are re-read from L2 by the other M/8 row chunks.
 __global__ void __launch_bounds__(256) gemv_f32_rows_kernel(const float* __restrict__ A, const float* __restrict__ W,
                                                              int M, int N, int K, GemmEpilogue epi) {
-  constexpr int MB = 8;
+  constexpr int RN = 4, MB = 8;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n = blockIdx.x * 8 + warp, m0 = blockIdx.y * MB;
-  if (n >= N) return;
-  const float* w = W + (size_t)n * K;
-  float acc[MB];
+  const int n0 = (blockIdx.x * 8 + warp) * RN, m0 = blockIdx.y * MB;
+  if (n0 >= N) return;
+  const float* w[RN];
+  const float* a[MB];
 #pragma unroll
-  for (int m = 0; m < MB; ++m) acc[m] = 0.f;
+  for (int r = 0; r < RN; ++r) w[r] = W + (size_t)min(n0 + r, N - 1) * K;  // rows past N / M are clamped and never stored
+#pragma unroll
+  for (int m = 0; m < MB; ++m) a[m] = A + (size_t)min(m0 + m, M - 1) * K;
+  float acc[RN * MB];
+#pragma unroll
+  for (int i = 0; i < RN * MB; ++i) acc[i] = 0.f;
   for (int k = lane * 4; k < K; k += 128) {
-    const float4 w0 = load4(w + k);
+    float4 wv[RN], av[MB];
 #pragma unroll
-    for (int m = 0; m < MB; ++m) {
-      const float4 a0 = load4(A + (size_t)min(m0 + m, M - 1) * K + k);  // rows past M are clamped and never stored
-      acc[m] += w0.x * a0.x + w0.y * a0.y + w0.z * a0.z + w0.w * a0.w;
+    for (int r = 0; r < RN; ++r) wv[r] = load4(w[r] + k);
+#pragma unroll
+    for (int m = 0; m < MB; ++m) av[m] = load4(a[m] + k);
+#pragma unroll
+    for (int r = 0; r < RN; ++r)
+#pragma unroll
+      for (int m = 0; m < MB; ++m)
+        acc[r * MB + m] += wv[r].x * av[m].x + wv[r].y * av[m].y + wv[r].z * av[m].z + wv[r].w * av[m].w;
+  }
+  // butterfly: at distance off a lane keeps the half of its values selected by its own bit and sends the other half
+#pragma unroll
+  for (int off = 16, cnt = RN * MB; off >= 1; off >>= 1, cnt >>= 1) {
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < cnt / 2; ++i) {
+      const float lo = acc[i], hi = acc[i + cnt / 2];
+      acc[i] = (upper ? hi : lo) + __shfl_xor_sync(0xffffffffu, upper ? lo : hi, off);
     }
   }
-#pragma unroll
-  for (int m = 0; m < MB; ++m) {
-    const float s = warp_sum(acc[m]);
-    if (lane == 0 && m0 + m < M) epilogue_store(epi, m0 + m, n, s);
-  }
+  const int r = lane >> 3, m = lane & 7;
+  if (n0 + r < N && m0 + m < M) epilogue_store(epi, m0 + m, n0 + r, acc[0]);
 }
 
 // Same GEMV with the preceding LayerNorm folded in (decode, M <= 8): every CTA normalises the M input rows into
@@ -439,7 +458,7 @@ int k_gemm_f32(const float* A, const float* W, int M, int N, int K, const GemmEp
     }
 #undef GEMV_CASE
   } else if (M <= 64 && K % 128 == 0) {
-    gemv_f32_rows_kernel<<<dim3(ceil_div(N, 8), ceil_div(M, 8)), 256, 0, st>>>(A, W, M, N, K, epi);
+    gemv_f32_rows_kernel<<<dim3(ceil_div(N, 32), ceil_div(M, 8)), 256, 0, st>>>(A, W, M, N, K, epi);
   } else {
     ARG_CHECK(K % BK == 0, "gemm_f32: K=%d must be a multiple of %d", K, BK);
     dim3 grid(ceil_div(N, BN), ceil_div(M, BM)), block(256);

@@ -51,7 +51,10 @@ def _linear_ref(A, W, bias, res, act):
 
 @pytest.mark.parametrize("M,N,K,act,use_res", [(1, 768, 768, 0, True), (3, 2304, 768, 0, False), (8, 3072, 768, 1, False),
                                                (1, 768, 3072, 0, True), (37, 200, 128, 2, True),
-                                               (256, 384, 512, 1, False)])
+                                               (256, 384, 512, 1, False),
+                                               # 9..64 rows: the register-blocked weight-streaming kernel (4 x 8 per warp)
+                                               (32, 3072, 768, 1, False), (64, 768, 3072, 0, True), (9, 2304, 768, 0, False),
+                                               (33, 50, 256, 2, True), (17, 1001, 128, 0, True)])
 def test_linear_f32(pkg, lib, M, N, K, act, use_res):
     g = torch.Generator().manual_seed(M * 7 + N)
     A, W = torch.randn(M, K, generator=g).to(DEV), (torch.randn(N, K, generator=g) * 0.05).to(DEV)
