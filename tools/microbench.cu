@@ -1,7 +1,8 @@
 // Ground truth for the launch-bound decode chain: per-kernel cost of dependent launches inside a CUDA graph,
 // with and without programmatic dependent launch, for an empty kernel and for the library's decode kernels.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -I distributed-lms-raft-llm_b200/csrc \
-//        tools/microbench.cu -o gpurun_out/microbench -L distributed-lms-raft-llm_b200 -ltutor_b200
+//        tools/microbench.cu -o gpurun_out/microbench -L distributed-lms-raft-llm_b200 -ltutor_b200 -lcuda
+// (-DTUTOR_TRACE -DTUTOR_EXPERIMENTS adds the decode-attention template variants)
 #include <cstdio>
 #include <cstdlib>
 #include <functional>
@@ -125,11 +126,11 @@ int main() {
 #define ATT(NAME, ...)                                                                                              \
       t = time_graph(st, 48, false, [&](int i) { __VA_ARGS__; });                                                    \
       printf("attn %-42s %6.2f us  %7.2f TB/s\n", NAME, t, mb / t * 1e-3);
-      ATT("register kernel (128 thr)", (attn_decode_kernel<bf16, bf16, bf16, true, false><<<dim3(12, 64), 128, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, nullptr, nullptr)));
-      ATT("ring chunk 64 x 2 stages", (attn_decode_tma_kernel<false, 64, 2, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
-      ATT("ring chunk 64 x 2 stages, no math", (attn_decode_tma_kernel<false, 64, 2, false><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
-      ATT("ring chunk 32 x 4 stages", (attn_decode_tma_kernel<false, 32, 4, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
-      ATT("ring chunk 32 x 4 stages, no math", (attn_decode_tma_kernel<false, 32, 4, false><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
+      ATT("register kernel (128 thr)", (attn_decode_kernel<bf16, bf16, bf16, true, false><<<dim3(12, 64), 128, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, QkvFold{}, nullptr, nullptr, nullptr)));
+      ATT("ring chunk 64 x 2 stages", (attn_decode_tma_kernel<false, 64, 2, true><<<dim3(12, 64), 160, 32768, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, QkvFold{}, nullptr, 0)));
+      ATT("ring chunk 64 x 2 stages, no math", (attn_decode_tma_kernel<false, 64, 2, false><<<dim3(12, 64), 160, 32768, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, QkvFold{}, nullptr, 0)));
+      ATT("ring chunk 32 x 4 stages", (attn_decode_tma_kernel<false, 32, 4, true><<<dim3(12, 64), 160, 32768, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, QkvFold{}, nullptr, 0)));
+      ATT("ring chunk 32 x 4 stages, no math", (attn_decode_tma_kernel<false, 32, 4, false><<<dim3(12, 64), 160, 32768, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, QkvFold{}, nullptr, 0)));
       {  // tensor-core consumers: the cache of every "layer" as a [768*768, 64] bf16 matrix behind a tensor map
         static CUtensorMap tk[12], tv[12];
         for (int i = 0; i < 12; ++i) {
@@ -138,7 +139,7 @@ int main() {
         ATT("mma ring chunk 32 x 4 stages", (attn_decode_mma_kernel<false, true><<<dim3(12, 64), DM_THREADS, 0, st>>>(tk[i % 12], tv[i % 12], qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0, 0, nullptr, nullptr)));
         ATT("mma ring chunk 32 x 4 stages, no math", (attn_decode_mma_kernel<false, false><<<dim3(12, 64), DM_THREADS, 0, st>>>(tk[i % 12], tv[i % 12], qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0, 0, nullptr, nullptr)));
       }
-      ATT("ring chunk 16 x 8 stages", (attn_decode_tma_kernel<false, 16, 8, true><<<dim3(12, 64), 160, 0, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, nullptr, 0)));
+      ATT("ring chunk 16 x 8 stages", (attn_decode_tma_kernel<false, 16, 8, true><<<dim3(12, 64), 160, 32768, st>>>(qq, kp(i), vp(i), oo, 12, 768, nullptr, 640, nullptr, 0, nullptr, 64, QkvFold{}, nullptr, 0)));
     }
 #endif
     cudaFree(big); cudaFree(sink);
