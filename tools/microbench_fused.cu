@@ -76,11 +76,11 @@ int main() {
       printf("c_fc LN -> cluster gelu ks=%2d bn=%3d  %6.2f us/kernel\n", cfg.first, cfg.second, t); show_trace();
     }
     for (auto cfg : {std::pair<int,int>{6, 32}, {6, 16}}) {
-      t = time_graph(st, 96, pdl, [&](int i) { if (k_gemm_resid_stats(a, W(i), bias, B, d, d, cfg.first, cfg.second, xf, stats, st)) DIE(); });
+      t = time_graph(st, 96, pdl, [&](int i) { if (k_gemm_resid_stats(a, W(i), bias, B, d, d, cfg.first, cfg.second, xf, stats, nullptr, st)) DIE(); });
       printf("proj -> cluster resid   ks=%2d bn=%3d  %6.2f us/kernel\n", cfg.first, cfg.second, t); show_trace();
     }
     for (auto cfg : {std::pair<int,int>{8, 32}, {8, 16}}) {
-      t = time_graph(st, 96, pdl, [&](int i) { if (k_gemm_resid_stats(h, W(i), bias, B, d, 4 * d, cfg.first, cfg.second, xf, stats, st)) DIE(); });
+      t = time_graph(st, 96, pdl, [&](int i) { if (k_gemm_resid_stats(h, W(i), bias, B, d, 4 * d, cfg.first, cfg.second, xf, stats, nullptr, st)) DIE(); });
       printf("proj2 -> cluster resid  ks=%2d bn=%3d  %6.2f us/kernel\n", cfg.first, cfg.second, t); show_trace();
     }
     // the layer's GEMM chain as the engine issues it (attention left out)
@@ -88,9 +88,9 @@ int main() {
       int rc = 0;
       switch (i & 3) {
         case 0: rc = k_gemm_ln_splitk(xf, stats, 6, gam, bias, 1e-5f, W(i), B, 3 * d, d, 6, 64, partial, st); break;
-        case 1: rc = k_gemm_resid_stats(a, W(i), bias, B, d, d, 6, 32, xf, stats, st); break;
+        case 1: rc = k_gemm_resid_stats(a, W(i), bias, B, d, d, 6, 32, xf, stats, nullptr, st); break;
         case 2: rc = k_gemm_ln_act(xf, stats, 6, gam, bias, 1e-5f, W(i), bias, ACT_GELU_TANH, B, 4 * d, d, 6, 64, h, st); break;
-        default: rc = k_gemm_resid_stats(h, W(i), bias, B, d, 4 * d, 8, 32, xf, stats, st);
+        default: rc = k_gemm_resid_stats(h, W(i), bias, B, d, 4 * d, 8, 32, xf, stats, nullptr, st);
       }
       if (rc) DIE();
     });
